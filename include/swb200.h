@@ -1,0 +1,139 @@
+/*
+ * swb200.h -- C ABI of the B200-native Smith-Waterman / Needleman-Wunsch engine.
+ *
+ * This is the drop-in boundary for the alignment path of yamule/smithwaterman.  The reference has
+ * no FFI layer; the entry points below are what a Rust `-sys` crate (or cgo/ctypes) would bind to
+ * replace the following reference interfaces ("SA.rs" = rust/sequence_alignment/src/
+ * sequence_alignment.rs, "OCL.rs" = rust/sa_opencl/src/opencl_sequence_alignment.rs,
+ * "OCL-main.rs" = rust/sa_opencl/src/main.rs):
+ *
+ *   swb_engine_create      SequenceAlignment::new            SA.rs:26-45   (OCL.rs:103 new)
+ *   swb_engine_destroy     Drop of SequenceAlignment / OpenCLSequenceAlignment
+ *   swb_align              SequenceAlignment::align          SA.rs:389-392 (OCL.rs:796 align)
+ *   swb_align_batch        the serial loop of `sa_opencl -list`  OCL-main.rs:295-316 (one call, n pairs)
+ *   swb_score_batch        align_partial(.., score_only=true) per pair  SA.rs:393-467
+ *   swb_batch_*            the same as swb_score_batch, split into upload / run / fetch so that a
+ *                          caller can keep inputs resident in HBM (bench.py `value` vs `e2e`)
+ *   swb_alignment_free     Drop of the (Vec<String>,Vec<String>,f32) result
+ *   swb_last_error         replaces the reference's panics (SA.rs:370,636,676; OCL.rs:38)
+ *
+ * Conventions: plain pointers and sizes, no C++/torch types.  Sequences are byte strings, one
+ * residue per byte (the reference holds one `String` per residue, SA.rs:799-803; every letter its
+ * matrices know is one ASCII byte).  Unknown letters map to the matrix's `X` row, or fail with
+ * SWB_ERR_LETTER when the matrix has no `X` (SA.rs:669-679).  Penalties are sign-insensitive
+ * (SA.rs:28-35).  An engine is NOT thread-safe (the reference takes `&mut self`); distinct
+ * engines may be used concurrently.  There is no CPU fallback: every entry point that computes
+ * needs a CUDA device and fails with SWB_ERR_CUDA otherwise.
+ */
+#ifndef SWB200_H
+#define SWB200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* alignment_type, SA.rs:11-13 */
+#define SWB_GLOBAL 0
+#define SWB_GLOCAL 1
+#define SWB_LOCAL 2
+
+/* status codes (0 = ok) */
+#define SWB_OK 0
+#define SWB_ERR_ARG 1      /* bad argument (null pointer, bad mode, too many letters, ...) */
+#define SWB_ERR_SCALE 2    /* matrix / penalties are not on a common integer grid (<= 1/1024 or 1/1000) */
+#define SWB_ERR_LETTER 3   /* unknown residue and the matrix has no X row (SA.rs:676) */
+#define SWB_ERR_CUDA 4     /* CUDA runtime error or no device */
+#define SWB_ERR_EMPTY 5    /* both sequences empty in a non-local mode (reference panics, SA.rs:360-363) */
+#define SWB_ERR_NOMEM 6
+#define SWB_ERR_RANGE 7    /* scores do not fit the int32 lanes */
+
+/* flags of the batch calls */
+#define SWB_RETAIN_ALL 1u  /* retain_all of SA.rs:389 (ignored = forced for non-local modes, SA.rs:506) */
+
+typedef struct swb_engine swb_engine;
+typedef struct swb_batch swb_batch;
+
+/* Substitution matrix, SubstitutionMatrix of SA.rs:626-631: n letters, scores[a*n+b] (f32). */
+typedef struct swb_matrix {
+    int32_t n_letters;
+    const char *letters;     /* n_letters bytes, index = position (SA.rs:627-628) */
+    const float *scores;     /* n_letters*n_letters, row-major [a][b] (SA.rs:629) */
+} swb_matrix;
+
+/* Result of one alignment, the (Vec<i64>,Vec<i64>,f32) of backtrack SA.rs:273 plus the strings of
+ * align_partial SA.rs:470-550.  Owned by the library; release with swb_alignment_free. */
+typedef struct swb_alignment {
+    float score;             /* SA.rs:386 */
+    int64_t end_a, end_b;    /* 1-based DP cell the traceback starts from; -1,-1 = empty local alignment */
+    int64_t n_cols;          /* columns of the core alignment (length of idx_a / idx_b) */
+    int64_t *idx_a;          /* residue index per column, -1 = gap (SA.rs:359-373) */
+    int64_t *idx_b;
+    int64_t aln_len;         /* strlen(aln_a) == strlen(aln_b) */
+    char *aln_a;             /* padded strings per retain_all (SA.rs:502-550), NUL-terminated */
+    char *aln_b;
+} swb_alignment;
+
+/* Counters of the last compute call on an engine. */
+typedef struct swb_stats {
+    double cells;            /* sum la*lb of the requested work */
+    double kernel_ms;        /* device time of the DP kernels (CUDA events on the engine's stream) */
+    double h2d_bytes, d2h_bytes;
+    int64_t launches;        /* kernels launched */
+    int64_t i32_reruns;      /* pairs re-run in int32 lanes after s16 overflow */
+    int32_t scale;           /* integer rescaling factor in use (10/0.5 -> 2) */
+    int32_t exact_scale;     /* 1 = every input was exactly representable on the integer grid */
+} swb_stats;
+
+/* Built-in matrices (SA.rs:697-733 BLOSUM62, 24 letters; SA.rs:681-695 match/mismatch, A-Z).
+ * `scores` must hold n*n floats and `letters` n bytes; returns n (24 / 26). */
+int32_t swb_matrix_blosum62(char *letters, float *scores);
+int32_t swb_matrix_match_mismatch(float match, float mismatch, char *letters, float *scores);
+
+int swb_engine_create(const swb_matrix *m, float gap_open, float gap_extend, int mode, int device,
+                      swb_engine **out);
+void swb_engine_destroy(swb_engine *e);
+const char *swb_last_error(const swb_engine *e);   /* e may be NULL: last create error */
+int swb_get_stats(const swb_engine *e, swb_stats *out);
+int swb_device_count(void);
+
+/* One pair with traceback (SA.rs:389).  out is filled on SWB_OK. */
+int swb_align(swb_engine *e, const char *a, int64_t la, const char *b, int64_t lb, int retain_all,
+              swb_alignment *out);
+/* n pairs with traceback; sequences k = a_all[off_a[k]..off_a[k+1]), same for b; outs[n]. */
+int swb_align_batch(swb_engine *e, const char *a_all, const int64_t *off_a, const char *b_all,
+                    const int64_t *off_b, int64_t n, unsigned flags, swb_alignment *outs);
+void swb_alignment_free(swb_alignment *a);
+
+/* Score + end cell of n pairs, HOST buffers in and out (H2D, kernels, D2H inside the call).
+ * scores[k] as the reference's f32; end_a/end_b: first-maximum cell (local, SA.rs:286-294;
+ * -1,-1 when no positive score) or (la,lb) (global/glocal, SA.rs:296-309). */
+int swb_score_batch(swb_engine *e, const char *a_all, const int64_t *off_a, const char *b_all,
+                    const int64_t *off_b, int64_t n, float *scores, int64_t *end_a, int64_t *end_b);
+
+/* The same, staged: upload (encode + pack + H2D) once, run the kernels any number of times on the
+ * resident batch, fetch (D2H + unpermute).  swb_batch_run is asynchronous on the engine's stream;
+ * swb_batch_fetch synchronises. */
+int swb_batch_upload(swb_engine *e, const char *a_all, const int64_t *off_a, const char *b_all,
+                     const int64_t *off_b, int64_t n, swb_batch **out);
+int swb_batch_run(swb_engine *e, swb_batch *b);
+int swb_batch_fetch(swb_engine *e, swb_batch *b, float *scores, int64_t *end_a, int64_t *end_b);
+void swb_batch_free(swb_engine *e, swb_batch *b);
+/* device time (ms) of the last swb_batch_run, measured with CUDA events on the engine's stream;
+ * synchronises.  launches = kernels in that run. */
+int swb_batch_last_run_ms(swb_engine *e, swb_batch *b, float *ms, int64_t *launches);
+/* steps back-to-back runs bracketed by two CUDA events on the engine's stream; synchronises and
+ * returns the total device time (ms) and the number of kernels launched. */
+int swb_batch_run_n(swb_engine *e, swb_batch *b, int steps, float *total_ms, int64_t *launches);
+
+/* DPX / integer-pipe micro-benchmark (kernel K0): thread-instructions per second of the given
+ * instruction mix on the whole chip; which: 0 VIADDMNMX.S16x2, 1 VIMNMX3.S16x2, 2 VIADD.16x2,
+ * 3 the 4-op Gotoh cell mix, 4 VIADDMNMX (s32), 5 IMAD, 6 mix + IMAD interleaved. */
+int swb_dpx_peak(int device, int which, double *thread_instr_per_s);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SWB200_H */

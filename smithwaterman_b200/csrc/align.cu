@@ -1,0 +1,183 @@
+// Traceback path: swb_align / swb_align_batch.  Mirrors align_partial (SA.rs:393-551): encode ->
+// fill (KW with direction bytes) -> backtrack (KT) -> strings with the retain_all padding rules.
+#include <algorithm>
+#include <cstdlib>
+#include <cstring>
+
+#include "swb_internal.h"
+
+#define DIR_BUDGET_BYTES (24ll << 30)      // direction bytes resident per chunk of pairs
+
+struct DevBuf {                            // frees on scope exit
+    void *p = nullptr;
+    ~DevBuf() { if (p) cudaFree(p); }
+    template <class T> T *as() { return reinterpret_cast<T *>(p); }
+};
+
+static char *dup_n(const std::string &s)
+{
+    char *r = (char *)malloc(s.size() + 1);
+    if (r) { memcpy(r, s.data(), s.size()); r[s.size()] = 0; }
+    return r;
+}
+
+// String re-inflation (SA.rs:470-550).  idx lists are forward (start -> end), -1 = gap.
+static void inflate(const char *a, int64_t la, const char *b, int64_t lb, const int64_t *xa, const int64_t *xb,
+                    int64_t n, int mode, bool retain_all, std::string &ra, std::string &rb)
+{
+    std::string c1, c2;
+    int64_t s1 = -1, s2 = -1, e1 = -1, e2 = -1;
+    c1.reserve(n); c2.reserve(n);
+    for (int64_t k = 0; k < n; ++k) {
+        if (xa[k] > -1) { if (s1 < 0) s1 = xa[k]; c1.push_back(a[xa[k]]); e1 = xa[k]; } else c1.push_back('-');
+        if (xb[k] > -1) { if (s2 < 0) s2 = xb[k]; c2.push_back(b[xb[k]]); e2 = xb[k]; } else c2.push_back('-');
+    }
+    if (mode == SWB_LOCAL && !retain_all) { ra.swap(c1); rb.swap(c2); return; }      // SA.rs:502-504
+    ra.clear(); rb.clear();
+    ra.reserve(la + lb); rb.reserve(la + lb);
+    if (s1 < 0 || s2 < 0) {                                                           // SA.rs:512-524
+        ra.append(a, la); rb.append(la, '-');
+        ra.append(lb, '-'); rb.append(b, lb);
+        return;
+    }
+    ra.append(a, s1); rb.append(s1, '-');                                             // SA.rs:530-537
+    ra.append(s2, '-'); rb.append(b, s2);
+    ra += c1; rb += c2;
+    ra.append(a + e1 + 1, la - e1 - 1); rb.append(la - e1 - 1, '-');                  // SA.rs:542-549
+    ra.append(lb - e2 - 1, '-'); rb.append(b + e2 + 1, lb - e2 - 1);
+}
+
+static int fill_out(swb_alignment *out, float score, int64_t ei, int64_t ej, const std::vector<int64_t> &xa,
+                    const std::vector<int64_t> &xb, const std::string &ra, const std::string &rb)
+{
+    out->score = score; out->end_a = ei; out->end_b = ej; out->n_cols = (int64_t)xa.size();
+    out->idx_a = (int64_t *)malloc(sizeof(int64_t) * std::max<size_t>(1, xa.size()));
+    out->idx_b = (int64_t *)malloc(sizeof(int64_t) * std::max<size_t>(1, xb.size()));
+    out->aln_a = dup_n(ra); out->aln_b = dup_n(rb); out->aln_len = (int64_t)ra.size();
+    if (!out->idx_a || !out->idx_b || !out->aln_a || !out->aln_b) return SWB_ERR_NOMEM;
+    if (!xa.empty()) { memcpy(out->idx_a, xa.data(), xa.size() * sizeof(int64_t)); memcpy(out->idx_b, xb.data(), xb.size() * sizeof(int64_t)); }
+    return SWB_OK;
+}
+
+extern "C" void swb_alignment_free(swb_alignment *a)
+{
+    if (!a) return;
+    free(a->idx_a); free(a->idx_b); free(a->aln_a); free(a->aln_b);
+    memset(a, 0, sizeof(*a));
+}
+
+extern "C" int swb_align_batch(swb_engine *e, const char *a_all, const int64_t *off_a, const char *b_all,
+                               const int64_t *off_b, int64_t n, unsigned flags, swb_alignment *outs)
+{
+    if (!e) return SWB_ERR_ARG;
+    if (n < 0 || (n > 0 && (!off_a || !off_b || !outs))) { e->err = "bad argument"; return SWB_ERR_ARG; }
+    CUDA_TRY(e, cudaSetDevice(e->device));
+    const bool retain_all = (flags & SWB_RETAIN_ALL) != 0;
+    memset(outs, 0, sizeof(swb_alignment) * (size_t)n);
+    const float inv = 1.0f / (float)e->scale;
+    const bool dyadic = (e->scale & (e->scale - 1)) == 0;
+    auto to_f = [&](int64_t s) { return dyadic ? (float)s * inv : (float)((double)s / e->scale); };
+    e->stats = swb_stats{}; e->stats.scale = e->scale; e->stats.exact_scale = e->exact_scale;
+
+    // encode on the host (small inputs on this path); unknown letters as SA.rs:669-679
+    const int64_t na = n ? off_a[n] : 0, nb = n ? off_b[n] : 0;
+    std::vector<uint8_t> ca(na + 16), cb(nb + 16);
+    for (int64_t k = 0; k < na; ++k) { int c = e->code_of[(unsigned char)a_all[k]]; if (c < 0) { e->err = std::string("unknown letter ") + a_all[k] + ". please set X to allow scoring for undefined letter pair."; return SWB_ERR_LETTER; } ca[k] = (uint8_t)c; }
+    for (int64_t k = 0; k < nb; ++k) { int c = e->code_of[(unsigned char)b_all[k]]; if (c < 0) { e->err = std::string("unknown letter ") + b_all[k] + ". please set X to allow scoring for undefined letter pair."; return SWB_ERR_LETTER; } cb[k] = (uint8_t)c; }
+
+    std::vector<int64_t> work;                       // pairs that need the device
+    for (int64_t k = 0; k < n; ++k) {
+        const int64_t la = off_a[k + 1] - off_a[k], lb = off_b[k + 1] - off_b[k];
+        if (la < 0 || lb < 0 || la > 0x3FFFFFF0 || lb > 0x3FFFFFF0) { e->err = "bad offsets"; return SWB_ERR_ARG; }
+        e->stats.cells += (double)la * (double)lb;
+        if (la > 0 && lb > 0) { work.push_back(k); continue; }
+        // an empty sequence: the walk runs along the boundary row/column only (SA.rs:100-118, 296-383)
+        std::vector<int64_t> xa, xb; std::string ra, rb; float score = 0.0f; int64_t ei = -1, ej = -1;
+        if (e->mode != SWB_LOCAL) {
+            if (la == 0 && lb == 0) { e->err = "both sequences are empty (the reference panics here, SA.rs:360-363)"; return SWB_ERR_EMPTY; }
+            const int32_t so = (e->mode == SWB_GLOBAL) ? e->o : 0, se = (e->mode == SWB_GLOBAL) ? e->e : 0;
+            score = to_f((la + lb) * (int64_t)se + (so - se)); ei = la; ej = lb;
+            if (10 * e->o + 10 * e->e == 0) { e->err = "zero gap penalties with an empty sequence (the reference panics here)"; return SWB_ERR_EMPTY; }
+            for (int64_t t = 0; t < la; ++t) { xa.push_back(t); xb.push_back(-1); }
+            for (int64_t t = 0; t < lb; ++t) { xa.push_back(-1); xb.push_back(t); }
+        }
+        inflate(a_all + off_a[k], la, b_all + off_b[k], lb, xa.data(), xb.data(), (int64_t)xa.size(), e->mode, retain_all, ra, rb);
+        int rc = fill_out(&outs[k], score, ei, ej, xa, xb, ra, rb);
+        if (rc != SWB_OK) { e->err = "out of memory"; return rc; }
+    }
+    if (work.empty()) return SWB_OK;
+
+    DevBuf d_a, d_b;
+    CUDA_TRY(e, cudaMalloc(&d_a.p, ca.size())); CUDA_TRY(e, cudaMalloc(&d_b.p, cb.size()));
+    CUDA_TRY(e, cudaMemcpyAsync(d_a.p, ca.data(), ca.size(), cudaMemcpyHostToDevice, e->stream));
+    CUDA_TRY(e, cudaMemcpyAsync(d_b.p, cb.data(), cb.size(), cudaMemcpyHostToDevice, e->stream));
+    e->stats.h2d_bytes += (double)ca.size() + (double)cb.size();
+
+    size_t pos = 0;
+    while (pos < work.size()) {
+        // chunk of pairs whose direction bytes fit the budget
+        std::vector<KWPair> hp; std::vector<int64_t> out_off;
+        int64_t dir_total = 0, bnd_total = 0, out_total = 0;
+        size_t end = pos;
+        while (end < work.size()) {
+            const int64_t k = work[end];
+            const int32_t la = (int32_t)(off_a[k + 1] - off_a[k]), lb = (int32_t)(off_b[k + 1] - off_b[k]);
+            const int64_t db = kw_dir_bytes(la, lb);
+            if (!hp.empty() && dir_total + db > DIR_BUDGET_BYTES) break;
+            KWPair P; P.a_off = off_a[k]; P.b_off = off_b[k]; P.la = la; P.lb = lb; P.dir_off = dir_total; P.bnd_off = bnd_total;
+            hp.push_back(P); out_off.push_back(out_total);
+            dir_total += db; bnd_total += kw_bnd_elems(la, lb); out_total += (int64_t)la + lb + 1;
+            ++end;
+        }
+        const int np = (int)hp.size();
+        DevBuf d_pairs, d_res, d_dir, d_bnd, d_off, d_xa, d_xb, d_nc;
+        CUDA_TRY(e, cudaMalloc(&d_pairs.p, np * sizeof(KWPair))); CUDA_TRY(e, cudaMalloc(&d_res.p, np * sizeof(KWResult)));
+        CUDA_TRY(e, cudaMalloc(&d_dir.p, dir_total + 16)); CUDA_TRY(e, cudaMalloc(&d_bnd.p, bnd_total * sizeof(int4)));
+        CUDA_TRY(e, cudaMalloc(&d_off.p, np * sizeof(int64_t)));
+        CUDA_TRY(e, cudaMalloc(&d_xa.p, out_total * sizeof(int32_t))); CUDA_TRY(e, cudaMalloc(&d_xb.p, out_total * sizeof(int32_t)));
+        CUDA_TRY(e, cudaMalloc(&d_nc.p, np * sizeof(int32_t)));
+        CUDA_TRY(e, cudaMemcpyAsync(d_pairs.p, hp.data(), np * sizeof(KWPair), cudaMemcpyHostToDevice, e->stream));
+        CUDA_TRY(e, cudaMemcpyAsync(d_off.p, out_off.data(), np * sizeof(int64_t), cudaMemcpyHostToDevice, e->stream));
+        CUDA_TRY(e, cudaEventRecord(e->ev0, e->stream));
+        CUDA_TRY(e, kw_launch(e, d_a.as<uint8_t>(), d_b.as<uint8_t>(), d_pairs.as<KWPair>(), np, d_dir.as<uint8_t>(),
+                              d_bnd.as<int4>(), d_res.as<KWResult>(), e->stream));
+        CUDA_TRY(e, kt_launch(e, d_pairs.as<KWPair>(), d_res.as<KWResult>(), np, d_dir.as<uint8_t>(), d_off.as<int64_t>(),
+                              d_xa.as<int32_t>(), d_xb.as<int32_t>(), d_nc.as<int32_t>(), e->stream));
+        CUDA_TRY(e, cudaEventRecord(e->ev1, e->stream));
+        std::vector<KWResult> hr(np); std::vector<int32_t> hnc(np), hxa(out_total), hxb(out_total);
+        CUDA_TRY(e, cudaMemcpyAsync(hr.data(), d_res.p, np * sizeof(KWResult), cudaMemcpyDeviceToHost, e->stream));
+        CUDA_TRY(e, cudaMemcpyAsync(hnc.data(), d_nc.p, np * sizeof(int32_t), cudaMemcpyDeviceToHost, e->stream));
+        CUDA_TRY(e, cudaMemcpyAsync(hxa.data(), d_xa.p, out_total * sizeof(int32_t), cudaMemcpyDeviceToHost, e->stream));
+        CUDA_TRY(e, cudaMemcpyAsync(hxb.data(), d_xb.p, out_total * sizeof(int32_t), cudaMemcpyDeviceToHost, e->stream));
+        CUDA_TRY(e, cudaStreamSynchronize(e->stream));
+        float ms = 0; cudaEventElapsedTime(&ms, e->ev0, e->ev1);
+        e->stats.kernel_ms += ms; e->stats.launches += 2;
+        e->stats.h2d_bytes += (double)np * (sizeof(KWPair) + sizeof(int64_t));
+        e->stats.d2h_bytes += (double)np * (sizeof(KWResult) + 4) + 8.0 * out_total;
+        for (int t = 0; t < np; ++t) {
+            const int64_t k = work[pos + t];
+            if (hnc[t] < 0) { e->err = "traceback left the matrix (the reference panics here, SA.rs:360-371)"; return SWB_ERR_EMPTY; }
+            const int64_t nc = hnc[t];
+            std::vector<int64_t> xa(nc), xb(nc);
+            for (int64_t c = 0; c < nc; ++c) {                  // reverse (SA.rs:384-385)
+                xa[c] = hxa[out_off[t] + nc - 1 - c]; xb[c] = hxb[out_off[t] + nc - 1 - c];
+            }
+            std::string ra, rb;
+            inflate(a_all + off_a[k], hp[t].la, b_all + off_b[k], hp[t].lb, xa.data(), xb.data(), nc, e->mode, retain_all, ra, rb);
+            int rc = fill_out(&outs[k], to_f(hr[t].score), hr[t].end_i, hr[t].end_j, xa, xb, ra, rb);
+            if (rc != SWB_OK) { e->err = "out of memory"; return rc; }
+        }
+        pos = end;
+    }
+    return SWB_OK;
+}
+
+extern "C" int swb_align(swb_engine *e, const char *a, int64_t la, const char *b, int64_t lb, int retain_all,
+                         swb_alignment *out)
+{
+    if (!e) return SWB_ERR_ARG;
+    if (!out || la < 0 || lb < 0) { e->err = "bad argument"; return SWB_ERR_ARG; }
+    const int64_t oa[2] = {0, la}, ob[2] = {0, lb};
+    static const char empty[1] = {0};
+    return swb_align_batch(e, a ? a : empty, oa, b ? b : empty, ob, 1, retain_all ? SWB_RETAIN_ALL : 0u, out);
+}

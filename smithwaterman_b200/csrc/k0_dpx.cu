@@ -1,0 +1,88 @@
+// K0 -- DPX / integer-pipe micro-benchmark: the measured denominator of the GCUPS roofline
+// (SURVEY.md 8d).  Every thread runs 8 independent dependency chains of the chosen instruction so
+// that the issue rate, not the 4-cycle ALU latency, is the limit; all SMs are filled with 2048
+// threads.  Reported: thread-instructions per second (warp-instructions * 32 / elapsed).
+#include "swb_internal.h"
+
+#define K0_ITERS 4096
+#define K0_CHAINS 8
+
+template <int WHICH>
+__global__ void __launch_bounds__(1024) k0_kernel(unsigned *out, unsigned seed)
+{
+    unsigned v[K0_CHAINS], w[K0_CHAINS];
+    const unsigned tid = blockIdx.x * blockDim.x + threadIdx.x;
+#pragma unroll
+    for (int c = 0; c < K0_CHAINS; ++c) { v[c] = seed * (c + 1) + tid; w[c] = seed ^ (tid * (c + 3)); }
+    const unsigned k1 = seed | 0x00010001u, k2 = seed >> 3;
+#pragma unroll 1
+    for (int it = 0; it < K0_ITERS; ++it) {
+#pragma unroll
+        for (int c = 0; c < K0_CHAINS; ++c) {
+            if (WHICH == 0) { v[c] = __viaddmax_s16x2(v[c], k1, w[c]); }
+            else if (WHICH == 1) { v[c] = __vimax3_s16x2(v[c], k1, w[c]); }
+            else if (WHICH == 2) { v[c] = __vadd2(v[c], k1); }
+            else if (WHICH == 3) {      // the 4 DPX ops of one Gotoh cell-vector (+ packed add): 5 instructions
+                unsigned E = __viaddmax_s16x2(w[c], k1, v[c]);
+                unsigned F = __viaddmax_s16x2(v[c], k1, w[c]);
+                unsigned T = __vmaxs2(E, F);
+                unsigned H = __viaddmax_s16x2_relu(v[c], k2, T);
+                v[c] = __vadd2(H, k1); w[c] = E;
+            }
+            else if (WHICH == 4) { v[c] = (unsigned)__viaddmax_s32((int)v[c], (int)k1, (int)w[c]); }
+            else if (WHICH == 5) { v[c] = v[c] * k1 + w[c]; }
+            else if (WHICH == 6) {      // cell mix + 3 IMAD (address / merge work of K1) on the FMA pipe
+                unsigned E = __viaddmax_s16x2(w[c], k1, v[c]);
+                unsigned F = __viaddmax_s16x2(v[c], k1, w[c]);
+                unsigned T = __vmaxs2(E, F);
+                unsigned a0 = E * k2 + F, a1 = F * k2 + T, a2 = a0 * 65536u + a1;
+                unsigned H = __viaddmax_s16x2_relu(v[c], a2, T);
+                v[c] = __vadd2(H, k1); w[c] = E;
+            }
+        }
+    }
+    unsigned acc = 0;
+#pragma unroll
+    for (int c = 0; c < K0_CHAINS; ++c) acc ^= v[c] ^ w[c];
+    if (acc == 0x12345678u) out[tid & 1023] = acc;      // keeps the chains alive; practically never taken
+}
+
+template <int WHICH>
+static cudaError_t k0_time(int sm_count, int per_iter, double *rate)
+{
+    unsigned *d = nullptr;
+    cudaError_t err = cudaMalloc(&d, 1024 * sizeof(unsigned));
+    if (err != cudaSuccess) return err;
+    cudaEvent_t e0, e1;
+    cudaEventCreate(&e0); cudaEventCreate(&e1);
+    const int blocks = sm_count * 2, threads = 1024;
+    double best_ms = 1e30;
+    for (int rep = 0; rep < 12; ++rep) {
+        cudaEventRecord(e0);
+        k0_kernel<WHICH><<<blocks, threads>>>(d, 0x9E3779B9u + rep);
+        cudaEventRecord(e1);
+        err = cudaEventSynchronize(e1);
+        if (err != cudaSuccess) break;
+        float ms = 0; cudaEventElapsedTime(&ms, e0, e1);
+        if (rep >= 2 && ms < best_ms) best_ms = ms;
+    }
+    cudaEventDestroy(e0); cudaEventDestroy(e1); cudaFree(d);
+    if (err != cudaSuccess) return err;
+    const double instr = (double)blocks * threads * (double)K0_ITERS * K0_CHAINS * per_iter;
+    *rate = instr / (best_ms * 1e-3);
+    return cudaGetLastError();
+}
+
+cudaError_t k0_run(int which, int sm_count, double *rate)
+{
+    switch (which) {
+    case 0: return k0_time<0>(sm_count, 1, rate);
+    case 1: return k0_time<1>(sm_count, 1, rate);
+    case 2: return k0_time<2>(sm_count, 1, rate);
+    case 3: return k0_time<3>(sm_count, 5, rate);
+    case 4: return k0_time<4>(sm_count, 1, rate);
+    case 5: return k0_time<5>(sm_count, 1, rate);
+    case 6: return k0_time<6>(sm_count, 8, rate);
+    default: return cudaErrorInvalidValue;
+    }
+}

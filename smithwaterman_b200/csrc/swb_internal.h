@@ -1,0 +1,116 @@
+// Internal declarations shared by the host layer and the kernel translation units.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <string>
+#include <vector>
+
+#include "../../include/swb200.h"
+
+#define SWB_MAX_LETTERS 31          // residue codes 0..n-1, PAD code = n  (table stride n+1 <= 32)
+
+// ---- K1 (inter-sequence batch, packed s16x2) geometry ---------------------------------------
+#define K1_STRIP 32                 // DP columns per pass of one thread: 16 in the low s16 lane, 16 in the high
+#define K1_HALF 16
+#define K1_ROWCHUNK 16              // row residues fetched per 128-bit load
+#define K1_THREADS 256
+
+struct K1Group {                    // one warp-sized work item: 32 pairs of similar shape
+    int64_t a_off;                  // byte offset of the group's row-residue block   [chunk][lane][16]
+    int64_t b_off;                  // byte offset of the group's column-residue block [pass][lane][32]
+    int32_t la_max;                 // longest a in the group (row steps = la_max + 1)
+    int32_t n_pass;                 // ceil(max lb / 32)
+    int32_t first_pair;             // index of lane 0's pair in the sorted order
+    int32_t n_pairs;                // 1..32
+};
+
+struct K1Result {                   // per pair (sorted order)
+    int32_t score;                  // scaled integer score
+    int32_t end_i, end_j;           // 1-based first-maximum cell, -1,-1 if score == 0
+    int32_t flags;                  // bit0: s16 range exceeded -> re-run in int32
+};
+
+struct swb_engine {
+    int device = 0;
+    int mode = SWB_LOCAL;
+    int n = 0;                      // letters
+    char letters[SWB_MAX_LETTERS + 1] = {0};
+    int16_t code_of[256];           // byte -> residue code, -1 = unknown and no X
+    float go = 0, ge = 0;           // as given (sign-normalised negative, SA.rs:28-35)
+    int32_t scale = 1, exact_scale = 1;
+    int32_t o = 0, e = 0;           // scaled, <= 0
+    int32_t smax = 0, smin = 0;     // scaled matrix extremes
+    std::vector<int32_t> mat;       // n*n scaled
+    std::vector<float> matf;        // n*n as given
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    int sm_count = 0;
+    int32_t *d_mat = nullptr;       // (n+1)*(n+1) int32 scaled, PAD row/col included
+    // scratch owned by the engine, grown on demand
+    void *d_bnd = nullptr; size_t bnd_bytes = 0;
+    swb_stats stats = {};
+    std::string err;
+};
+
+struct BatchDev;
+struct swb_batch {
+    int64_t n = 0;
+    BatchDev *dev = nullptr;        // device-side part owned by batch.cu
+    std::vector<int32_t> order;     // sorted position -> caller's pair index
+    std::vector<int32_t> la, lb;    // per caller index
+    std::vector<K1Group> groups;
+    // device
+    uint8_t *d_a = nullptr, *d_b = nullptr;
+    K1Group *d_groups = nullptr;
+    int32_t *d_la = nullptr, *d_lb = nullptr;   // sorted order
+    K1Result *d_res = nullptr;
+    int32_t *d_counter = nullptr;
+    size_t a_bytes = 0, b_bytes = 0;
+    int32_t la_max = 0;
+    // generic (int32, 3-state) path for what K1 does not take: codes in caller order
+    std::vector<int32_t> generic_idx;           // caller indices routed to the generic kernel
+    std::vector<uint8_t> h_codes_a, h_codes_b;  // encoded residues, concatenated (caller order)
+    std::vector<int64_t> off_a, off_b;
+    float last_ms = 0; int64_t last_launches = 0;
+    double cells = 0;
+    std::vector<K1Result> h_res;    // pinned staging is overkill for 16 B/pair; plain vector
+};
+
+#define CUDA_TRY(e_, call)                                                                      \
+    do {                                                                                        \
+        cudaError_t err__ = (call);                                                             \
+        if (err__ != cudaSuccess) {                                                             \
+            (e_)->err = std::string(#call) + ": " + cudaGetErrorString(err__);                  \
+            return SWB_ERR_CUDA;                                                                \
+        }                                                                                       \
+    } while (0)
+
+// ---- kernel launchers (defined in the .cu files) ----------------------------------------------
+// K1: local, score + first-maximum cell, packed s16x2, one thread per pair.
+cudaError_t k1_launch(const swb_engine *e, const swb_batch *b, int n_blocks, cudaStream_t st);
+size_t k1_bnd_bytes(int n_blocks, int la_max);
+int k1_blocks_per_sm(const swb_engine *e);
+
+// KW: one warp per pair, exact 3-state int32 recurrence (all modes), optional direction bytes.
+struct KWPair {
+    int64_t a_off, b_off;           // offsets into the code arrays
+    int32_t la, lb;
+    int64_t dir_off;                // offset of this pair's direction bytes (skewed layout), -1 = none
+    int64_t bnd_off;                // offset (in int4 units) of the strip-boundary column buffer
+};
+struct KWResult {
+    int32_t score;                  // scaled
+    int32_t end_i, end_j;           // start cell of the traceback (1-based), -1 = empty
+    int32_t state;                  // state at the start cell (0 M, 1 X, 2 Y)
+};
+cudaError_t kw_launch(const swb_engine *e, const uint8_t *d_a, const uint8_t *d_b, const KWPair *d_pairs,
+                      int n_pairs, uint8_t *d_dir, int4 *d_bnd, KWResult *d_res, cudaStream_t st);
+int64_t kw_dir_bytes(int32_t la, int32_t lb);        // bytes of the skewed direction store of one pair
+int64_t kw_bnd_elems(int32_t la, int32_t lb);
+// KT: pointer walk over the direction bytes; one thread per pair.  Writes reversed column lists.
+cudaError_t kt_launch(const swb_engine *e, const KWPair *d_pairs, const KWResult *d_res, int n_pairs,
+                      const uint8_t *d_dir, const int64_t *d_out_off, int32_t *d_idx_a, int32_t *d_idx_b,
+                      int32_t *d_ncols, cudaStream_t st);
+
+// K0
+cudaError_t k0_run(int which, int sm_count, double *thread_instr_per_s);

@@ -1,0 +1,233 @@
+"""GPU parity tests: the CUDA engine (through the C ABI) against the CPU oracle and the committed
+golden fixtures.  Bit-exact: scores, end cells, index lists and alignment strings."""
+import numpy as np
+import pytest
+
+from conftest import trim_terminal
+import smithwaterman_b200 as swb
+from oracle import oracle as O
+
+pytestmark = pytest.mark.gpu
+
+AA = "ARNDCQEGHILKMFPSTWYV"
+
+
+def _matrix(spec):
+    m = swb.SubstitutionMatrix.get_blosum62_matrix() if spec["kind"] == "blosum62" else \
+        swb.SubstitutionMatrix.get_mat_matrix(spec["match"], spec["mismatch"])
+    if spec.get("scale", 1.0) != 1.0:
+        m = swb.SubstitutionMatrix(m.index_to_string, m.scores * np.float32(spec["scale"]))
+    return m
+
+
+def _omatrix(m):
+    return O.Matrix(m.index_to_string, m.scores)
+
+
+def test_rust_kats(rust_kats):
+    """SA.rs:921-1221 / OCL.rs:1292-1448 known answers (the PSSM case is a 'next' row)."""
+    done = 0
+    for c in rust_kats:
+        if c["pssm"]:
+            continue
+        eng = swb.SequenceAlignment(_matrix(c["matrix"]), c["go"], c["ge"], c["mode"])
+        r1, r2, sc = eng.align(swb.SeqData.create("", "", c["seq1"]), swb.SeqData.create("", "", c["seq2"]), c["retain_all"])
+        if "score" in c:
+            assert sc == c["score"], c["test"]
+        if "r1" in c:
+            assert "".join(r1) == c["r1"], c["test"]
+            assert "".join(r2) == c["r2"], c["test"]
+        done += 1
+        eng.close()
+    assert done == 25
+
+
+@pytest.mark.parametrize("mode,key", [(swb.ALIGN_LOCAL, "local"), (swb.ALIGN_GLOCAL, "glocal"), (swb.ALIGN_GLOBAL, "global")])
+def test_emboss_goldens(emboss, mode, key):
+    """config[0]: the 100 test/inputs pairs vs test/emboss_results (strings + scores) and vs the oracle
+    (index lists, end cells), through the batch-list call."""
+    m = swb.SubstitutionMatrix.get_blosum62_matrix()
+    eng = swb.SequenceAlignment(m, 10.0, 0.5, mode)
+    res = eng.align_list([r["seq1"] for r in emboss], [r["seq2"] for r in emboss], retain_all=True)
+    oeng = O.Engine(_omatrix(m), 10.0, 0.5, mode)
+    for rec, out in zip(emboss, res):
+        s1, s2 = out["aln_a"], out["aln_b"]
+        assert s1.replace("-", "") == rec["seq1"] and s2.replace("-", "") == rec["seq2"]
+        if mode == swb.ALIGN_LOCAL:
+            s1, s2 = trim_terminal(s1, s2)
+        assert s1 == rec[key]["s1"] and s2 == rec[key]["s2"], (key, rec["id"])
+        assert out["score"] == rec[key]["score"], (key, rec["id"])
+        xa, xb, sc, ei, ej = oeng.raw(oeng.matrix.seq_to_index(rec["seq1"]), oeng.matrix.seq_to_index(rec["seq2"]))
+        assert np.array_equal(out["idx_a"], xa) and np.array_equal(out["idx_b"], xb)
+        assert (out["end_a"], out["end_b"]) == (ei, ej)
+    # the score-only batch call agrees with the traceback call
+    sc, ea, eb = eng.score_batch([r["seq1"] for r in emboss], [r["seq2"] for r in emboss])
+    assert [float(x) for x in sc] == [o["score"] for o in res]
+    assert [int(x) for x in ea] == [o["end_a"] for o in res] and [int(x) for x in eb] == [o["end_b"] for o in res]
+    eng.close()
+
+
+def _rand_seqs(rng, n, lo, hi, alphabet=AA, weights=None):
+    ls = rng.integers(lo, hi + 1, n)
+    letters = np.frombuffer(alphabet.encode(), np.uint8)
+    return [bytes(letters[rng.choice(len(letters), k, p=weights)]) for k in ls]
+
+
+def _oracle_scores(m, sa, sb, go, ge, mode, scale=2):
+    om = _omatrix(m)
+    a, oa = O.pack([om.seq_to_index(s.decode()) for s in sa])
+    b, ob = O.pack([om.seq_to_index(s.decode()) for s in sb])
+    mi = np.rint(m.scores * scale).astype(np.int32)
+    return O.score_batch_int(a, oa, b, ob, mi, -int(round(go * scale)), -int(round(ge * scale)), scale, mode, nthreads=8)
+
+
+@pytest.mark.parametrize("mode", [swb.ALIGN_LOCAL, swb.ALIGN_GLOCAL, swb.ALIGN_GLOBAL])
+def test_score_batch_random(mode):
+    """K1 (local, packed s16x2) / KW (other modes) vs the integer oracle: score and end cell, ragged shapes."""
+    rng = np.random.default_rng(20242 + mode)
+    m = swb.SubstitutionMatrix.get_blosum62_matrix()
+    eng = swb.SequenceAlignment(m, 10.0, 0.5, mode)
+    n = 3000 if mode == swb.ALIGN_LOCAL else 600
+    sa = _rand_seqs(rng, n, 1, 200)
+    sb = _rand_seqs(rng, n, 1, 200)
+    # shapes around the 16/32-column lane boundaries and 16-row chunks; related pairs; repeats (tie-breaking)
+    for la, lb in [(1, 1), (1, 33), (33, 1), (15, 16), (16, 16), (17, 17), (31, 32), (32, 32), (33, 33), (64, 64),
+                   (100, 31), (100, 65), (300, 500), (500, 100), (129, 257)]:
+        sa.append(_rand_seqs(rng, 1, la, la)[0]); sb.append(_rand_seqs(rng, 1, lb, lb)[0])
+    for k in range(200):
+        base = _rand_seqs(rng, 1, 50, 400)[0]
+        mut = bytearray(base)
+        for p in rng.integers(0, len(mut), max(1, len(mut) // 6)):
+            mut[p] = ord(AA[rng.integers(0, 20)])
+        cut = rng.integers(0, len(mut) // 2)
+        sa.append(base); sb.append(bytes(mut[cut:]))
+    for k in range(60):
+        sa.append(b"K" * int(rng.integers(1, 120))); sb.append(b"K" * int(rng.integers(1, 120)))
+        sa.append((b"AKL" * 50)[: int(rng.integers(3, 150))]); sb.append((b"KLA" * 50)[: int(rng.integers(3, 150))])
+    sc, ea, eb = eng.score_batch(sa, sb)
+    osc, oi, oj = _oracle_scores(m, sa, sb, 10.0, 0.5, mode)
+    assert np.array_equal(np.rint(sc.astype(np.float64) * 2).astype(np.int64), osc)
+    assert np.array_equal(ea, oi) and np.array_equal(eb, oj)
+    eng.close()
+
+
+def test_score_batch_edge_cases():
+    m = swb.SubstitutionMatrix.get_blosum62_matrix()
+    for mode in (swb.ALIGN_LOCAL, swb.ALIGN_GLOCAL, swb.ALIGN_GLOBAL):
+        eng = swb.SequenceAlignment(m, 10.0, 0.5, mode)
+        sa = [b"", b"ACD", b"", b"W", b"AAAA", b"acdx", b"BZX*"]      # empty, ragged, lower-case -> X, special letters
+        sb = [b"ACD", b"", b"", b"W", b"WWWW", b"ACDX", b"BZX*"]
+        sc, ea, eb = eng.score_batch(sa, sb)
+        osc, oi, oj = _oracle_scores(m, sa, sb, 10.0, 0.5, mode)
+        assert np.array_equal(np.rint(sc.astype(np.float64) * 2).astype(np.int64), osc), mode
+        assert np.array_equal(ea, oi) and np.array_equal(eb, oj), mode
+        assert len(eng.score_batch([], [])[0]) == 0
+        eng.close()
+
+
+def test_s16_overflow_rerun():
+    """Scores beyond the s16 lanes are re-run in int32 (overflow path must exist and be tested)."""
+    m = swb.SubstitutionMatrix.get_blosum62_matrix()
+    eng = swb.SequenceAlignment(m, 10.0, 0.5, swb.ALIGN_LOCAL)
+    rng = np.random.default_rng(5)
+    big = _rand_seqs(rng, 1, 3500, 3500)[0]
+    sa = [b"W" * 2000, big, _rand_seqs(rng, 1, 300, 300)[0]]
+    sb = [b"W" * 1800, big[100:], _rand_seqs(rng, 1, 200, 200)[0]]
+    sc, ea, eb = eng.score_batch(sa, sb)
+    assert eng.stats()["i32_reruns"] >= 2
+    osc, oi, oj = _oracle_scores(m, sa, sb, 10.0, 0.5, swb.ALIGN_LOCAL)
+    assert np.array_equal(np.rint(sc.astype(np.float64) * 2).astype(np.int64), osc)
+    assert np.array_equal(ea, oi) and np.array_equal(eb, oj)
+    assert sc[0] == 11.0 * 1800
+    eng.close()
+
+
+@pytest.mark.parametrize("go,ge,match,mismatch", [(5.0, 2.0, 2.0, -3.0), (10.0, 0.5, 5.0, -4.0), (0.5, 0.5, 1.0, -1.0), (2.0, 3.0, 2.0, -3.0)])
+def test_dna_traceback_all_modes(go, ge, match, mismatch):
+    """DNA-like inputs (+2/-3 of configs 4/5), including |open| < |extend| which only the 3-state kernel handles."""
+    rng = np.random.default_rng(int(go * 10 + ge))
+    m = swb.SubstitutionMatrix.get_mat_matrix(match, mismatch)
+    for mode in (swb.ALIGN_LOCAL, swb.ALIGN_GLOCAL, swb.ALIGN_GLOBAL):
+        eng = swb.SequenceAlignment(m, go, ge, mode)
+        oeng = O.Engine(_omatrix(m), go, ge, mode)
+        sa, sb = [], []
+        for k in range(40):
+            base = bytearray(_rand_seqs(rng, 1, 20, 700, "ACGT")[0])
+            out = bytearray()
+            for ch in base:                                        # noisy copy: sub / ins / del
+                r = rng.random()
+                if r < 0.05:
+                    out.append(ord("ACGT"[rng.integers(0, 4)]))
+                elif r < 0.10:
+                    out.append(ch); out.append(ord("ACGT"[rng.integers(0, 4)]))
+                elif r < 0.15:
+                    continue
+                else:
+                    out.append(ch)
+            sa.append(bytes(base)); sb.append(bytes(out) if out else b"A")
+        res = eng.align_list(sa, sb, retain_all=(mode != swb.ALIGN_LOCAL) or True)
+        for a, b, out in zip(sa, sb, res):
+            xa, xb, sc, ei, ej = oeng.raw(oeng.matrix.seq_to_index(a.decode()), oeng.matrix.seq_to_index(b.decode()))
+            assert out["score"] == sc
+            assert np.array_equal(out["idx_a"], xa) and np.array_equal(out["idx_b"], xb)
+            r1, r2 = O.inflate(list(a.decode()), list(b.decode()), xa, xb, mode, True)
+            assert out["aln_a"] == "".join(r1) and out["aln_b"] == "".join(r2)
+        sc2, _, _ = eng.score_batch(sa, sb)
+        assert [float(x) for x in sc2] == [o["score"] for o in res]
+        eng.close()
+
+
+def test_retain_all_false_and_empty_alignment():
+    m = swb.SubstitutionMatrix.get_blosum62_matrix()
+    eng = swb.SequenceAlignment(m, 10.0, 0.5, swb.ALIGN_LOCAL)
+    oeng = O.Engine(_omatrix(m), 10.0, 0.5, swb.ALIGN_LOCAL)
+    for a, b in [("WWWW", "PPPP"), ("AAAWCDEAAA", "GGWCDEGG"), ("", "ACD"), ("ACD", ""), ("MKV", "MKV")]:
+        for ra in (True, False):
+            r1, r2, sc = eng.align(a, b, ra)
+            o1, o2, osc = oeng.align(a, b, ra)
+            assert ("".join(r1), "".join(r2), sc) == ("".join(o1), "".join(o2), osc), (a, b, ra)
+    eng.close()
+
+
+def test_errors_instead_of_panics():
+    m = swb.SubstitutionMatrix.get_mat_matrix(1.0, -1.0)
+    eng = swb.SequenceAlignment(m, 10.0, 0.5, swb.ALIGN_GLOBAL)
+    with pytest.raises(swb.SwbError):
+        eng.align("", "", True)                                    # reference underflows (SA.rs:360-363)
+    sc, ea, eb = eng.score_batch([b""], [b""])                     # score_only of two empty sequences is 0 (SA.rs:451-462)
+    assert sc[0] == 0.0
+    eng.close()
+    with pytest.raises(swb.SwbError):
+        swb.SequenceAlignment(swb.SubstitutionMatrix.get_mat_matrix(1.0, -1.0), 10.0, 0.3337, swb.ALIGN_LOCAL)   # no integer grid
+
+
+def test_unknown_letter_without_x():
+    sm = swb.SubstitutionMatrix.load_from_lines(["  A T G C", "A 1 -3 -3 -3", "T -3 1 -3 -3", "G -3 -3 1 -3", "C -3 -3 -3 1"])
+    eng = swb.SequenceAlignment(sm, 5.0, 2.0, swb.ALIGN_LOCAL)
+    with pytest.raises(swb.SwbError):
+        eng.score_batch([b"ACGN"], [b"ACGT"])                      # SA.rs:676
+    with pytest.raises(swb.SwbError):
+        eng.align("ACGN", "ACGT")
+    sc, _, _ = eng.score_batch([b"ACGT"], [b"ACGT"])
+    assert sc[0] == 4.0
+    eng.close()
+
+
+def test_symmetry_property_large():
+    """Size-independent property at BASELINE config-2 shapes: score(a,b) == score(b,a) for a symmetric matrix
+    (end cells transpose only when the maximum is unique, so only scores are compared)."""
+    rng = np.random.default_rng(20242)
+    m = swb.SubstitutionMatrix.get_blosum62_matrix()
+    eng = swb.SequenceAlignment(m, 10.0, 0.5, swb.ALIGN_LOCAL)
+    n = 20000
+    sa = _rand_seqs(rng, n, 100, 500)
+    sb = _rand_seqs(rng, n, 100, 500)
+    s1, ea, eb = eng.score_batch(sa, sb)
+    s2, _, _ = eng.score_batch(sb, sa)
+    assert np.array_equal(s1, s2)
+    assert (s1 > 0).all() and (ea >= 1).all() and (eb >= 1).all()
+    sub = rng.choice(n, 300, replace=False)
+    osc, oi, oj = _oracle_scores(m, [sa[k] for k in sub], [sb[k] for k in sub], 10.0, 0.5, swb.ALIGN_LOCAL)
+    assert np.array_equal(np.rint(s1[sub].astype(np.float64) * 2).astype(np.int64), osc)
+    assert np.array_equal(ea[sub], oi) and np.array_equal(eb[sub], oj)
+    eng.close()
