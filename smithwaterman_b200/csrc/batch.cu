@@ -215,7 +215,8 @@ extern "C" int swb_batch_upload(swb_engine *e, const char *a_all, const int64_t 
 
     if (d->n_k1) {
         const int ng = (int)b->groups.size();
-        CUDA_TRY(e, cudaMalloc(&b->d_a, b->a_bytes)); CUDA_TRY(e, cudaMalloc(&b->d_b, b->b_bytes));
+        CUDA_TRY(e, cudaMalloc(&b->d_a, b->a_bytes + 32 * 16));   // one chunk of slack: K1 prefetches a chunk ahead
+        CUDA_TRY(e, cudaMalloc(&b->d_b, b->b_bytes));
         CUDA_TRY(e, cudaMalloc(&b->d_groups, ng * sizeof(K1Group)));
         CUDA_TRY(e, cudaMalloc(&b->d_la, d->n_k1 * sizeof(int32_t))); CUDA_TRY(e, cudaMalloc(&b->d_lb, d->n_k1 * sizeof(int32_t)));
         CUDA_TRY(e, cudaMalloc(&b->d_res, d->n_k1 * sizeof(K1Result)));

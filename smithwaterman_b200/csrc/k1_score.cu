@@ -14,10 +14,11 @@
 //
 // Recurrence (Gotoh form, equal in value to the reference's 3-state form when |open| >= |extend|,
 // SURVEY.md 8a note 3), all registers hold Ho = H + open:
-//     E  = max(E + ext, Ho_left)           VIADDMNMX.S16x2
-//     F  = max(F + ext, Ho_up)             VIADDMNMX.S16x2
-//     H  = max(Ho_diag + (s - open), E, F, 0)   VIMNMX.S16x2 + VIADDMNMX.S16x2.RELU
-//     Ho = H + open                        VIADD.16x2
+//     F  = max(F + ext, Ho_up)                  VIADDMNMX.S16x2
+//     G  = max(Ho_diag + (s - open), F, 0)      VIADDMNMX.S16x2.RELU
+//     Go = G + open                             VIADD.16x2
+//     E  = max(E + ext, Go_left)                VIADDMNMX.S16x2   (the only op on the row's dependency chain)
+//     Ho = max(E + open, Go)  (= H + open)      VIADDMNMX.S16x2
 // Substitution scores (s - open) come from a shared-memory table replicated per lane
 // (bank == lane, conflict-free): one LDS per s16 lane, merged with one IMAD.
 //
@@ -39,18 +40,21 @@ __device__ __forceinline__ int lo16(unsigned v) { return (int)(short)(v & 0xFFFF
 __device__ __forceinline__ int hi16(unsigned v) { return ((int)v) >> 16; }
 __device__ __forceinline__ unsigned pack2(int lo, int hi) { return ((unsigned)lo & 0xFFFFu) | ((unsigned)hi << 16); }
 
+// One packed cell-vector.  The only loop-carried dependency along k is the single VIADDMNMX of E:
+//   G  = max(Hdiag + s, F, 0)                 (independent of the row chain)
+//   E  = max(E + ext, Go_prev)                == max(E + ext, Ho_prev) because open <= ext
+//   Ho = max(Go, E + open)                    == max(G, E) + open
 #define K1_CELL(k)                                                                                   \
     {                                                                                                \
         unsigned s_lo = lds32(cb_lo[k] + roff_lo);                                                   \
         unsigned s_hi = lds32(cb_hi[k] + roff_hi);                                                   \
         unsigned s2 = s_hi * 65536u + s_lo;                                                          \
-        E = __viaddmax_s16x2(E, ext2, HoL);                                                          \
         unsigned Fk = __viaddmax_s16x2(F[k], ext2, Ho[k]);                                           \
-        unsigned T = __vmaxs2(E, Fk);                                                           \
-        unsigned H = __viaddmax_s16x2_relu(HoD, s2, T);                                              \
+        unsigned G = __viaddmax_s16x2_relu(HoD, s2, Fk);                                             \
+        E = __viaddmax_s16x2(E, ext2, GoP);                                                          \
+        GoP = __vadd2(G, open2);                                                                     \
         HoD = Ho[k];                                                                                 \
-        HoL = __vadd2(H, open2);                                                                     \
-        Ho[k] = HoL;                                                                                 \
+        Ho[k] = __viaddmax_s16x2(E, open2, GoP);                                                     \
         F[k] = Fk;                                                                                   \
     }
 
@@ -58,7 +62,7 @@ __global__ void __launch_bounds__(K1_THREADS * 2, 1)
 k1_local_kernel(const uint8_t *__restrict__ a_pk, const uint8_t *__restrict__ b_pk,
                 const K1Group *__restrict__ groups, int n_groups, const int32_t *__restrict__ la_arr,
                 const int32_t *__restrict__ lb_arr, const int32_t *__restrict__ mat, int nl, int open, int ext,
-                int limit_ho, uint2 *__restrict__ bnd, int bnd_rows, int *counter, K1Result *__restrict__ res)
+                int limit_ho, unsigned *__restrict__ bnd, int bnd_rows, int *counter, K1Result *__restrict__ res)
 {
     extern __shared__ unsigned T_sh[];               // [nl*nl][32 lanes]: (s - open) & 0xFFFF
     for (int idx = threadIdx.x; idx < nl * nl * 32; idx += blockDim.x)
@@ -67,7 +71,7 @@ k1_local_kernel(const uint8_t *__restrict__ a_pk, const uint8_t *__restrict__ b_
 
     const int lane = threadIdx.x & 31;
     const int wslot = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
-    uint2 *mybnd = bnd + (size_t)wslot * (size_t)bnd_rows * 32 + lane;      // [row][lane]
+    unsigned *mybnd = bnd + (size_t)wslot * (size_t)bnd_rows * 32 + lane;   // [row][lane]: (Ho, E) of the pass's last column
     const unsigned tbase = (unsigned)__cvta_generic_to_shared(T_sh) + lane * 4;
     const unsigned rowstride = (unsigned)nl * 128u;
     const unsigned open2 = pack2(open, open), ext2 = pack2(ext, ext);
@@ -77,16 +81,16 @@ k1_local_kernel(const uint8_t *__restrict__ a_pk, const uint8_t *__restrict__ b_
         if (lane == 0) g = atomicAdd(counter, 1);
         g = __shfl_sync(0xffffffffu, g, 0);
         if (g >= n_groups) break;
-        const K1Group G = groups[g];
-        const int p = G.first_pair + lane;
-        const bool valid = lane < G.n_pairs;
+        const K1Group G_ = groups[g];
+        const int p = G_.first_pair + lane;
+        const bool valid = lane < G_.n_pairs;
         const int la = valid ? la_arr[p] : 0;
         int bestHo = open, bi = -1, bj = -1, ovf = 0;
-        const uint4 *ap = reinterpret_cast<const uint4 *>(a_pk + G.a_off) + lane;       // chunk c at ap[c*32]
-        const uint4 *bp = reinterpret_cast<const uint4 *>(b_pk + G.b_off) + lane * 2;   // pass q at bp[q*64]
-        const int nsteps = G.la_max + 1;
+        const uint4 *ap = reinterpret_cast<const uint4 *>(a_pk + G_.a_off) + lane;       // chunk c at ap[c*32]
+        const uint4 *bp = reinterpret_cast<const uint4 *>(b_pk + G_.b_off) + lane * 2;   // pass q at bp[q*64]
+        const int nsteps = G_.la_max + 1;
 
-        for (int q = 0; q < G.n_pass; ++q) {
+        for (int q = 0; q < G_.n_pass; ++q) {
             unsigned cb_lo[K1_HALF], cb_hi[K1_HALF], Ho[K1_HALF], F[K1_HALF];
             {
                 const uint4 c0 = bp[q * 64], c1 = bp[q * 64 + 1];
@@ -99,19 +103,21 @@ k1_local_kernel(const uint8_t *__restrict__ a_pk, const uint8_t *__restrict__ b_
                     F[k] = 0u;              // any value <= 0 is equivalent under the clamp
                 }
             }
-            const bool first = (q == 0), last = (q == G.n_pass - 1);
+            const bool first = (q == 0), last = (q == G_.n_pass - 1);
             unsigned HoD = open2;                        // diag of the left boundary, row 0
-            unsigned HoL_next, E_next;                   // packed left boundary for the coming step
-            {
-                uint2 b0 = first ? make_uint2(open2, open2) : mybnd[32];   // row 1, high lanes hold the values
-                HoL_next = __byte_perm(b0.x, open2, 0x5432);
-                E_next = __byte_perm(b0.y, open2, 0x5432);
-            }
+            // Left boundary words, one per row step: low s16 = Ho, high s16 = E of column 32q-1.
+            // bq[t] feeds step i0+t+1 (it holds row i0+t+1); prefetched one 4-step block ahead.
+            unsigned bq[4], bq_next[4];
+#pragma unroll
+            for (int t = 0; t < 4; ++t) bq[t] = first ? open2 : mybnd[(size_t)(t + 1) * 32];
             unsigned r_prev = (unsigned)(nl - 1);        // PAD row for the high lane's "row 0"
+            unsigned lo15_Ho = open2, lo15_E = open2;    // low lane's column 15 at the previous row (low s16 used)
             const int jbase = q * K1_STRIP;
+            uint4 ar_next = ap[0];
 
             for (int c = 0; c * K1_ROWCHUNK < nsteps; ++c) {
-                uint4 ar = ap[c * 32];
+                uint4 ar = ar_next;
+                ar_next = ap[(c + 1) * 32];              // a_pk has one chunk of slack
 #pragma unroll 1
                 for (int w4 = 0; w4 < 4; ++w4) {
                     const int i0 = c * K1_ROWCHUNK + w4 * 4;      // rows i0+1 .. i0+4 (low lane)
@@ -119,22 +125,22 @@ k1_local_kernel(const uint8_t *__restrict__ a_pk, const uint8_t *__restrict__ b_
                     const unsigned word = ar.x;
                     ar.x = ar.y; ar.y = ar.z; ar.z = ar.w;
 #pragma unroll
+                    for (int t = 0; t < 4; ++t) bq_next[t] = first ? open2 : mybnd[(size_t)(i0 + 5 + t) * 32];
+#pragma unroll
                     for (int t = 0; t < 4; ++t) {
                         const int i = i0 + t + 1;                // low lane row; high lane row = i-1
                         const unsigned r = (word >> (t * 8)) & 0xFFu;
                         const unsigned roff_lo = r * rowstride, roff_hi = r_prev * rowstride;
                         r_prev = r;
-                        unsigned HoL = HoL_next, E = E_next;
-                        const unsigned HoD_next = HoL;
-                        // prefetch next row's left boundary (previous pass wrote rows 1..nsteps-1; beyond = PAD rows)
-                        uint2 bn = make_uint2(open2, open2);
-                        if (!first && i + 1 < nsteps) bn = mybnd[(size_t)(i + 1) * 32];
+                        // packed left boundary: low lane <- previous pass (row i), high lane <- low lane's column 15 (row i-1)
+                        unsigned GoP = __byte_perm(bq[t], lo15_Ho, 0x5410);
+                        unsigned E = __byte_perm(bq[t], lo15_E, 0x5432);
+                        const unsigned HoD_next = GoP;
                         K1_CELL(0) K1_CELL(1) K1_CELL(2) K1_CELL(3) K1_CELL(4) K1_CELL(5) K1_CELL(6) K1_CELL(7)
                         K1_CELL(8) K1_CELL(9) K1_CELL(10) K1_CELL(11) K1_CELL(12) K1_CELL(13) K1_CELL(14) K1_CELL(15)
                         // pass boundary: high lanes of (Ho[15], E) are column 32q+31 at row i-1
-                        if (!last && i >= 2) mybnd[(size_t)(i - 1) * 32] = make_uint2(Ho[15], E);
-                        HoL_next = __byte_perm(bn.x, Ho[15], 0x5432);
-                        E_next = __byte_perm(bn.y, E, 0x5432);
+                        if (!last && i >= 2) mybnd[(size_t)(i - 1) * 32] = __byte_perm(Ho[15], E, 0x7632);
+                        lo15_Ho = Ho[15]; lo15_E = E;
                         HoD = HoD_next;
                         // packed row maximum of Ho (low lane: row i, high lane: row i-1)
                         unsigned rm = __vimax3_s16x2(Ho[0], Ho[1], Ho[2]);
@@ -148,7 +154,6 @@ k1_local_kernel(const uint8_t *__restrict__ a_pk, const uint8_t *__restrict__ b_
                         const int rlo = lo16(rm), rhi = hi16(rm);
                         const int mm = max(rlo, rhi);
                         if (mm > bestHo || (mm == bestHo && mm > open && i - 1 < bi)) {
-                            if (mm >= limit_ho) ovf = 1;
                             // low lane: row i
                             if (i <= la && (rlo > bestHo || (rlo == bestHo && rlo > open && i < bi))) {
                                 int kk = 0;
@@ -156,6 +161,7 @@ k1_local_kernel(const uint8_t *__restrict__ a_pk, const uint8_t *__restrict__ b_
                                 for (int k = K1_HALF - 1; k >= 0; --k)
                                     if (lo16(Ho[k]) == rlo) kk = k;
                                 bestHo = rlo; bi = i; bj = jbase + kk + 1;
+                                if (rlo >= limit_ho) ovf = 1;
                             }
                             // high lane: row i-1
                             if (i >= 2 && i - 1 <= la && (rhi > bestHo || (rhi == bestHo && rhi > open && i - 1 < bi))) {
@@ -164,9 +170,12 @@ k1_local_kernel(const uint8_t *__restrict__ a_pk, const uint8_t *__restrict__ b_
                                 for (int k = K1_HALF - 1; k >= 0; --k)
                                     if (hi16(Ho[k]) == rhi) kk = k;
                                 bestHo = rhi; bi = i - 1; bj = jbase + K1_HALF + kk + 1;
+                                if (rhi >= limit_ho) ovf = 1;
                             }
                         }
                     }
+#pragma unroll
+                    for (int t = 0; t < 4; ++t) bq[t] = bq_next[t];
                 }
             }
         }
@@ -183,7 +192,7 @@ k1_local_kernel(const uint8_t *__restrict__ a_pk, const uint8_t *__restrict__ b_
 
 size_t k1_bnd_bytes(int n_blocks, int la_max)
 {
-    return (size_t)n_blocks * (K1_THREADS * 2 / 32) * (size_t)(la_max + 2) * 32 * sizeof(uint2);
+    return (size_t)n_blocks * (K1_THREADS * 2 / 32) * (size_t)(la_max + K1_BND_SLACK) * 32 * sizeof(unsigned);
 }
 
 cudaError_t k1_launch(const swb_engine *e, const swb_batch *b, int n_blocks, cudaStream_t st)
@@ -198,6 +207,6 @@ cudaError_t k1_launch(const swb_engine *e, const swb_batch *b, int n_blocks, cud
     const int limit_ho = 32767 - 2 * e->smax + e->o - 1;
     k1_local_kernel<<<n_blocks, K1_THREADS * 2, smem, st>>>(
         b->d_a, b->d_b, b->d_groups, (int)b->groups.size(), b->d_la, b->d_lb, e->d_mat, nl, e->o, e->e, limit_ho,
-        reinterpret_cast<uint2 *>(e->d_bnd), b->la_max + 2, b->d_counter, b->d_res);
+        reinterpret_cast<unsigned *>(e->d_bnd), b->la_max + K1_BND_SLACK, b->d_counter, b->d_res);
     return cudaGetLastError();
 }

@@ -14,6 +14,7 @@
 #define K1_HALF 16
 #define K1_ROWCHUNK 16              // row residues fetched per 128-bit load
 #define K1_THREADS 256
+#define K1_BND_SLACK 16            // row steps run in blocks of 4: up to 3 steps past la_max+1 touch the boundary buffer
 
 struct K1Group {                    // one warp-sized work item: 32 pairs of similar shape
     int64_t a_off;                  // byte offset of the group's row-residue block   [chunk][lane][16]

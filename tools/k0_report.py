@@ -1,0 +1,12 @@
+"""Prints the K0 DPX / integer-pipe micro-benchmark table (thread-instructions per second)."""
+import json
+import sys, os
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import smithwaterman_b200 as swb
+names = ["VIADDMNMX.S16x2", "VIMNMX3.S16x2", "VIADD.16x2", "gotoh-cell-mix(5)", "VIADDMNMX.S32", "IMAD", "cell-mix+3IMAD(8)"]
+out = {}
+for k, n in enumerate(names):
+    v = swb.dpx_peak(k)
+    out[n] = v
+    print("%-20s %8.3f T thread-instr/s  (%.1f lanes/clk/SM at 1965 MHz, 148 SMs)" % (n, v / 1e12, v / 148 / 1.965e9))
+print(json.dumps(out))
