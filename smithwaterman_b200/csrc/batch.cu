@@ -52,7 +52,7 @@ __global__ void encode_kernel(uint8_t *buf, int64_t nbytes, const int16_t *__res
     }
 }
 
-// One block per K1 work item: gathers the 32 pairs' residues into the [chunk][lane][16] row layout
+// One block per K1 work item: gathers the 32 pairs' residues into the [4-row block][lane] row layout
 // and the [pass][lane][32] column layout, PAD-filled, and writes the per-pair lengths.
 __global__ void k1_pack_kernel(const uint8_t *__restrict__ codes_a, const uint8_t *__restrict__ codes_b,
                                const int64_t *__restrict__ off_a, const int64_t *__restrict__ off_b,
@@ -70,21 +70,16 @@ __global__ void k1_pack_kernel(const uint8_t *__restrict__ codes_a, const uint8_
         ob = off_b[src]; lb = (int)(off_b[src + 1] - ob);
         if (sub == 0) { la_arr[G.first_pair + lane] = la; lb_arr[G.first_pair + lane] = lb; }
     }
-    const int n_chunk = (G.la_max + 1 + K1_ROWCHUNK - 1) / K1_ROWCHUNK;
-    for (int c = sub; c < n_chunk; c += nsub) {
-        unsigned w[4];
+    const int n_blk = (G.la_max + 1 + 3) / 4 + 1;              // 4 rows per word, one word of slack (all PAD)
+    for (int c = sub; c < n_blk; c += nsub) {
+        unsigned r = 0;
 #pragma unroll
-        for (int q = 0; q < 4; ++q) {
-            unsigned r = 0;
-#pragma unroll
-            for (int s = 0; s < 4; ++s) {
-                const int row = c * K1_ROWCHUNK + q * 4 + s;
-                const unsigned code = (row < la) ? codes_a[oa + row] : (unsigned)pad;
-                r |= code << (8 * s);
-            }
-            w[q] = r;
+        for (int s = 0; s < 4; ++s) {
+            const int row = c * 4 + s;
+            const unsigned code = (row < la) ? codes_a[oa + row] : (unsigned)pad;
+            r |= code << (8 * s);
         }
-        reinterpret_cast<uint4 *>(a_pk + G.a_off)[c * 32 + lane] = make_uint4(w[0], w[1], w[2], w[3]);
+        reinterpret_cast<unsigned *>(a_pk + G.a_off)[c * 32 + lane] = r;
     }
     for (int h = sub; h < G.n_pass * 2; h += nsub) {       // 16-byte halves of the 32-column passes
         unsigned w[4];
@@ -185,7 +180,7 @@ extern "C" int swb_batch_upload(swb_engine *e, const char *a_all, const int64_t 
                 npm = std::max(npm, (b->lb[k] + K1_STRIP - 1) / K1_STRIP);
             }
             G.la_max = lam; G.n_pass = npm; G.a_off = a_off; G.b_off = b_off;
-            a_off += (int64_t)((lam + 1 + K1_ROWCHUNK - 1) / K1_ROWCHUNK) * 32 * 16;
+            a_off += (int64_t)((lam + 1 + 3) / 4 + 1) * 32 * 4;
             b_off += (int64_t)npm * 32 * 32;
         }
         b->a_bytes = (size_t)a_off; b->b_bytes = (size_t)b_off; b->la_max = la_cap;

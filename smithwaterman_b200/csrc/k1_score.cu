@@ -62,7 +62,7 @@ __global__ void __launch_bounds__(K1_THREADS * 2, 1)
 k1_local_kernel(const uint8_t *__restrict__ a_pk, const uint8_t *__restrict__ b_pk,
                 const K1Group *__restrict__ groups, int n_groups, const int32_t *__restrict__ la_arr,
                 const int32_t *__restrict__ lb_arr, const int32_t *__restrict__ mat, int nl, int open, int ext,
-                int limit_ho, unsigned *__restrict__ bnd, int bnd_rows, int *counter, K1Result *__restrict__ res)
+                int limit_ho, uint4 *__restrict__ bnd, int bnd_blocks, int *counter, K1Result *__restrict__ res)
 {
     extern __shared__ unsigned T_sh[];               // [nl*nl][32 lanes]: (s - open) & 0xFFFF
     for (int idx = threadIdx.x; idx < nl * nl * 32; idx += blockDim.x)
@@ -71,7 +71,9 @@ k1_local_kernel(const uint8_t *__restrict__ a_pk, const uint8_t *__restrict__ b_
 
     const int lane = threadIdx.x & 31;
     const int wslot = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
-    unsigned *mybnd = bnd + (size_t)wslot * (size_t)bnd_rows * 32 + lane;   // [row][lane]: (Ho, E) of the pass's last column
+    // Pass-boundary column, one word per row (low s16 = Ho, high s16 = E), stored as [row block of 4][lane] uint4:
+    // storage block B holds rows 4B+1 .. 4B+4, i.e. exactly what the 4 row steps i0 = 4B need.
+    uint4 *mybnd = bnd + (size_t)wslot * (size_t)bnd_blocks * 32 + lane;
     const unsigned tbase = (unsigned)__cvta_generic_to_shared(T_sh) + lane * 4;
     const unsigned rowstride = (unsigned)nl * 128u;
     const unsigned open2 = pack2(open, open), ext2 = pack2(ext, ext);
@@ -86,9 +88,9 @@ k1_local_kernel(const uint8_t *__restrict__ a_pk, const uint8_t *__restrict__ b_
         const bool valid = lane < G_.n_pairs;
         const int la = valid ? la_arr[p] : 0;
         int bestHo = open, bi = -1, bj = -1, ovf = 0;
-        const uint4 *ap = reinterpret_cast<const uint4 *>(a_pk + G_.a_off) + lane;       // chunk c at ap[c*32]
-        const uint4 *bp = reinterpret_cast<const uint4 *>(b_pk + G_.b_off) + lane * 2;   // pass q at bp[q*64]
-        const int nsteps = G_.la_max + 1;
+        const unsigned *ap = reinterpret_cast<const unsigned *>(a_pk + G_.a_off) + lane;  // rows 4B+1..4B+4 at ap[B*32]
+        const uint4 *bp = reinterpret_cast<const uint4 *>(b_pk + G_.b_off) + lane * 2;    // pass q at bp[q*64]
+        const int nblk = (G_.la_max + 1 + 3) >> 2;      // row steps run in blocks of 4
 
         for (int q = 0; q < G_.n_pass; ++q) {
             unsigned cb_lo[K1_HALF], cb_hi[K1_HALF], Ho[K1_HALF], F[K1_HALF];
@@ -105,79 +107,79 @@ k1_local_kernel(const uint8_t *__restrict__ a_pk, const uint8_t *__restrict__ b_
             }
             const bool first = (q == 0), last = (q == G_.n_pass - 1);
             unsigned HoD = open2;                        // diag of the left boundary, row 0
-            // Left boundary words, one per row step: low s16 = Ho, high s16 = E of column 32q-1.
-            // bq[t] feeds step i0+t+1 (it holds row i0+t+1); prefetched one 4-step block ahead.
-            unsigned bq[4], bq_next[4];
-#pragma unroll
-            for (int t = 0; t < 4; ++t) bq[t] = first ? open2 : mybnd[(size_t)(t + 1) * 32];
             unsigned r_prev = (unsigned)(nl - 1);        // PAD row for the high lane's "row 0"
             unsigned lo15_Ho = open2, lo15_E = open2;    // low lane's column 15 at the previous row (low s16 used)
             const int jbase = q * K1_STRIP;
-            uint4 ar_next = ap[0];
+            // Improvement test: a half of the packed row maximum beats thr.  In passes q > 0 a tie with the best can
+            // still win (smaller row), so ties enter the exact path as well.
+            unsigned thr2 = pack2(bestHo - (first ? 0 : 1), bestHo - (first ? 0 : 1));
+            const uint4 open4 = make_uint4(open2, open2, open2, open2);
+            uint4 bq_next = first ? open4 : mybnd[0];
+            unsigned word_next = ap[0];
+            unsigned c1 = open2, c2 = open2, c3 = open2; // boundary words of rows i0-3..i0-1 waiting for their 4th
 
-            for (int c = 0; c * K1_ROWCHUNK < nsteps; ++c) {
-                uint4 ar = ar_next;
-                ar_next = ap[(c + 1) * 32];              // a_pk has one chunk of slack
 #pragma unroll 1
-                for (int w4 = 0; w4 < 4; ++w4) {
-                    const int i0 = c * K1_ROWCHUNK + w4 * 4;      // rows i0+1 .. i0+4 (low lane)
-                    if (i0 >= nsteps) break;
-                    const unsigned word = ar.x;
-                    ar.x = ar.y; ar.y = ar.z; ar.z = ar.w;
+            for (int blk = 0; blk < nblk; ++blk) {
+                const int i0 = blk * 4;                           // rows i0+1 .. i0+4 (low lane)
+                const unsigned word = word_next;
+                const uint4 bq4 = bq_next;
+                word_next = ap[(blk + 1) * 32];                   // a_pk / bnd have one block of slack
+                if (!first) bq_next = mybnd[(size_t)(blk + 1) * 32];
+                const unsigned bq[4] = {bq4.x, bq4.y, bq4.z, bq4.w};
+                unsigned wout[4];
 #pragma unroll
-                    for (int t = 0; t < 4; ++t) bq_next[t] = first ? open2 : mybnd[(size_t)(i0 + 5 + t) * 32];
-#pragma unroll
-                    for (int t = 0; t < 4; ++t) {
-                        const int i = i0 + t + 1;                // low lane row; high lane row = i-1
-                        const unsigned r = (word >> (t * 8)) & 0xFFu;
-                        const unsigned roff_lo = r * rowstride, roff_hi = r_prev * rowstride;
-                        r_prev = r;
-                        // packed left boundary: low lane <- previous pass (row i), high lane <- low lane's column 15 (row i-1)
-                        unsigned GoP = __byte_perm(bq[t], lo15_Ho, 0x5410);
-                        unsigned E = __byte_perm(bq[t], lo15_E, 0x5432);
-                        const unsigned HoD_next = GoP;
-                        K1_CELL(0) K1_CELL(1) K1_CELL(2) K1_CELL(3) K1_CELL(4) K1_CELL(5) K1_CELL(6) K1_CELL(7)
-                        K1_CELL(8) K1_CELL(9) K1_CELL(10) K1_CELL(11) K1_CELL(12) K1_CELL(13) K1_CELL(14) K1_CELL(15)
-                        // pass boundary: high lanes of (Ho[15], E) are column 32q+31 at row i-1
-                        if (!last && i >= 2) mybnd[(size_t)(i - 1) * 32] = __byte_perm(Ho[15], E, 0x7632);
-                        lo15_Ho = Ho[15]; lo15_E = E;
-                        HoD = HoD_next;
-                        // packed row maximum of Ho (low lane: row i, high lane: row i-1)
-                        unsigned rm = __vimax3_s16x2(Ho[0], Ho[1], Ho[2]);
-                        rm = __vimax3_s16x2(rm, Ho[3], Ho[4]);
-                        rm = __vimax3_s16x2(rm, Ho[5], Ho[6]);
-                        rm = __vimax3_s16x2(rm, Ho[7], Ho[8]);
-                        rm = __vimax3_s16x2(rm, Ho[9], Ho[10]);
-                        rm = __vimax3_s16x2(rm, Ho[11], Ho[12]);
-                        rm = __vimax3_s16x2(rm, Ho[13], Ho[14]);
-                        rm = __vmaxs2(rm, Ho[15]);
+                for (int t = 0; t < 4; ++t) {
+                    const int i = i0 + t + 1;                    // low lane row; high lane row = i-1
+                    const unsigned r = (word >> (t * 8)) & 0xFFu;
+                    const unsigned roff_lo = r * rowstride, roff_hi = r_prev * rowstride;
+                    r_prev = r;
+                    // packed left boundary: low lane <- previous pass (row i), high lane <- low lane's column 15 (row i-1)
+                    unsigned GoP = __byte_perm(bq[t], lo15_Ho, 0x5410);
+                    unsigned E = __byte_perm(bq[t], lo15_E, 0x5432);
+                    const unsigned HoD_next = GoP;
+                    K1_CELL(0) K1_CELL(1) K1_CELL(2) K1_CELL(3) K1_CELL(4) K1_CELL(5) K1_CELL(6) K1_CELL(7)
+                    K1_CELL(8) K1_CELL(9) K1_CELL(10) K1_CELL(11) K1_CELL(12) K1_CELL(13) K1_CELL(14) K1_CELL(15)
+                    // pass boundary: high lanes of (Ho[15], E) are column 32q+31 at row i-1
+                    wout[t] = __byte_perm(Ho[15], E, 0x7632);
+                    if (t == 0 && !last && blk > 0) mybnd[(size_t)(blk - 1) * 32] = make_uint4(c1, c2, c3, wout[0]);
+                    lo15_Ho = Ho[15]; lo15_E = E;
+                    HoD = HoD_next;
+                    // packed row maximum of Ho (low lane: row i, high lane: row i-1)
+                    unsigned rm = __vimax3_s16x2(Ho[0], Ho[1], Ho[2]);
+                    rm = __vimax3_s16x2(rm, Ho[3], Ho[4]);
+                    rm = __vimax3_s16x2(rm, Ho[5], Ho[6]);
+                    rm = __vimax3_s16x2(rm, Ho[7], Ho[8]);
+                    rm = __vimax3_s16x2(rm, Ho[9], Ho[10]);
+                    rm = __vimax3_s16x2(rm, Ho[11], Ho[12]);
+                    rm = __vimax3_s16x2(rm, Ho[13], Ho[14]);
+                    rm = __vmaxs2(rm, Ho[15]);
+                    // (the predicate outputs of __vibmax_s16x2 gave wrong answers here with nvcc 12.9; compare the max instead)
+                    if (__vmaxs2(thr2, rm) != thr2) {
                         const int rlo = lo16(rm), rhi = hi16(rm);
-                        const int mm = max(rlo, rhi);
-                        if (mm > bestHo || (mm == bestHo && mm > open && i - 1 < bi)) {
-                            // low lane: row i
-                            if (i <= la && (rlo > bestHo || (rlo == bestHo && rlo > open && i < bi))) {
-                                int kk = 0;
+                        // low lane: row i
+                        if (i <= la && (rlo > bestHo || (rlo == bestHo && rlo > open && i < bi))) {
+                            int kk = 0;
 #pragma unroll
-                                for (int k = K1_HALF - 1; k >= 0; --k)
-                                    if (lo16(Ho[k]) == rlo) kk = k;
-                                bestHo = rlo; bi = i; bj = jbase + kk + 1;
-                                if (rlo >= limit_ho) ovf = 1;
-                            }
-                            // high lane: row i-1
-                            if (i >= 2 && i - 1 <= la && (rhi > bestHo || (rhi == bestHo && rhi > open && i - 1 < bi))) {
-                                int kk = 0;
-#pragma unroll
-                                for (int k = K1_HALF - 1; k >= 0; --k)
-                                    if (hi16(Ho[k]) == rhi) kk = k;
-                                bestHo = rhi; bi = i - 1; bj = jbase + K1_HALF + kk + 1;
-                                if (rhi >= limit_ho) ovf = 1;
-                            }
+                            for (int k = K1_HALF - 1; k >= 0; --k)
+                                if (lo16(Ho[k]) == rlo) kk = k;
+                            bestHo = rlo; bi = i; bj = jbase + kk + 1;
+                            if (rlo >= limit_ho) ovf = 1;
                         }
-                    }
+                        // high lane: row i-1
+                        if (i >= 2 && i - 1 <= la && (rhi > bestHo || (rhi == bestHo && rhi > open && i - 1 < bi))) {
+                            int kk = 0;
 #pragma unroll
-                    for (int t = 0; t < 4; ++t) bq[t] = bq_next[t];
+                            for (int k = K1_HALF - 1; k >= 0; --k)
+                                if (hi16(Ho[k]) == rhi) kk = k;
+                            bestHo = rhi; bi = i - 1; bj = jbase + K1_HALF + kk + 1;
+                            if (rhi >= limit_ho) ovf = 1;
+                        }
+                        thr2 = pack2(bestHo - (first ? 0 : 1), bestHo - (first ? 0 : 1));
+                    }
                 }
+                c1 = wout[1]; c2 = wout[2]; c3 = wout[3];
             }
+            if (!last) mybnd[(size_t)(nblk - 1) * 32] = make_uint4(c1, c2, c3, open2);   // rows 4(nblk-1)+1..+3
         }
         if (valid) {
             K1Result r;
@@ -190,9 +192,11 @@ k1_local_kernel(const uint8_t *__restrict__ a_pk, const uint8_t *__restrict__ b_
     }
 }
 
+static int k1_bnd_blocks(int la_max) { return (la_max + 1 + 3) / 4 + 2; }
+
 size_t k1_bnd_bytes(int n_blocks, int la_max)
 {
-    return (size_t)n_blocks * (K1_THREADS * 2 / 32) * (size_t)(la_max + K1_BND_SLACK) * 32 * sizeof(unsigned);
+    return (size_t)n_blocks * (K1_THREADS * 2 / 32) * (size_t)k1_bnd_blocks(la_max) * 32 * sizeof(uint4);
 }
 
 cudaError_t k1_launch(const swb_engine *e, const swb_batch *b, int n_blocks, cudaStream_t st)
@@ -207,6 +211,6 @@ cudaError_t k1_launch(const swb_engine *e, const swb_batch *b, int n_blocks, cud
     const int limit_ho = 32767 - 2 * e->smax + e->o - 1;
     k1_local_kernel<<<n_blocks, K1_THREADS * 2, smem, st>>>(
         b->d_a, b->d_b, b->d_groups, (int)b->groups.size(), b->d_la, b->d_lb, e->d_mat, nl, e->o, e->e, limit_ho,
-        reinterpret_cast<unsigned *>(e->d_bnd), b->la_max + K1_BND_SLACK, b->d_counter, b->d_res);
+        reinterpret_cast<uint4 *>(e->d_bnd), k1_bnd_blocks(b->la_max), b->d_counter, b->d_res);
     return cudaGetLastError();
 }

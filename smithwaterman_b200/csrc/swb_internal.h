@@ -17,7 +17,7 @@
 #define K1_BND_SLACK 16            // row steps run in blocks of 4: up to 3 steps past la_max+1 touch the boundary buffer
 
 struct K1Group {                    // one warp-sized work item: 32 pairs of similar shape
-    int64_t a_off;                  // byte offset of the group's row-residue block   [chunk][lane][16]
+    int64_t a_off;                  // byte offset of the group's row-residue block   [4-row block][lane] u32
     int64_t b_off;                  // byte offset of the group's column-residue block [pass][lane][32]
     int32_t la_max;                 // longest a in the group (row steps = la_max + 1)
     int32_t n_pass;                 // ceil(max lb / 32)
