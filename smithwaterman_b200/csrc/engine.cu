@@ -141,12 +141,20 @@ extern "C" int swb_engine_create(const swb_matrix *m, float gap_open, float gap_
     std::vector<int32_t> tab((size_t)nl * nl, pad);
     for (int i = 0; i < e->n; ++i) for (int j = 0; j < e->n; ++j) tab[(size_t)i * nl + j] = e->mat[(size_t)i * e->n + j];
     if ((ce = cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking)) != cudaSuccess ||
+        (ce = cudaStreamCreateWithFlags(&e->stream_up, cudaStreamNonBlocking)) != cudaSuccess ||
         (ce = cudaEventCreate(&e->ev0)) != cudaSuccess || (ce = cudaEventCreate(&e->ev1)) != cudaSuccess ||
         (ce = cudaMalloc(&e->d_mat, tab.size() * sizeof(int32_t))) != cudaSuccess ||
         (ce = cudaMemcpy(e->d_mat, tab.data(), tab.size() * sizeof(int32_t), cudaMemcpyHostToDevice)) != cudaSuccess) {
         g_create_err = std::string("CUDA init: ") + cudaGetErrorString(ce);
         swb_engine_destroy(e);
         return SWB_ERR_CUDA;
+    }
+    {   // keep freed blocks in the stream-ordered pool (cudaMallocAsync) instead of returning them to the driver
+        cudaMemPool_t pool;
+        if (cudaDeviceGetDefaultMemPool(&pool, device) == cudaSuccess) {
+            unsigned long long keep = ~0ull;
+            cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep);
+        }
     }
     e->stats.scale = e->scale; e->stats.exact_scale = e->exact_scale;
     *out = e;
@@ -159,9 +167,11 @@ extern "C" void swb_engine_destroy(swb_engine *e)
     cudaSetDevice(e->device);
     if (e->d_mat) cudaFree(e->d_mat);
     if (e->d_bnd) cudaFree(e->d_bnd);
+    if (e->h_stage) cudaFreeHost(e->h_stage);
     if (e->ev0) cudaEventDestroy(e->ev0);
     if (e->ev1) cudaEventDestroy(e->ev1);
     if (e->stream) cudaStreamDestroy(e->stream);
+    if (e->stream_up) cudaStreamDestroy(e->stream_up);
     delete e;
 }
 

@@ -43,12 +43,14 @@ struct swb_engine {
     int32_t smax = 0, smin = 0;     // scaled matrix extremes
     std::vector<int32_t> mat;       // n*n scaled
     std::vector<float> matf;        // n*n as given
-    cudaStream_t stream = nullptr;
+    cudaStream_t stream = nullptr;      // compute stream (kernels, result D2H)
+    cudaStream_t stream_up = nullptr;   // copy stream of the pipelined host-buffer path (H2D, encode, pack)
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     int sm_count = 0;
     int32_t *d_mat = nullptr;       // (n+1)*(n+1) int32 scaled, PAD row/col included
     // scratch owned by the engine, grown on demand
     void *d_bnd = nullptr; size_t bnd_bytes = 0;
+    void *h_stage = nullptr; size_t stage_bytes = 0, stage_used = 0;   // pinned results arena of swb_score_batch
     swb_stats stats = {};
     std::string err;
 };
