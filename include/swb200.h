@@ -12,6 +12,7 @@
  *   swb_align              SequenceAlignment::align          SA.rs:389-392 (OCL.rs:796 align)
  *   swb_align_batch        the serial loop of `sa_opencl -list`  OCL-main.rs:295-316 (one call, n pairs)
  *   swb_score_batch        align_partial(.., score_only=true) per pair  SA.rs:393-467
+ *   swb_search_scores      the all-vs-all loops of the CLIs with one fixed query (SA-main.rs:35-45), n subjects per call
  *   swb_batch_*            the same as swb_score_batch, split into upload / run / fetch so that a
  *                          caller can keep inputs resident in HBM (bench.py `value` vs `e2e`)
  *   swb_alignment_free     Drop of the (Vec<String>,Vec<String>,f32) result
@@ -112,6 +113,12 @@ void swb_alignment_free(swb_alignment *a);
  * -1,-1 when no positive score) or (la,lb) (global/glocal, SA.rs:296-309). */
 int swb_score_batch(swb_engine *e, const char *a_all, const int64_t *off_a, const char *b_all,
                     const int64_t *off_b, int64_t n, float *scores, int64_t *end_a, int64_t *end_b);
+
+/* Database search, scoring stage: one query (the `a` sequence) against n database sequences (`b`); results as
+ * swb_score_batch.  The caller selects its top-K from `scores` (ties: lower index first keeps multi-GPU runs
+ * deterministic) and obtains the alignments of those hits with swb_align_batch. */
+int swb_search_scores(swb_engine *e, const char *query, int64_t lq, const char *db_all, const int64_t *off_db,
+                      int64_t n, float *scores, int64_t *end_q, int64_t *end_t);
 
 /* The same, staged: upload (encode + pack + H2D) once, run the kernels any number of times on the
  * resident batch, fetch (D2H + unpermute).  swb_batch_run is asynchronous on the engine's stream;

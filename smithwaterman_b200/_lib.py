@@ -81,6 +81,7 @@ def lib():
         "swb_align_batch": (c.c_int, [vp, vp, vp, vp, vp, i64, c.c_uint, c.POINTER(Alignment)]),
         "swb_alignment_free": (None, [c.POINTER(Alignment)]),
         "swb_score_batch": (c.c_int, [vp, vp, vp, vp, vp, i64, vp, vp, vp]),
+        "swb_search_scores": (c.c_int, [vp, vp, i64, vp, vp, i64, vp, vp, vp]),
         "swb_batch_upload": (c.c_int, [vp, vp, vp, vp, vp, i64, c.POINTER(vp)]),
         "swb_batch_run": (c.c_int, [vp, vp]),
         "swb_batch_fetch": (c.c_int, [vp, vp, vp, vp, vp]),

@@ -12,7 +12,7 @@
 
 #include "swb_internal.h"
 
-#define K1_MAX_LEN 4096            // longer pairs go to the wavefront kernel
+#define K1_MAX_LEN 8192            // longer pairs go to the wavefront kernel
 
 struct BatchDev {                  // device-only members that do not fit the plain struct in the header
     uint8_t *codes_a = nullptr, *codes_b = nullptr;   // encoded residues, caller layout
@@ -25,6 +25,7 @@ struct BatchDev {                  // device-only members that do not fit the pl
     std::vector<int32_t> degenerate;                         // caller indices with la==0 or lb==0
     int n_k1 = 0;
     int64_t base_a = 0, base_b = 0;                          // caller offset of the first residue held on the device
+    int64_t shared_la = -1;                                  // >= 0: all pairs share one `a` (database search)
     int16_t *d_tab = nullptr;
     K1Result *h_res = nullptr; KWResult *h_kwres = nullptr; int32_t *h_err = nullptr;   // pinned staging (engine arena or own)
     bool own_stage = false;
@@ -65,7 +66,7 @@ __global__ void k1_pack_kernel(const uint8_t *__restrict__ codes_a, const uint8_
                                const int64_t *__restrict__ off_a, const int64_t *__restrict__ off_b,
                                const int32_t *__restrict__ order, const K1Group *__restrict__ groups,
                                uint8_t *__restrict__ a_pk, uint8_t *__restrict__ b_pk, int32_t *__restrict__ la_arr,
-                               int32_t *__restrict__ lb_arr, int pad, int64_t base_a, int64_t base_b)
+                               int32_t *__restrict__ lb_arr, int pad, int64_t base_a, int64_t base_b, int shared_la)
 {
     const K1Group G = groups[blockIdx.x];
     const int lane = threadIdx.x & 31, sub = threadIdx.x >> 5, nsub = blockDim.x >> 5;
@@ -73,12 +74,13 @@ __global__ void k1_pack_kernel(const uint8_t *__restrict__ codes_a, const uint8_
     int64_t oa = 0, ob = 0; int la = 0, lb = 0;
     if (valid) {
         const int src = order[G.first_pair + lane];
-        oa = off_a[src] - base_a; la = (int)(off_a[src + 1] - off_a[src]);
+        if (shared_la < 0) { oa = off_a[src] - base_a; la = (int)(off_a[src + 1] - off_a[src]); }
         ob = off_b[src] - base_b; lb = (int)(off_b[src + 1] - off_b[src]);
-        if (sub == 0) { la_arr[G.first_pair + lane] = la; lb_arr[G.first_pair + lane] = lb; }
     }
+    if (shared_la >= 0) { oa = 0; la = shared_la; }                // database search: every lane reads the same `a` (the query)
+    if (valid && sub == 0) { la_arr[G.first_pair + lane] = la; lb_arr[G.first_pair + lane] = lb; }
     const int n_blk = (G.la_max + 1 + 3) / 4 + 1;              // 4 rows per word, one word of slack (all PAD)
-    for (int c = sub; c < n_blk; c += nsub) {
+    for (int c = sub; c < n_blk && (shared_la < 0 || blockIdx.x == 0); c += nsub) {   // shared query: one row block for all items
         unsigned r = 0;
 #pragma unroll
         for (int s = 0; s < 4; ++s) {
@@ -151,7 +153,7 @@ extern "C" void swb_batch_free(swb_engine *e, swb_batch *b) { if (e) batch_relea
 // residues and offsets, in-place encoding, packing into the K1 layout.  `off_*` are the caller's absolute offsets;
 // residues are taken from a_all[off_a[0] .. off_a[n]).  use_arena: results staging comes from the engine's arena.
 static int batch_upload_impl(swb_engine *e, const char *a_all, const int64_t *off_a, const char *b_all,
-                             const int64_t *off_b, int64_t n, bool use_arena, cudaStream_t up, swb_batch **out)
+                             const int64_t *off_b, int64_t n, int64_t shared_la, bool use_arena, cudaStream_t up, swb_batch **out)
 {
     *out = nullptr;
     swb_batch *b = new swb_batch();
@@ -159,8 +161,10 @@ static int batch_upload_impl(swb_engine *e, const char *a_all, const int64_t *of
     b->dev = d;
     b->n = n;
     struct Guard { swb_engine *e; swb_batch *b; bool ok = false; ~Guard() { if (!ok) batch_release(e, b); } } guard{e, b};
-    d->base_a = n ? off_a[0] : 0; d->base_b = n ? off_b[0] : 0;
-    const int64_t na = n ? off_a[n] - d->base_a : 0, nb = n ? off_b[n] - d->base_b : 0;
+    const bool shared = shared_la >= 0;
+    d->shared_la = shared_la;
+    d->base_a = (n && !shared) ? off_a[0] : 0; d->base_b = n ? off_b[0] : 0;
+    const int64_t na = shared ? shared_la : (n ? off_a[n] - d->base_a : 0), nb = n ? off_b[n] - d->base_b : 0;
     if (na < 0 || nb < 0 || (na > 0 && !a_all) || (nb > 0 && !b_all)) { e->err = "bad sequence buffer / offsets"; return SWB_ERR_ARG; }
     const bool use_k1 = (e->mode == SWB_LOCAL && e->o <= e->e);
 
@@ -171,7 +175,7 @@ static int batch_upload_impl(swb_engine *e, const char *a_all, const int64_t *of
     int la_cap = 0, pass_cap = 0;
     b->cells = 0;
     for (int64_t k = 0; k < n; ++k) {
-        const int64_t la = off_a[k + 1] - off_a[k], lb = off_b[k + 1] - off_b[k];
+        const int64_t la = shared ? shared_la : off_a[k + 1] - off_a[k], lb = off_b[k + 1] - off_b[k];
         if (la < 0 || lb < 0 || la > 0x3FFFFFFF || lb > 0x3FFFFFFF) { e->err = "bad offsets"; return SWB_ERR_ARG; }
         b->la[k] = (int32_t)la; b->lb[k] = (int32_t)lb;
         b->cells += (double)la * (double)lb;
@@ -206,8 +210,8 @@ static int batch_upload_impl(swb_engine *e, const char *a_all, const int64_t *of
                 lam = std::max(lam, b->la[k]);
                 npm = std::max(npm, (b->lb[k] + K1_STRIP - 1) / K1_STRIP);
             }
-            G.la_max = lam; G.n_pass = npm; G.a_off = a_off; G.b_off = b_off;
-            a_off += (int64_t)((lam + 1 + 3) / 4 + 1) * 32 * 4;
+            G.la_max = lam; G.n_pass = npm; G.a_off = shared ? 0 : a_off; G.b_off = b_off;
+            if (!shared || g == 0) a_off += (int64_t)((lam + 1 + 3) / 4 + 1) * 32 * 4;
             b_off += (int64_t)npm * 32 * 32;
         }
         b->a_bytes = (size_t)a_off; b->b_bytes = (size_t)b_off; b->la_max = la_cap;
@@ -216,7 +220,8 @@ static int batch_upload_impl(swb_engine *e, const char *a_all, const int64_t *of
     // ---- device buffers + H2D (stream-ordered, no host synchronisation)
     const int64_t na_p = pad16(na) + 16, nb_p = pad16(nb) + 16;
     DEV_ALLOC_ON(e, up, d->codes_a, na_p); DEV_ALLOC_ON(e, up, d->codes_b, nb_p);
-    DEV_ALLOC_ON(e, up, d->off_a, (n + 1) * sizeof(int64_t)); DEV_ALLOC_ON(e, up, d->off_b, (n + 1) * sizeof(int64_t));
+    if (!shared) DEV_ALLOC_ON(e, up, d->off_a, (n + 1) * sizeof(int64_t));
+    DEV_ALLOC_ON(e, up, d->off_b, (n + 1) * sizeof(int64_t));
     DEV_ALLOC_ON(e, up, d->err, sizeof(int32_t));
     DEV_ALLOC_ON(e, up, d->d_tab, 256 * sizeof(int16_t));
     CUDA_TRY(e, cudaMemsetAsync(d->err, 0, sizeof(int32_t), up));
@@ -225,7 +230,7 @@ static int batch_upload_impl(swb_engine *e, const char *a_all, const int64_t *of
     if (na) CUDA_TRY(e, cudaMemcpyAsync(d->codes_a, a_all + d->base_a, na, cudaMemcpyHostToDevice, up));
     if (nb) CUDA_TRY(e, cudaMemcpyAsync(d->codes_b, b_all + d->base_b, nb, cudaMemcpyHostToDevice, up));
     if (n) {
-        CUDA_TRY(e, cudaMemcpyAsync(d->off_a, off_a, (n + 1) * sizeof(int64_t), cudaMemcpyHostToDevice, up));
+        if (!shared) CUDA_TRY(e, cudaMemcpyAsync(d->off_a, off_a, (n + 1) * sizeof(int64_t), cudaMemcpyHostToDevice, up));
         CUDA_TRY(e, cudaMemcpyAsync(d->off_b, off_b, (n + 1) * sizeof(int64_t), cudaMemcpyHostToDevice, up));
     }
     e->stats.h2d_bytes += (double)na + (double)nb + 2.0 * (n + 1) * sizeof(int64_t);
@@ -247,7 +252,7 @@ static int batch_upload_impl(swb_engine *e, const char *a_all, const int64_t *of
         CUDA_TRY(e, cudaMemcpyAsync(d->order, b->order.data(), d->n_k1 * sizeof(int32_t), cudaMemcpyHostToDevice, up));
         e->stats.h2d_bytes += (double)ng * sizeof(K1Group) + (double)d->n_k1 * sizeof(int32_t);
         k1_pack_kernel<<<ng, 128, 0, up>>>(d->codes_a, d->codes_b, d->off_a, d->off_b, d->order, b->d_groups,
-                                                  b->d_a, b->d_b, b->d_la, b->d_lb, e->n, d->base_a, d->base_b);
+                                                  b->d_a, b->d_b, b->d_la, b->d_lb, e->n, d->base_a, d->base_b, (int)shared_la);
         CUDA_TRY(e, cudaGetLastError());
         const size_t need = k1_bnd_bytes(e->sm_count, b->la_max);
         if (need > e->bnd_bytes) {                          // engine-owned scratch, grown on demand (rare)
@@ -266,7 +271,7 @@ static int batch_upload_impl(swb_engine *e, const char *a_all, const int64_t *of
         for (int t = 0; t < d->n_kw; ++t) {
             const int32_t k = d->kw_idx[t];
             KWPair &P = d->h_kw[t];
-            P.a_off = off_a[k] - d->base_a; P.b_off = off_b[k] - d->base_b; P.la = b->la[k]; P.lb = b->lb[k];
+            P.a_off = shared ? 0 : off_a[k] - d->base_a; P.b_off = off_b[k] - d->base_b; P.la = b->la[k]; P.lb = b->lb[k];
             P.dir_off = -1; P.bnd_off = bnd_off;
             bnd_off += kw_bnd_elems(P.la, P.lb);
         }
@@ -310,7 +315,7 @@ extern "C" int swb_batch_upload(swb_engine *e, const char *a_all, const int64_t 
     CUDA_TRY(e, cudaSetDevice(e->device));
     e->stats.cells = 0; e->stats.h2d_bytes = 0; e->stats.d2h_bytes = 0; e->stats.i32_reruns = 0;
     swb_batch *b = nullptr;
-    int rc = batch_upload_impl(e, a_all, off_a, b_all, off_b, n, false, e->stream, &b);
+    int rc = batch_upload_impl(e, a_all, off_a, b_all, off_b, n, -1, false, e->stream, &b);
     if (rc != SWB_OK) return rc;
     CUDA_TRY(e, cudaStreamSynchronize(e->stream));           // the staged API reports letter errors here
     if (*b->dev->h_err) {
@@ -427,13 +432,13 @@ static int batch_fetch_finish(swb_engine *e, swb_batch *b, float *scores, int64_
         const int nr = (int)redo.size();
         std::vector<KWPair> hp(nr);
         std::vector<int64_t> oa(b->n + 1), ob(b->n + 1);
-        CUDA_TRY(e, cudaMemcpyAsync(oa.data(), d->off_a, (b->n + 1) * sizeof(int64_t), cudaMemcpyDeviceToHost, e->stream));
+        if (d->shared_la < 0) CUDA_TRY(e, cudaMemcpyAsync(oa.data(), d->off_a, (b->n + 1) * sizeof(int64_t), cudaMemcpyDeviceToHost, e->stream));
         CUDA_TRY(e, cudaMemcpyAsync(ob.data(), d->off_b, (b->n + 1) * sizeof(int64_t), cudaMemcpyDeviceToHost, e->stream));
         CUDA_TRY(e, cudaStreamSynchronize(e->stream));
         int64_t bnd_off = 0;
         for (int t = 0; t < nr; ++t) {
             const int32_t k = redo[t];
-            hp[t].a_off = oa[k] - d->base_a; hp[t].b_off = ob[k] - d->base_b; hp[t].la = b->la[k]; hp[t].lb = b->lb[k];
+            hp[t].a_off = d->shared_la >= 0 ? 0 : oa[k] - d->base_a; hp[t].b_off = ob[k] - d->base_b; hp[t].la = b->la[k]; hp[t].lb = b->lb[k];
             hp[t].dir_off = -1; hp[t].bnd_off = bnd_off;
             bnd_off += kw_bnd_elems(hp[t].la, hp[t].lb);
         }
@@ -470,11 +475,9 @@ extern "C" int swb_batch_fetch(swb_engine *e, swb_batch *b, float *scores, int64
 // sorts chunk c+2 / scatters the results of chunk c-1 (with pinned caller memory the copies are truly asynchronous).
 #define SCORE_CHUNK_PAIRS 262144
 
-extern "C" int swb_score_batch(swb_engine *e, const char *a_all, const int64_t *off_a, const char *b_all,
-                               const int64_t *off_b, int64_t n, float *scores, int64_t *end_a, int64_t *end_b)
+static int score_pipeline(swb_engine *e, const char *a_all, const int64_t *off_a, int64_t shared_la, const char *b_all,
+                          const int64_t *off_b, int64_t n, float *scores, int64_t *end_a, int64_t *end_b)
 {
-    if (!e) return SWB_ERR_ARG;
-    if (n < 0 || (n > 0 && (!off_a || !off_b || !scores || !end_a || !end_b))) { e->err = "bad argument"; return SWB_ERR_ARG; }
     if (n > 0x7FFFFFF0) { e->err = "too many pairs"; return SWB_ERR_ARG; }
     CUDA_TRY(e, cudaSetDevice(e->device));
     e->stats.cells = 0; e->stats.h2d_bytes = 0; e->stats.d2h_bytes = 0; e->stats.i32_reruns = 0; e->stats.launches = 0;
@@ -504,7 +507,8 @@ extern "C" int swb_score_batch(swb_engine *e, const char *a_all, const int64_t *
         const int64_t start = cuts[c], cnt = cuts[c + 1] - cuts[c];
         swb_batch *cur = nullptr;
         double t0 = now();
-        rc = batch_upload_impl(e, a_all, off_a + start, b_all, off_b + start, cnt, true, e->stream_up, &cur);
+        rc = batch_upload_impl(e, a_all, shared_la >= 0 ? nullptr : off_a + start, b_all, off_b + start, cnt, shared_la, true,
+                               e->stream_up, &cur);
         double t1 = now(); t_up += t1 - t0;
         int64_t launches = 0;
         if (rc == SWB_OK) rc = batch_launch(e, cur, &launches);
@@ -535,4 +539,23 @@ extern "C" int swb_score_batch(swb_engine *e, const char *a_all, const int64_t *
                            (long long)n, (long long)n_chunks, now() - t_begin, t_up, t_launch, t_fin, t_rel, ms);
     }
     return rc;
+}
+
+extern "C" int swb_score_batch(swb_engine *e, const char *a_all, const int64_t *off_a, const char *b_all,
+                               const int64_t *off_b, int64_t n, float *scores, int64_t *end_a, int64_t *end_b)
+{
+    if (!e) return SWB_ERR_ARG;
+    if (n < 0 || (n > 0 && (!off_a || !off_b || !scores || !end_a || !end_b))) { e->err = "bad argument"; return SWB_ERR_ARG; }
+    return score_pipeline(e, a_all, off_a, -1, b_all, off_b, n, scores, end_a, end_b);
+}
+
+// Database search, scoring stage: one query against n database sequences (score_only semantics per pair,
+// SA.rs:438-467).  The query is uploaded and packed once and shared by all K1 work items.
+extern "C" int swb_search_scores(swb_engine *e, const char *query, int64_t lq, const char *db_all, const int64_t *off_db,
+                                 int64_t n, float *scores, int64_t *end_q, int64_t *end_t)
+{
+    if (!e) return SWB_ERR_ARG;
+    if (lq < 0 || n < 0 || (lq > 0 && !query) || (n > 0 && (!off_db || !scores || !end_q || !end_t))) { e->err = "bad argument"; return SWB_ERR_ARG; }
+    if (lq > 0x3FFFFFFF) { e->err = "query too long"; return SWB_ERR_ARG; }
+    return score_pipeline(e, query, nullptr, lq, db_all, off_db, n, scores, end_q, end_t);
 }

@@ -231,3 +231,36 @@ def test_symmetry_property_large():
     assert np.array_equal(np.rint(s1[sub].astype(np.float64) * 2).astype(np.int64), osc)
     assert np.array_equal(ea[sub], oi) and np.array_equal(eb[sub], oj)
     eng.close()
+
+
+def test_database_search_topk_with_traceback():
+    """configs[2] in miniature: one query vs a database with planted homologs; top-k list (scores, order, end cells)
+    and the hit alignments must equal the oracle's; the shared-query K1 path and the per-pair path must agree."""
+    from smithwaterman_b200 import search as S
+    rng = np.random.default_rng(20243)
+    m = swb.SubstitutionMatrix.get_blosum62_matrix()
+    eng = swb.SequenceAlignment(m, 10.0, 0.5, swb.ALIGN_LOCAL)
+    query = _rand_seqs(rng, 1, 700, 700)[0]
+    seqs = _rand_seqs(rng, 3000, 30, 900)
+    for k in range(0, 3000, 60):                                   # planted homologs: mutated windows of the query
+        lo = int(rng.integers(0, 400)); w = bytearray(query[lo:lo + int(rng.integers(100, 300))])
+        for p in rng.integers(0, len(w), len(w) // 4):
+            w[p] = ord(AA[rng.integers(0, 20)])
+        seqs[k] = bytes(w)
+    seqs[61] = seqs[60]                                            # exact duplicate -> tie, lower index first
+    db = S.Database.from_sequences(seqs)
+    hits = S.search(eng, query, db, topk=40, traceback=True, retain_all=False)
+    sc, eq, et = S.search_scores(eng, query, db)
+    sc2, eq2, et2 = eng.score_batch([query] * len(seqs), seqs)
+    assert np.array_equal(sc, sc2) and np.array_equal(eq, eq2) and np.array_equal(et, et2)
+    osc, oi, oj = _oracle_scores(m, [query] * len(seqs), seqs, 10.0, 0.5, swb.ALIGN_LOCAL)
+    assert np.array_equal(np.rint(sc.astype(np.float64) * 2).astype(np.int64), osc)
+    order = np.lexsort((np.arange(len(seqs)), -osc))[:40]
+    assert [h["idx"] for h in hits] == order.tolist()
+    assert any(h["idx"] == 60 for h in hits) and [h["idx"] for h in hits].index(60) + 1 == [h["idx"] for h in hits].index(61)
+    oeng = O.Engine(_omatrix(m), 10.0, 0.5, swb.ALIGN_LOCAL)
+    for h in hits:
+        r1, r2, s = oeng.align(query.decode(), seqs[h["idx"]].decode(), False)
+        assert (h["aln_q"], h["aln_t"], h["score"]) == ("".join(r1), "".join(r2), s)
+        assert (h["end_q"], h["end_t"]) == (oi[h["idx"]], oj[h["idx"]])
+    eng.close()
