@@ -117,30 +117,32 @@ extern "C" int swb_align_batch(swb_engine *e, const char *a_all, const int64_t *
     while (pos < work.size()) {
         // chunk of pairs whose direction bytes fit the budget
         std::vector<KWPair> hp; std::vector<int64_t> out_off;
-        int64_t dir_total = 0, bnd_total = 0, out_total = 0;
+        int64_t dir_total = 0, out_total = 0;
         size_t end = pos;
         while (end < work.size()) {
             const int64_t k = work[end];
             const int32_t la = (int32_t)(off_a[k + 1] - off_a[k]), lb = (int32_t)(off_b[k + 1] - off_b[k]);
             const int64_t db = kw_dir_bytes(la, lb);
             if (!hp.empty() && dir_total + db > DIR_BUDGET_BYTES) break;
-            KWPair P; P.a_off = off_a[k]; P.b_off = off_b[k]; P.la = la; P.lb = lb; P.dir_off = dir_total; P.bnd_off = bnd_total;
+            KWPair P; P.a_off = off_a[k]; P.b_off = off_b[k]; P.la = la; P.lb = lb; P.dir_off = dir_total; P.bnd_off = 0; P.scr_off = 0;
             hp.push_back(P); out_off.push_back(out_total);
-            dir_total += db; bnd_total += kw_bnd_elems(la, lb); out_total += (int64_t)la + lb + 1;
+            dir_total += db; out_total += (int64_t)la + lb + 1;
             ++end;
         }
         const int np = (int)hp.size();
-        DevBuf d_pairs, d_res, d_dir, d_bnd, d_off, d_xa, d_xb, d_nc;
+        KWPlan plan; kw_plan(e, hp.data(), np, &plan);
+        DevBuf d_pairs, d_res, d_dir, d_bnd, d_scr, d_off, d_xa, d_xb, d_nc;
         CUDA_TRY(e, cudaMalloc(&d_pairs.p, np * sizeof(KWPair))); CUDA_TRY(e, cudaMalloc(&d_res.p, np * sizeof(KWResult)));
-        CUDA_TRY(e, cudaMalloc(&d_dir.p, dir_total + 16)); CUDA_TRY(e, cudaMalloc(&d_bnd.p, bnd_total * sizeof(int4)));
+        CUDA_TRY(e, cudaMalloc(&d_dir.p, dir_total + 16)); CUDA_TRY(e, cudaMalloc(&d_bnd.p, plan.bnd_elems * sizeof(int4)));
+        CUDA_TRY(e, cudaMalloc(&d_scr.p, plan.scratch_ints * sizeof(int)));
         CUDA_TRY(e, cudaMalloc(&d_off.p, np * sizeof(int64_t)));
         CUDA_TRY(e, cudaMalloc(&d_xa.p, out_total * sizeof(int32_t))); CUDA_TRY(e, cudaMalloc(&d_xb.p, out_total * sizeof(int32_t)));
         CUDA_TRY(e, cudaMalloc(&d_nc.p, np * sizeof(int32_t)));
         CUDA_TRY(e, cudaMemcpyAsync(d_pairs.p, hp.data(), np * sizeof(KWPair), cudaMemcpyHostToDevice, e->stream));
         CUDA_TRY(e, cudaMemcpyAsync(d_off.p, out_off.data(), np * sizeof(int64_t), cudaMemcpyHostToDevice, e->stream));
         CUDA_TRY(e, cudaEventRecord(e->ev0, e->stream));
-        CUDA_TRY(e, kw_launch(e, d_a.as<uint8_t>(), d_b.as<uint8_t>(), d_pairs.as<KWPair>(), np, d_dir.as<uint8_t>(),
-                              d_bnd.as<int4>(), d_res.as<KWResult>(), e->stream));
+        CUDA_TRY(e, kw_launch(e, d_a.as<uint8_t>(), d_b.as<uint8_t>(), d_pairs.as<KWPair>(), np, plan, d_dir.as<uint8_t>(),
+                              d_bnd.as<int4>(), d_scr.as<int>(), d_res.as<KWResult>(), e->stream));
         CUDA_TRY(e, kt_launch(e, d_pairs.as<KWPair>(), d_res.as<KWResult>(), np, d_dir.as<uint8_t>(), d_off.as<int64_t>(),
                               d_xa.as<int32_t>(), d_xb.as<int32_t>(), d_nc.as<int32_t>(), e->stream));
         CUDA_TRY(e, cudaEventRecord(e->ev1, e->stream));

@@ -19,7 +19,7 @@ struct BatchDev {                  // device-only members that do not fit the pl
     int64_t *off_a = nullptr, *off_b = nullptr;
     int32_t *order = nullptr;                          // sorted position -> caller index (K1 pairs)
     int32_t *err = nullptr;
-    KWPair *kw_pairs = nullptr; KWResult *kw_res = nullptr; int4 *kw_bnd = nullptr;
+    KWPair *kw_pairs = nullptr; KWResult *kw_res = nullptr; int4 *kw_bnd = nullptr; int *kw_scr = nullptr; KWPlan kw_plan_;
     int n_kw = 0;
     std::vector<KWPair> h_kw; std::vector<int32_t> kw_idx;   // caller index of each KW pair
     std::vector<int32_t> degenerate;                         // caller indices with la==0 or lb==0
@@ -133,7 +133,7 @@ static void batch_release(swb_engine *e, swb_batch *b)
     BatchDev *d = dev_of(b);
     if (d) {
         dev_free(e, d->codes_a); dev_free(e, d->codes_b); dev_free(e, d->off_a); dev_free(e, d->off_b); dev_free(e, d->order);
-        dev_free(e, d->err); dev_free(e, d->kw_pairs); dev_free(e, d->kw_res); dev_free(e, d->kw_bnd); dev_free(e, d->d_tab);
+        dev_free(e, d->err); dev_free(e, d->kw_pairs); dev_free(e, d->kw_res); dev_free(e, d->kw_bnd); dev_free(e, d->kw_scr); dev_free(e, d->d_tab);
         if (d->own_stage) { cudaFreeHost(d->h_res); cudaFreeHost(d->h_kwres); cudaFreeHost(d->h_err); }
         if (d->ev0) cudaEventDestroy(d->ev0);
         if (d->ev1) cudaEventDestroy(d->ev1);
@@ -267,17 +267,17 @@ static int batch_upload_impl(swb_engine *e, const char *a_all, const int64_t *of
     d->n_kw = (int)d->kw_idx.size();
     if (d->n_kw) {
         d->h_kw.resize(d->n_kw);
-        int64_t bnd_off = 0;
         for (int t = 0; t < d->n_kw; ++t) {
             const int32_t k = d->kw_idx[t];
             KWPair &P = d->h_kw[t];
             P.a_off = shared ? 0 : off_a[k] - d->base_a; P.b_off = off_b[k] - d->base_b; P.la = b->la[k]; P.lb = b->lb[k];
-            P.dir_off = -1; P.bnd_off = bnd_off;
-            bnd_off += kw_bnd_elems(P.la, P.lb);
+            P.dir_off = -1;
         }
+        kw_plan(e, d->h_kw.data(), d->n_kw, &d->kw_plan_);
         DEV_ALLOC_ON(e, up, d->kw_pairs, d->n_kw * sizeof(KWPair));
         DEV_ALLOC_ON(e, up, d->kw_res, d->n_kw * sizeof(KWResult));
-        DEV_ALLOC_ON(e, up, d->kw_bnd, bnd_off * sizeof(int4));
+        DEV_ALLOC_ON(e, up, d->kw_bnd, d->kw_plan_.bnd_elems * sizeof(int4));
+        DEV_ALLOC_ON(e, up, d->kw_scr, d->kw_plan_.scratch_ints * sizeof(int));
         CUDA_TRY(e, cudaMemcpyAsync(d->kw_pairs, d->h_kw.data(), d->n_kw * sizeof(KWPair), cudaMemcpyHostToDevice, up));
         e->stats.h2d_bytes += (double)d->n_kw * sizeof(KWPair);
     }
@@ -333,7 +333,7 @@ static int batch_launch(swb_engine *e, swb_batch *b, int64_t *launches)
     CUDA_TRY(e, cudaStreamWaitEvent(e->stream, d->ev_ready, 0));     // upload may have run on the copy stream
     if (d->n_k1) { CUDA_TRY(e, k1_launch(e, b, e->sm_count, e->stream)); ++*launches; }
     if (d->n_kw) {
-        CUDA_TRY(e, kw_launch(e, d->codes_a, d->codes_b, d->kw_pairs, d->n_kw, nullptr, d->kw_bnd, d->kw_res, e->stream));
+        CUDA_TRY(e, kw_launch(e, d->codes_a, d->codes_b, d->kw_pairs, d->n_kw, d->kw_plan_, nullptr, d->kw_bnd, d->kw_scr, d->kw_res, e->stream));
         ++*launches;
     }
     return SWB_OK;
@@ -435,21 +435,21 @@ static int batch_fetch_finish(swb_engine *e, swb_batch *b, float *scores, int64_
         if (d->shared_la < 0) CUDA_TRY(e, cudaMemcpyAsync(oa.data(), d->off_a, (b->n + 1) * sizeof(int64_t), cudaMemcpyDeviceToHost, e->stream));
         CUDA_TRY(e, cudaMemcpyAsync(ob.data(), d->off_b, (b->n + 1) * sizeof(int64_t), cudaMemcpyDeviceToHost, e->stream));
         CUDA_TRY(e, cudaStreamSynchronize(e->stream));
-        int64_t bnd_off = 0;
         for (int t = 0; t < nr; ++t) {
             const int32_t k = redo[t];
             hp[t].a_off = d->shared_la >= 0 ? 0 : oa[k] - d->base_a; hp[t].b_off = ob[k] - d->base_b; hp[t].la = b->la[k]; hp[t].lb = b->lb[k];
-            hp[t].dir_off = -1; hp[t].bnd_off = bnd_off;
-            bnd_off += kw_bnd_elems(hp[t].la, hp[t].lb);
+            hp[t].dir_off = -1;
         }
-        KWPair *dp = nullptr; KWResult *dr = nullptr; int4 *db = nullptr;
-        DEV_ALLOC(e, dp, nr * sizeof(KWPair)); DEV_ALLOC(e, dr, nr * sizeof(KWResult)); DEV_ALLOC(e, db, bnd_off * sizeof(int4));
+        KWPlan pl; kw_plan(e, hp.data(), nr, &pl);
+        KWPair *dp = nullptr; KWResult *dr = nullptr; int4 *db = nullptr; int *ds = nullptr;
+        DEV_ALLOC(e, dp, nr * sizeof(KWPair)); DEV_ALLOC(e, dr, nr * sizeof(KWResult)); DEV_ALLOC(e, db, pl.bnd_elems * sizeof(int4));
+        DEV_ALLOC(e, ds, pl.scratch_ints * sizeof(int));
         CUDA_TRY(e, cudaMemcpyAsync(dp, hp.data(), nr * sizeof(KWPair), cudaMemcpyHostToDevice, e->stream));
-        CUDA_TRY(e, kw_launch(e, d->codes_a, d->codes_b, dp, nr, nullptr, db, dr, e->stream));
+        CUDA_TRY(e, kw_launch(e, d->codes_a, d->codes_b, dp, nr, pl, nullptr, db, ds, dr, e->stream));
         std::vector<KWResult> rr(nr);
         CUDA_TRY(e, cudaMemcpyAsync(rr.data(), dr, nr * sizeof(KWResult), cudaMemcpyDeviceToHost, e->stream));
         CUDA_TRY(e, cudaStreamSynchronize(e->stream));
-        dev_free(e, dp); dev_free(e, dr); dev_free(e, db);
+        dev_free(e, dp); dev_free(e, dr); dev_free(e, db); dev_free(e, ds);
         for (int t = 0; t < nr; ++t) {
             const int32_t k = redo[t];
             scores[k] = to_f(rr[t].score); end_a[k] = rr[t].end_i; end_b[k] = rr[t].end_j;

@@ -264,3 +264,37 @@ def test_database_search_topk_with_traceback():
         assert (h["aln_q"], h["aln_t"], h["score"]) == ("".join(r1), "".join(r2), s)
         assert (h["end_q"], h["end_t"]) == (oi[h["idx"]], oj[h["idx"]])
     eng.close()
+
+
+@pytest.mark.parametrize("mode", [swb.ALIGN_LOCAL, swb.ALIGN_GLOCAL, swb.ALIGN_GLOBAL])
+def test_long_pairs_team_wavefront(mode):
+    """A few long pairs make the wavefront kernel sweep each pair with a team of warps (strips handed over through
+    the global boundary ring): strings and scores must still equal the dense oracle."""
+    rng = np.random.default_rng(77 + mode)
+    m = swb.SubstitutionMatrix.get_mat_matrix(2.0, -3.0)
+    eng = swb.SequenceAlignment(m, 5.0, 2.0, mode)
+    oeng = O.Engine(_omatrix(m), 5.0, 2.0, mode)
+    sa, sb = [], []
+    for la in (2500, 4000, 1800):
+        base = _rand_seqs(rng, 1, la, la, "ACGT")[0]
+        out = bytearray()
+        for ch in base:
+            r = rng.random()
+            if r < 0.05:
+                out.append(ord("ACGT"[rng.integers(0, 4)]))
+            elif r < 0.08:
+                out.append(ch); out.append(ord("ACGT"[rng.integers(0, 4)]))
+            elif r < 0.11:
+                continue
+            else:
+                out.append(ch)
+        sa.append(base); sb.append(bytes(out))
+    res = eng.align_list(sa, sb, True)
+    for a, b, out in zip(sa, sb, res):
+        r1, r2, sc = oeng.align(a.decode(), b.decode(), True)
+        assert out["score"] == sc
+        assert out["aln_a"] == "".join(r1) and out["aln_b"] == "".join(r2)
+    sc2, ea, eb = eng.score_batch(sa, sb)                      # score-only path of the same kernel (non-local) / K1 (local)
+    assert [float(x) for x in sc2] == [o["score"] for o in res]
+    assert [int(x) for x in ea] == [o["end_a"] for o in res] and [int(x) for x in eb] == [o["end_b"] for o in res]
+    eng.close()
