@@ -26,7 +26,6 @@ struct BatchDev {                  // device-only members that do not fit the pl
     int n_k1 = 0;
     int64_t base_a = 0, base_b = 0;                          // caller offset of the first residue held on the device
     int64_t shared_la = -1;                                  // >= 0: all pairs share one `a` (database search)
-    int16_t *d_tab = nullptr;
     K1Result *h_res = nullptr; KWResult *h_kwres = nullptr; int32_t *h_err = nullptr;   // pinned staging (engine arena or own)
     bool own_stage = false;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr, ev_done = nullptr, ev_ready = nullptr;
@@ -133,7 +132,7 @@ static void batch_release(swb_engine *e, swb_batch *b)
     BatchDev *d = dev_of(b);
     if (d) {
         dev_free(e, d->codes_a); dev_free(e, d->codes_b); dev_free(e, d->off_a); dev_free(e, d->off_b); dev_free(e, d->order);
-        dev_free(e, d->err); dev_free(e, d->kw_pairs); dev_free(e, d->kw_res); dev_free(e, d->kw_bnd); dev_free(e, d->kw_scr); dev_free(e, d->d_tab);
+        dev_free(e, d->err); dev_free(e, d->kw_pairs); dev_free(e, d->kw_res); dev_free(e, d->kw_bnd); dev_free(e, d->kw_scr);
         if (d->own_stage) { cudaFreeHost(d->h_res); cudaFreeHost(d->h_kwres); cudaFreeHost(d->h_err); }
         if (d->ev0) cudaEventDestroy(d->ev0);
         if (d->ev1) cudaEventDestroy(d->ev1);
@@ -167,6 +166,27 @@ static int batch_upload_impl(swb_engine *e, const char *a_all, const int64_t *of
     const int64_t na = shared ? shared_la : (n ? off_a[n] - d->base_a : 0), nb = n ? off_b[n] - d->base_b : 0;
     if (na < 0 || nb < 0 || (na > 0 && !a_all) || (nb > 0 && !b_all)) { e->err = "bad sequence buffer / offsets"; return SWB_ERR_ARG; }
     const bool use_k1 = (e->mode == SWB_LOCAL && e->o <= e->e);
+
+    // ---- device buffers + H2D of the raw residues first (stream-ordered, no host synchronisation): the copy engine works
+    //      while the host sorts
+    const int64_t na_p = pad16(na) + 16, nb_p = pad16(nb) + 16;
+    DEV_ALLOC_ON(e, up, d->codes_a, na_p); DEV_ALLOC_ON(e, up, d->codes_b, nb_p);
+    if (!shared) DEV_ALLOC_ON(e, up, d->off_a, (n + 1) * sizeof(int64_t));
+    DEV_ALLOC_ON(e, up, d->off_b, (n + 1) * sizeof(int64_t));
+    DEV_ALLOC_ON(e, up, d->err, sizeof(int32_t));
+    CUDA_TRY(e, cudaMemsetAsync(d->err, 0, sizeof(int32_t), up));
+    CUDA_TRY(e, cudaMemsetAsync(d->codes_a + pad16(na) - (na ? 16 : 0), 0, na ? 32 : 16, up));
+    CUDA_TRY(e, cudaMemsetAsync(d->codes_b + pad16(nb) - (nb ? 16 : 0), 0, nb ? 32 : 16, up));
+    if (na) CUDA_TRY(e, cudaMemcpyAsync(d->codes_a, a_all + d->base_a, na, cudaMemcpyHostToDevice, up));
+    if (nb) CUDA_TRY(e, cudaMemcpyAsync(d->codes_b, b_all + d->base_b, nb, cudaMemcpyHostToDevice, up));
+    if (n) {
+        if (!shared) CUDA_TRY(e, cudaMemcpyAsync(d->off_a, off_a, (n + 1) * sizeof(int64_t), cudaMemcpyHostToDevice, up));
+        CUDA_TRY(e, cudaMemcpyAsync(d->off_b, off_b, (n + 1) * sizeof(int64_t), cudaMemcpyHostToDevice, up));
+    }
+    e->stats.h2d_bytes += (double)na + (double)nb + 2.0 * (n + 1) * sizeof(int64_t);
+    if (na) encode_kernel<<<(int)std::min<int64_t>((na_p / 16 + 255) / 256, e->sm_count * 8), 256, 0, up>>>(d->codes_a, na, e->d_code_tab, d->err, e->n);
+    if (nb) encode_kernel<<<(int)std::min<int64_t>((nb_p / 16 + 255) / 256, e->sm_count * 8), 256, 0, up>>>(d->codes_b, nb, e->d_code_tab, d->err, e->n);
+    CUDA_TRY(e, cudaGetLastError());
 
     // ---- shape sort (counting sort on (passes, la), longest first) and routing
     b->la.resize(n); b->lb.resize(n);
@@ -217,39 +237,29 @@ static int batch_upload_impl(swb_engine *e, const char *a_all, const int64_t *of
         b->a_bytes = (size_t)a_off; b->b_bytes = (size_t)b_off; b->la_max = la_cap;
     }
 
-    // ---- device buffers + H2D (stream-ordered, no host synchronisation)
-    const int64_t na_p = pad16(na) + 16, nb_p = pad16(nb) + 16;
-    DEV_ALLOC_ON(e, up, d->codes_a, na_p); DEV_ALLOC_ON(e, up, d->codes_b, nb_p);
-    if (!shared) DEV_ALLOC_ON(e, up, d->off_a, (n + 1) * sizeof(int64_t));
-    DEV_ALLOC_ON(e, up, d->off_b, (n + 1) * sizeof(int64_t));
-    DEV_ALLOC_ON(e, up, d->err, sizeof(int32_t));
-    DEV_ALLOC_ON(e, up, d->d_tab, 256 * sizeof(int16_t));
-    CUDA_TRY(e, cudaMemsetAsync(d->err, 0, sizeof(int32_t), up));
-    CUDA_TRY(e, cudaMemsetAsync(d->codes_a + pad16(na) - (na ? 16 : 0), 0, na ? 32 : 16, up));
-    CUDA_TRY(e, cudaMemsetAsync(d->codes_b + pad16(nb) - (nb ? 16 : 0), 0, nb ? 32 : 16, up));
-    if (na) CUDA_TRY(e, cudaMemcpyAsync(d->codes_a, a_all + d->base_a, na, cudaMemcpyHostToDevice, up));
-    if (nb) CUDA_TRY(e, cudaMemcpyAsync(d->codes_b, b_all + d->base_b, nb, cudaMemcpyHostToDevice, up));
-    if (n) {
-        if (!shared) CUDA_TRY(e, cudaMemcpyAsync(d->off_a, off_a, (n + 1) * sizeof(int64_t), cudaMemcpyHostToDevice, up));
-        CUDA_TRY(e, cudaMemcpyAsync(d->off_b, off_b, (n + 1) * sizeof(int64_t), cudaMemcpyHostToDevice, up));
-    }
-    e->stats.h2d_bytes += (double)na + (double)nb + 2.0 * (n + 1) * sizeof(int64_t);
-    CUDA_TRY(e, cudaMemcpyAsync(d->d_tab, e->code_of, 256 * sizeof(int16_t), cudaMemcpyHostToDevice, up));
-    if (na) encode_kernel<<<(int)std::min<int64_t>((na_p / 16 + 255) / 256, e->sm_count * 8), 256, 0, up>>>(d->codes_a, na, d->d_tab, d->err, e->n);
-    if (nb) encode_kernel<<<(int)std::min<int64_t>((nb_p / 16 + 255) / 256, e->sm_count * 8), 256, 0, up>>>(d->codes_b, nb, d->d_tab, d->err, e->n);
-    CUDA_TRY(e, cudaGetLastError());
-
     if (d->n_k1) {
         const int ng = (int)b->groups.size();
         DEV_ALLOC_ON(e, up, b->d_a, b->a_bytes + 32 * 16);        // one block of slack: K1 prefetches a row block ahead
         DEV_ALLOC_ON(e, up, b->d_b, b->b_bytes);
         DEV_ALLOC_ON(e, up, b->d_groups, ng * sizeof(K1Group));
         DEV_ALLOC_ON(e, up, b->d_la, d->n_k1 * sizeof(int32_t)); DEV_ALLOC_ON(e, up, b->d_lb, d->n_k1 * sizeof(int32_t));
-        DEV_ALLOC_ON(e, up, b->d_res, d->n_k1 * sizeof(K1Result));
+        DEV_ALLOC_ON(e, up, b->d_res, n * sizeof(K1Result));
+        CUDA_TRY(e, cudaMemsetAsync(b->d_res, 0, n * sizeof(K1Result), up));      // pairs K1 does not take keep flags == 0
         DEV_ALLOC_ON(e, up, b->d_counter, sizeof(int32_t));
         DEV_ALLOC_ON(e, up, d->order, d->n_k1 * sizeof(int32_t));
-        CUDA_TRY(e, cudaMemcpyAsync(b->d_groups, b->groups.data(), ng * sizeof(K1Group), cudaMemcpyHostToDevice, up));
-        CUDA_TRY(e, cudaMemcpyAsync(d->order, b->order.data(), d->n_k1 * sizeof(int32_t), cudaMemcpyHostToDevice, up));
+        b->d_order = d->order;
+        // the work-item table and the order go through pinned staging when the arena has room: an asynchronous copy from
+        // pageable memory makes the host wait for the residue copies queued before it
+        const void *src_g = b->groups.data(), *src_o = b->order.data();
+        if (use_arena) {
+            void *pg = stage_alloc(e, ng * sizeof(K1Group)), *po = stage_alloc(e, d->n_k1 * sizeof(int32_t));
+            if (pg && po) {
+                memcpy(pg, src_g, ng * sizeof(K1Group)); memcpy(po, src_o, d->n_k1 * sizeof(int32_t));
+                src_g = pg; src_o = po;
+            }
+        }
+        CUDA_TRY(e, cudaMemcpyAsync(b->d_groups, src_g, ng * sizeof(K1Group), cudaMemcpyHostToDevice, up));
+        CUDA_TRY(e, cudaMemcpyAsync(d->order, src_o, d->n_k1 * sizeof(int32_t), cudaMemcpyHostToDevice, up));
         e->stats.h2d_bytes += (double)ng * sizeof(K1Group) + (double)d->n_k1 * sizeof(int32_t);
         k1_pack_kernel<<<ng, 128, 0, up>>>(d->codes_a, d->codes_b, d->off_a, d->off_b, d->order, b->d_groups,
                                                   b->d_a, b->d_b, b->d_la, b->d_lb, e->n, d->base_a, d->base_b, (int)shared_la);
@@ -285,14 +295,14 @@ static int batch_upload_impl(swb_engine *e, const char *a_all, const int64_t *of
     CUDA_TRY(e, cudaEventCreateWithFlags(&d->ev_done, cudaEventDisableTiming));
     // ---- pinned staging for the results
     if (use_arena) {
-        d->h_res = (K1Result *)stage_alloc(e, (size_t)std::max(1, d->n_k1) * sizeof(K1Result));
+        d->h_res = (K1Result *)stage_alloc(e, (size_t)std::max<int64_t>(1, n) * sizeof(K1Result));
         d->h_kwres = (KWResult *)stage_alloc(e, (size_t)std::max(1, d->n_kw) * sizeof(KWResult));
         d->h_err = (int32_t *)stage_alloc(e, sizeof(int32_t));
     }
     if (!d->h_res || !d->h_kwres || !d->h_err) {
         d->h_res = nullptr; d->h_kwres = nullptr; d->h_err = nullptr;
         d->own_stage = true;
-        CUDA_TRY(e, cudaMallocHost((void **)&d->h_res, (size_t)std::max(1, d->n_k1) * sizeof(K1Result)));
+        CUDA_TRY(e, cudaMallocHost((void **)&d->h_res, (size_t)std::max<int64_t>(1, n) * sizeof(K1Result)));
         CUDA_TRY(e, cudaMallocHost((void **)&d->h_kwres, (size_t)std::max(1, d->n_kw) * sizeof(KWResult)));
         CUDA_TRY(e, cudaMallocHost((void **)&d->h_err, sizeof(int32_t)));
     }
@@ -388,10 +398,10 @@ extern "C" int swb_batch_run_n(swb_engine *e, swb_batch *b, int steps, float *to
 static int batch_fetch_enqueue(swb_engine *e, swb_batch *b)
 {
     BatchDev *d = b->dev;
-    if (d->n_k1) CUDA_TRY(e, cudaMemcpyAsync(d->h_res, b->d_res, d->n_k1 * sizeof(K1Result), cudaMemcpyDeviceToHost, e->stream));
+    if (d->n_k1) CUDA_TRY(e, cudaMemcpyAsync(d->h_res, b->d_res, b->n * sizeof(K1Result), cudaMemcpyDeviceToHost, e->stream));
     if (d->n_kw) CUDA_TRY(e, cudaMemcpyAsync(d->h_kwres, d->kw_res, d->n_kw * sizeof(KWResult), cudaMemcpyDeviceToHost, e->stream));
     CUDA_TRY(e, cudaEventRecord(d->ev_done, e->stream));
-    e->stats.d2h_bytes += (double)d->n_k1 * sizeof(K1Result) + (double)d->n_kw * sizeof(KWResult);
+    e->stats.d2h_bytes += (d->n_k1 ? (double)b->n * sizeof(K1Result) : 0.0) + (double)d->n_kw * sizeof(KWResult);
     return SWB_OK;
 }
 
@@ -409,11 +419,13 @@ static int batch_fetch_finish(swb_engine *e, swb_batch *b, float *scores, int64_
     const bool dyadic = (e->scale & (e->scale - 1)) == 0;
     auto to_f = [&](int32_t s) { return dyadic ? (float)s * inv : (float)((double)s / e->scale); };
     std::vector<int32_t> redo;                       // pairs whose s16 lanes overflowed
-    for (int pos = 0; pos < d->n_k1; ++pos) {
-        const K1Result &r = d->h_res[pos];
-        const int32_t k = b->order[pos];
-        if (r.flags & 1) { redo.push_back(k); continue; }
-        scores[k] = to_f(r.score); end_a[k] = r.end_i; end_b[k] = r.end_j;
+    if (d->n_k1) {
+        const K1Result *hr = d->h_res;                 // caller order (K1 scatters); non-K1 entries are zero and overwritten below
+        for (int64_t k = 0; k < b->n; ++k) {
+            const K1Result r = hr[k];
+            if (r.flags & 1) { redo.push_back((int32_t)k); continue; }
+            scores[k] = to_f(r.score); end_a[k] = r.end_i; end_b[k] = r.end_j;
+        }
     }
     for (int t = 0; t < d->n_kw; ++t) {
         const int32_t k = d->kw_idx[t];
@@ -473,7 +485,8 @@ extern "C" int swb_batch_fetch(swb_engine *e, swb_batch *b, float *scores, int64
 // Host buffers in, host buffers out.  The pair list is cut into chunks that flow through a two-stream software
 // pipeline: the copy stream uploads, encodes and packs chunk c+1 while the compute stream aligns chunk c and the host
 // sorts chunk c+2 / scatters the results of chunk c-1 (with pinned caller memory the copies are truly asynchronous).
-#define SCORE_CHUNK_PAIRS 262144
+#define SCORE_CHUNK_PAIRS 393216
+#define SCORE_CHUNK_FIRST 131072
 
 static int score_pipeline(swb_engine *e, const char *a_all, const int64_t *off_a, int64_t shared_la, const char *b_all,
                           const int64_t *off_b, int64_t n, float *scores, int64_t *end_a, int64_t *end_b)
@@ -482,13 +495,26 @@ static int score_pipeline(swb_engine *e, const char *a_all, const int64_t *off_a
     CUDA_TRY(e, cudaSetDevice(e->device));
     e->stats.cells = 0; e->stats.h2d_bytes = 0; e->stats.d2h_bytes = 0; e->stats.i32_reruns = 0; e->stats.launches = 0;
     // results arena: 16 B per pair + slack per chunk
-    // equal chunks of >= 3.5 K1 waves: smaller launches leave the GPU waiting for their longest work item
-    // (measured: graded 64k/128k/256k chunks were 8 % slower end to end than 4 x 256k)
+    // chunking pays only while the copy is a visible fraction of the work: a long shared query (database search) makes the
+    // upload negligible next to the DP, and every extra launch adds the tail of its own longest work item
+    int64_t chunk_pairs = SCORE_CHUNK_PAIRS;
+    if (n > 0) {
+        const double nb_tot = (double)(off_b[n] - off_b[0]), na_tot = shared_la >= 0 ? (double)shared_la : (double)(off_a[n] - off_a[0]);
+        const double est_cells = shared_la >= 0 ? na_tot * nb_tot : (na_tot / n) * (nb_tot / n) * n;
+        const double copy_ms = (na_tot + nb_tot) / 50e6, dp_ms = est_cells / 4e9;
+        if (copy_ms < 0.05 * dp_ms) chunk_pairs = n;
+    }
+    // graded chunks: a small first chunk gets K1 going after ~1 ms of copy; each following chunk is as much larger as the
+    // copy engine is faster than K1 (x1.8 on configs[1]), so its upload hides behind the previous chunk's DP
     std::vector<int64_t> cuts(1, 0);
-    while (cuts.back() < n) cuts.push_back(std::min<int64_t>(n, cuts.back() + SCORE_CHUNK_PAIRS));
+    for (int64_t sz = (chunk_pairs == n) ? n : SCORE_CHUNK_FIRST; cuts.back() < n; sz = std::min<int64_t>(chunk_pairs, sz * 9 / 5)) {
+        int64_t next = std::min<int64_t>(n, cuts.back() + sz);
+        if (n - next < SCORE_CHUNK_FIRST) next = n;          // no crumbs at the end
+        cuts.push_back(next);
+    }
     if (cuts.size() == 1) cuts.push_back(0);
     const int64_t n_chunks = (int64_t)cuts.size() - 1;
-    const size_t need = (size_t)n * (sizeof(K1Result) + sizeof(KWResult)) + (size_t)n_chunks * 4096;
+    const size_t need = (size_t)n * (sizeof(K1Result) + sizeof(KWResult) + sizeof(int32_t) + 2) + (size_t)n_chunks * 8192;
     if (need > e->stage_bytes) {
         CUDA_TRY(e, cudaStreamSynchronize(e->stream));
         if (e->h_stage) cudaFreeHost(e->h_stage);
@@ -498,37 +524,47 @@ static int score_pipeline(swb_engine *e, const char *a_all, const int64_t *off_a
     }
     e->stage_used = 0;
     int rc = SWB_OK;
-    swb_batch *prev = nullptr; int64_t prev_start = 0;
+    std::vector<swb_batch *> live((size_t)n_chunks, nullptr);   // chunks in flight; finished in order as their results land
+    int64_t next_finish = 0;
     const bool trace = getenv("SWB_TRACE") != nullptr;       // host-side phase times of the pipeline, to stderr
     auto now = [] { return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now().time_since_epoch()).count(); };
     double t_up = 0, t_launch = 0, t_fin = 0, t_rel = 0; const double t_begin = now();
     CUDA_TRY(e, cudaEventRecord(e->ev0, e->stream));
+    std::vector<cudaEvent_t> tev;                             // trace only: per chunk {upload begin, packed, K1 done}
+    auto mark = [&](cudaStream_t st) { if (trace) { cudaEvent_t ev; cudaEventCreate(&ev); cudaEventRecord(ev, st); tev.push_back(ev); } };
+    if (trace) CUDA_TRY(e, cudaStreamWaitEvent(e->stream_up, e->ev0, 0));
     for (int64_t c = 0; c < n_chunks && rc == SWB_OK; ++c) {
         const int64_t start = cuts[c], cnt = cuts[c + 1] - cuts[c];
         swb_batch *cur = nullptr;
         double t0 = now();
+        mark(e->stream_up);
         rc = batch_upload_impl(e, a_all, shared_la >= 0 ? nullptr : off_a + start, b_all, off_b + start, cnt, shared_la, true,
                                e->stream_up, &cur);
         double t1 = now(); t_up += t1 - t0;
+        mark(e->stream_up);
         int64_t launches = 0;
         if (rc == SWB_OK) rc = batch_launch(e, cur, &launches);
+        mark(e->stream);
         if (rc == SWB_OK) rc = batch_fetch_enqueue(e, cur);
         e->stats.launches += launches;
         double t2 = now(); t_launch += t2 - t1;
-        if (prev) {                                   // scatter the previous chunk while this one runs
-            int rc2 = batch_fetch_finish(e, prev, scores + prev_start, end_a + prev_start, end_b + prev_start);
-            double t3 = now(); t_fin += t3 - t2;
-            batch_release(e, prev);
-            t_rel += now() - t3;
-            prev = nullptr;
-            if (rc == SWB_OK) rc = rc2;
+        live[c] = cur;
+        // scatter the chunks whose results have already landed; never block here: the next chunk's sort and upload come first
+        while (rc == SWB_OK && next_finish < c && cudaEventQuery(live[next_finish]->dev->ev_done) == cudaSuccess) {
+            double t3 = now();
+            rc = batch_fetch_finish(e, live[next_finish], scores + cuts[next_finish], end_a + cuts[next_finish], end_b + cuts[next_finish]);
+            double t4 = now(); t_fin += t4 - t3;
+            batch_release(e, live[next_finish]); live[next_finish] = nullptr;
+            t_rel += now() - t4;
+            ++next_finish;
         }
-        prev = cur; prev_start = start;
     }
-    if (prev) {
-        int rc2 = (rc == SWB_OK) ? batch_fetch_finish(e, prev, scores + prev_start, end_a + prev_start, end_b + prev_start) : rc;
-        batch_release(e, prev);
-        if (rc == SWB_OK) rc = rc2;
+    for (int64_t c = next_finish; c < n_chunks; ++c) {
+        if (!live[c]) continue;
+        double t3 = now();
+        if (rc == SWB_OK) rc = batch_fetch_finish(e, live[c], scores + cuts[c], end_a + cuts[c], end_b + cuts[c]);
+        t_fin += now() - t3;
+        batch_release(e, live[c]); live[c] = nullptr;
     }
     if (rc == SWB_OK) {
         CUDA_TRY(e, cudaEventRecord(e->ev1, e->stream));
@@ -537,6 +573,12 @@ static int score_pipeline(swb_engine *e, const char *a_all, const int64_t *off_a
         e->stats.kernel_ms = ms;                      // device time of the whole pipelined call
         if (trace) fprintf(stderr, "[swb] score_batch n=%lld chunks=%lld total %.2f ms: upload(host) %.2f launch %.2f finish(wait+scatter) %.2f release %.2f device-span %.2f\n",
                            (long long)n, (long long)n_chunks, now() - t_begin, t_up, t_launch, t_fin, t_rel, ms);
+        for (size_t k = 0; k + 2 < tev.size() + 0 && trace; k += 3) {
+            float a = 0, b2 = 0, c2 = 0;
+            cudaEventElapsedTime(&a, e->ev0, tev[k]); cudaEventElapsedTime(&b2, e->ev0, tev[k + 1]); cudaEventElapsedTime(&c2, e->ev0, tev[k + 2]);
+            fprintf(stderr, "[swb]   chunk %zu: upload begins %.2f  packed %.2f  K1 done %.2f ms\n", k / 3, a, b2, c2);
+        }
+        for (cudaEvent_t ev : tev) cudaEventDestroy(ev);
     }
     return rc;
 }

@@ -144,7 +144,9 @@ extern "C" int swb_engine_create(const swb_matrix *m, float gap_open, float gap_
         (ce = cudaStreamCreateWithFlags(&e->stream_up, cudaStreamNonBlocking)) != cudaSuccess ||
         (ce = cudaEventCreate(&e->ev0)) != cudaSuccess || (ce = cudaEventCreate(&e->ev1)) != cudaSuccess ||
         (ce = cudaMalloc(&e->d_mat, tab.size() * sizeof(int32_t))) != cudaSuccess ||
-        (ce = cudaMemcpy(e->d_mat, tab.data(), tab.size() * sizeof(int32_t), cudaMemcpyHostToDevice)) != cudaSuccess) {
+        (ce = cudaMemcpy(e->d_mat, tab.data(), tab.size() * sizeof(int32_t), cudaMemcpyHostToDevice)) != cudaSuccess ||
+        (ce = cudaMalloc(&e->d_code_tab, 256 * sizeof(int16_t))) != cudaSuccess ||
+        (ce = cudaMemcpy(e->d_code_tab, e->code_of, 256 * sizeof(int16_t), cudaMemcpyHostToDevice)) != cudaSuccess) {
         g_create_err = std::string("CUDA init: ") + cudaGetErrorString(ce);
         swb_engine_destroy(e);
         return SWB_ERR_CUDA;
@@ -166,6 +168,7 @@ extern "C" void swb_engine_destroy(swb_engine *e)
     if (!e) return;
     cudaSetDevice(e->device);
     if (e->d_mat) cudaFree(e->d_mat);
+    if (e->d_code_tab) cudaFree(e->d_code_tab);
     if (e->d_bnd) cudaFree(e->d_bnd);
     if (e->h_stage) cudaFreeHost(e->h_stage);
     if (e->ev0) cudaEventDestroy(e->ev0);

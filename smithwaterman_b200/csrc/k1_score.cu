@@ -62,7 +62,8 @@ __global__ void __launch_bounds__(K1_THREADS * 2, 1)
 k1_local_kernel(const uint8_t *__restrict__ a_pk, const uint8_t *__restrict__ b_pk,
                 const K1Group *__restrict__ groups, int n_groups, const int32_t *__restrict__ la_arr,
                 const int32_t *__restrict__ lb_arr, const int32_t *__restrict__ mat, int nl, int open, int ext,
-                int limit_ho, uint4 *__restrict__ bnd, int bnd_blocks, int *counter, K1Result *__restrict__ res)
+                int limit_ho, uint4 *__restrict__ bnd, int bnd_blocks, int *counter, const int32_t *__restrict__ order,
+                K1Result *__restrict__ res)
 {
     extern __shared__ unsigned T_sh[];               // [nl*nl][32 lanes]: (s - open) & 0xFFFF
     for (int idx = threadIdx.x; idx < nl * nl * 32; idx += blockDim.x)
@@ -187,7 +188,7 @@ k1_local_kernel(const uint8_t *__restrict__ a_pk, const uint8_t *__restrict__ b_
             r.end_i = (bestHo > open) ? bi : -1;
             r.end_j = (bestHo > open) ? bj : -1;
             r.flags = ovf;
-            res[p] = r;
+            res[order[p]] = r;                      // scatter to the caller's order: the host pass over the results is linear
         }
     }
 }
@@ -211,6 +212,6 @@ cudaError_t k1_launch(const swb_engine *e, const swb_batch *b, int n_blocks, cud
     const int limit_ho = 32767 - 2 * e->smax + e->o - 1;
     k1_local_kernel<<<n_blocks, K1_THREADS * 2, smem, st>>>(
         b->d_a, b->d_b, b->d_groups, (int)b->groups.size(), b->d_la, b->d_lb, e->d_mat, nl, e->o, e->e, limit_ho,
-        reinterpret_cast<uint4 *>(e->d_bnd), k1_bnd_blocks(b->la_max), b->d_counter, b->d_res);
+        reinterpret_cast<uint4 *>(e->d_bnd), k1_bnd_blocks(b->la_max), b->d_counter, b->d_order, b->d_res);
     return cudaGetLastError();
 }

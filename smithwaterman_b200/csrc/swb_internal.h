@@ -25,7 +25,7 @@ struct K1Group {                    // one warp-sized work item: 32 pairs of sim
     int32_t n_pairs;                // 1..32
 };
 
-struct K1Result {                   // per pair (sorted order)
+struct K1Result {                   // per pair (caller order)
     int32_t score;                  // scaled integer score
     int32_t end_i, end_j;           // 1-based first-maximum cell, -1,-1 if score == 0
     int32_t flags;                  // bit0: s16 range exceeded -> re-run in int32
@@ -48,6 +48,7 @@ struct swb_engine {
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     int sm_count = 0;
     int32_t *d_mat = nullptr;       // (n+1)*(n+1) int32 scaled, PAD row/col included
+    int16_t *d_code_tab = nullptr;  // byte -> residue code (device copy of code_of)
     // scratch owned by the engine, grown on demand
     void *d_bnd = nullptr; size_t bnd_bytes = 0;
     void *h_stage = nullptr; size_t stage_bytes = 0, stage_used = 0;   // pinned results arena of swb_score_batch
@@ -66,7 +67,8 @@ struct swb_batch {
     uint8_t *d_a = nullptr, *d_b = nullptr;
     K1Group *d_groups = nullptr;
     int32_t *d_la = nullptr, *d_lb = nullptr;   // sorted order
-    K1Result *d_res = nullptr;
+    K1Result *d_res = nullptr;                  // indexed by the caller's pair index within the batch (K1 scatters)
+    const int32_t *d_order = nullptr;           // sorted position -> caller index (device copy)
     int32_t *d_counter = nullptr;
     size_t a_bytes = 0, b_bytes = 0;
     int32_t la_max = 0;
