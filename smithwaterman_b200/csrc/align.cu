@@ -122,7 +122,7 @@ extern "C" int swb_align_batch(swb_engine *e, const char *a_all, const int64_t *
         while (end < work.size()) {
             const int64_t k = work[end];
             const int32_t la = (int32_t)(off_a[k + 1] - off_a[k]), lb = (int32_t)(off_b[k + 1] - off_b[k]);
-            const int64_t db = kw_dir_bytes(la, lb);
+            const int64_t db = kw_dir_bytes(la, lb, 8);              // upper bound over both strip widths
             if (!hp.empty() && dir_total + db > DIR_BUDGET_BYTES) break;
             KWPair P; P.a_off = off_a[k]; P.b_off = off_b[k]; P.la = la; P.lb = lb; P.dir_off = dir_total; P.bnd_off = 0; P.scr_off = 0;
             hp.push_back(P); out_off.push_back(out_total);
@@ -130,7 +130,8 @@ extern "C" int swb_align_batch(swb_engine *e, const char *a_all, const int64_t *
             ++end;
         }
         const int np = (int)hp.size();
-        KWPlan plan; kw_plan(e, hp.data(), np, &plan);
+        KWPlan plan; kw_plan(e, hp.data(), np, true, &plan);       // assigns the direction-byte offsets
+        dir_total = plan.dir_bytes;
         DevBuf d_pairs, d_res, d_dir, d_bnd, d_scr, d_off, d_xa, d_xb, d_nc;
         CUDA_TRY(e, cudaMalloc(&d_pairs.p, np * sizeof(KWPair))); CUDA_TRY(e, cudaMalloc(&d_res.p, np * sizeof(KWResult)));
         CUDA_TRY(e, cudaMalloc(&d_dir.p, dir_total + 16)); CUDA_TRY(e, cudaMalloc(&d_bnd.p, plan.bnd_elems * sizeof(int4)));
@@ -143,7 +144,7 @@ extern "C" int swb_align_batch(swb_engine *e, const char *a_all, const int64_t *
         CUDA_TRY(e, cudaEventRecord(e->ev0, e->stream));
         CUDA_TRY(e, kw_launch(e, d_a.as<uint8_t>(), d_b.as<uint8_t>(), d_pairs.as<KWPair>(), np, plan, d_dir.as<uint8_t>(),
                               d_bnd.as<int4>(), d_scr.as<int>(), d_res.as<KWResult>(), e->stream));
-        CUDA_TRY(e, kt_launch(e, d_pairs.as<KWPair>(), d_res.as<KWResult>(), np, d_dir.as<uint8_t>(), d_off.as<int64_t>(),
+        CUDA_TRY(e, kt_launch(e, d_pairs.as<KWPair>(), d_res.as<KWResult>(), np, d_dir.as<uint8_t>(), plan.cols, d_off.as<int64_t>(),
                               d_xa.as<int32_t>(), d_xb.as<int32_t>(), d_nc.as<int32_t>(), e->stream));
         CUDA_TRY(e, cudaEventRecord(e->ev1, e->stream));
         std::vector<KWResult> hr(np); std::vector<int32_t> hnc(np), hxa(out_total), hxb(out_total);

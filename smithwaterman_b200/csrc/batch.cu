@@ -283,7 +283,7 @@ static int batch_upload_impl(swb_engine *e, const char *a_all, const int64_t *of
             P.a_off = shared ? 0 : off_a[k] - d->base_a; P.b_off = off_b[k] - d->base_b; P.la = b->la[k]; P.lb = b->lb[k];
             P.dir_off = -1;
         }
-        kw_plan(e, d->h_kw.data(), d->n_kw, &d->kw_plan_);
+        kw_plan(e, d->h_kw.data(), d->n_kw, false, &d->kw_plan_);
         DEV_ALLOC_ON(e, up, d->kw_pairs, d->n_kw * sizeof(KWPair));
         DEV_ALLOC_ON(e, up, d->kw_res, d->n_kw * sizeof(KWResult));
         DEV_ALLOC_ON(e, up, d->kw_bnd, d->kw_plan_.bnd_elems * sizeof(int4));
@@ -452,7 +452,7 @@ static int batch_fetch_finish(swb_engine *e, swb_batch *b, float *scores, int64_
             hp[t].a_off = d->shared_la >= 0 ? 0 : oa[k] - d->base_a; hp[t].b_off = ob[k] - d->base_b; hp[t].la = b->la[k]; hp[t].lb = b->lb[k];
             hp[t].dir_off = -1;
         }
-        KWPlan pl; kw_plan(e, hp.data(), nr, &pl);
+        KWPlan pl; kw_plan(e, hp.data(), nr, false, &pl);
         KWPair *dp = nullptr; KWResult *dr = nullptr; int4 *db = nullptr; int *ds = nullptr;
         DEV_ALLOC(e, dp, nr * sizeof(KWPair)); DEV_ALLOC(e, dr, nr * sizeof(KWResult)); DEV_ALLOC(e, db, pl.bnd_elems * sizeof(int4));
         DEV_ALLOC(e, ds, pl.scratch_ints * sizeof(int));

@@ -19,45 +19,47 @@
 // strip.  Direction bytes (three 2-bit predecessor codes; code 3 = "local score is 0, stop here",
 // SA.rs:354-357) are stored step-major: the warp writes 32*KW_C contiguous bytes per step.
 #include <algorithm>
+#include <cstdlib>
 
 #include "swb_internal.h"
 
-#define KW_C 8
-#define KW_SW (32 * KW_C)
 #define KW_WARPS 8
 #define NEG_INF_I32 (-(1 << 29))
 
-int64_t kw_dir_bytes(int32_t la, int32_t lb)
+int64_t kw_dir_bytes(int32_t la, int32_t lb, int cols)
 {
-    int64_t strips = (lb + KW_SW - 1) / KW_SW;
-    return strips * (int64_t)(la + 31) * KW_SW;
+    const int sw = 32 * cols;
+    int64_t strips = (lb + sw - 1) / sw;
+    return strips * (int64_t)(la + 31) * sw;
 }
 
+// Priority argmax of a cell's three states, M > X > Y (the MATCH predecessor rule, SA.rs:139-158).
+// (Decisions compare the candidates with each other, never a maximum with its own operands: nvcc 12.9 folds
+// `x = max(a, b); x == b` into the predicate outputs of VIMNMX[.RELU], which report the selected operand, not equality,
+// and the tie cases then come out wrong.)
+__device__ __forceinline__ unsigned kw_am(int m, int x, int y) { return (m >= x && m >= y) ? 0u : ((x >= y) ? 1u : 2u); }
+
+// One cell, branch-free.  hd / amd: max and priority argmax of the diagonal cell's states; (tM,tX,tY) the left cell,
+// (lM,lX,lY) the upper cell.  The predecessor of a gap state is read off the maximum by equality tests in priority
+// order, which is the same decision as the reference's nested comparisons on the sums (SA.rs:164-252).
 template <int MODE>
-__device__ __forceinline__ void kw_cell(int dM, int dX, int dY, int tM, int tX, int tY, int lM, int lX, int lY, int s,
+__device__ __forceinline__ void kw_cell(int hd, unsigned amd, int tM, int tX, int tY, int lM, int lX, int lY, int s,
                                         int po, int pe, int qo, int qe, int &m, int &x, int &y, unsigned &code)
 {
-    int pm, px, py;
-    if (dM >= dX) { if (dM >= dY) { m = dM; pm = 0; } else { m = dY; pm = 2; } }
-    else          { if (dX >= dY) { m = dX; pm = 1; } else { m = dY; pm = 2; } }
-    m += s;
     const int a = tM + po, b = tX + pe, c = tY + po;
     const int f = lM + qo, g = lY + qe, h = lX + qo;
+    unsigned pm = amd, px, py;
+    m = hd + s;
     if (MODE != SWB_LOCAL) {
-        if (a > b) { if (a >= c) { x = a; px = 0; } else { x = c; px = 2; } }
-        else       { if (b >= c) { x = b; px = 1; } else { x = c; px = 2; } }
-        if (f > g) { if (f >= h) { y = f; py = 0; } else { y = h; py = 1; } }
-        else       { if (g >= h) { y = g; py = 2; } else { y = h; py = 1; } }
+        x = __vimax3_s32(a, b, c); px = (b >= a && b >= c) ? 4u : ((a >= c) ? 0u : 8u);    // X > M > Y  (SA.rs:172-189)
+        y = __vimax3_s32(f, g, h); py = (g >= f && g >= h) ? 32u : ((f >= h) ? 0u : 16u);  // Y > M > X  (SA.rs:192-211)
     } else {
-        if (a >= b) { if (a > c) { x = a; px = 0; } else { x = c; px = 2; } }
-        else        { if (b > c) { x = b; px = 1; } else { x = c; px = 2; } }
-        if (f >= g) { if (f > h) { y = f; py = 0; } else { y = h; py = 1; } }
-        else        { if (g > h) { y = g; py = 2; } else { y = h; py = 1; } }
-        if (m <= 0) { m = 0; pm = 3; }
-        if (x <= 0) { x = 0; px = 3; }
-        if (y <= 0) { y = 0; py = 3; }
+        x = __vimax3_s32_relu(a, b, c); px = (c >= a && c >= b) ? 8u : ((a >= b) ? 0u : 4u);   // Y > M > X  (SA.rs:214-231)
+        y = __vimax3_s32_relu(f, g, h); py = (h >= f && h >= g) ? 16u : ((f >= g) ? 0u : 32u); // X > M > Y  (SA.rs:233-252)
+        m = max(m, 0);                                                               // clamp after the choice (SA.rs:256-260)
+        pm = (m <= 0) ? 3u : pm; px = (x <= 0) ? 12u : px; py = (y <= 0) ? 48u : py; // code 3: "score is 0", the walk's stop test
     }
-    code = (unsigned)pm | ((unsigned)px << 2) | ((unsigned)py << 4);
+    code = pm + px + py;
 }
 
 // Team scheduling: a pair is swept by a TEAM of T warps (T = 1 for batches of many pairs; up to several hundred for a
@@ -65,19 +67,33 @@ __device__ __forceinline__ void kw_cell(int dM, int dX, int dY, int tM, int tX, 
 // strip s-1 row by row through a ring of T+1 column buffers in global memory (L2 resident) guarded by a per-strip
 // progress counter (rows published, release/acquire through __threadfence + volatile accesses).  Waits only ever point
 // to a lower strip, so there is no cycle; the launcher sizes the grid so that every warp of every team is resident.
+// C = columns per lane (strip width 32*C): 8 for batches (fewest instructions per cell), 2 when a few long pairs must be
+// spread over many warps (the per-step dependency chain, not the issue rate, bounds a lone warp).
 __device__ __forceinline__ int ld_volatile(const int *p) { return *reinterpret_cast<const volatile int *>(p); }
 
-template <int MODE, bool DIRS>
+template <int C> struct KWCodes;
+template <> struct KWCodes<8> { typedef unsigned long long T; };
+template <> struct KWCodes<4> { typedef unsigned T; };
+template <> struct KWCodes<2> { typedef unsigned short T; };
+
+template <int MODE, bool DIRS, int C>
 __global__ void __launch_bounds__(KW_WARPS * 32)
 kw_kernel(const uint8_t *__restrict__ a_all, const uint8_t *__restrict__ b_all, const KWPair *__restrict__ pairs,
           int n_pairs, int team_warps, int n_teams, const int32_t *__restrict__ mat, int nl, int o, int e, int unit,
           uint8_t *__restrict__ dir, int4 *__restrict__ bnd, int *__restrict__ scratch, KWResult *__restrict__ res)
 {
+    constexpr int SW = 32 * C;
+    typedef typename KWCodes<C>::T codes_t;
     extern __shared__ int mat_sh[];
-    for (int k = threadIdx.x; k < nl * nl; k += blockDim.x) mat_sh[k] = mat[k];
+    __shared__ int4 bnd_sh[KW_WARPS][32];
+    __shared__ uint8_t a_sh[KW_WARPS][64];
+    // local mode: PAD row/column scores are made so negative that a padded column's MATCH is always clamped to 0 and can
+    // never become a strict maximum (the int32 lanes have the room; K1's s16 table keeps the small PAD of the engine)
+    for (int k = threadIdx.x; k < nl * nl; k += blockDim.x)
+        mat_sh[k] = (MODE == SWB_LOCAL && (k % nl == nl - 1 || k / nl == nl - 1)) ? NEG_INF_I32 : mat[k];
     __syncthreads();
-    const int lane = threadIdx.x & 31;
-    const int gw = blockIdx.x * KW_WARPS + (threadIdx.x >> 5);
+    const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
+    const int gw = blockIdx.x * KW_WARPS + wib;
     const int team = gw / team_warps, w = gw - team * team_warps;
     if (team >= n_teams) return;
     const int so = (MODE == SWB_GLOBAL) ? o : 0, se = (MODE == SWB_GLOBAL) ? e : 0;
@@ -87,7 +103,7 @@ kw_kernel(const uint8_t *__restrict__ a_all, const uint8_t *__restrict__ b_all, 
         const KWPair P = pairs[pidx];
         const uint8_t *a = a_all + P.a_off, *b = b_all + P.b_off;
         const int la = P.la, lb = P.lb;
-        const int n_strips = (lb + KW_SW - 1) / KW_SW;
+        const int n_strips = (lb + SW - 1) / SW;
         const int nbuf = min(n_strips, team_warps + 1);
         int *counter = scratch + P.scr_off;                    // [0] arrivals, [1..n_strips] rows published per strip,
         int *prog = counter + 1;                               // then 4 ints per team warp (local-mode candidates)
@@ -97,32 +113,46 @@ kw_kernel(const uint8_t *__restrict__ a_all, const uint8_t *__restrict__ b_all, 
         bool have_fin = false;
 
         for (int sidx = w; sidx < n_strips; sidx += team_warps) {
-            const int j0 = sidx * KW_SW + lane * KW_C;         // 0-based first column of this lane; DP column = j0+c+1
+            const int j0 = sidx * SW + lane * C;               // 0-based first column of this lane; DP column = j0+c+1
             int4 *bnd_out = bnd + P.bnd_off + (int64_t)(sidx % nbuf) * (la + 2);
             const int4 *bnd_in = bnd + P.bnd_off + (int64_t)((sidx + nbuf - 1) % nbuf) * (la + 2);
             const bool wait_prev = (team_warps > 1 && sidx > 0);
-            int Mu[KW_C], Xu[KW_C], Yu[KW_C], brow[KW_C];
+            // per column: the three states of the cell above, their max / priority argmax (the next row's diagonal),
+            // the column's offset into the score table
+            int Mu[C], Xu[C], Yu[C], Hu[C], boff[C];
+            unsigned Au[C];
 #pragma unroll
-            for (int c = 0; c < KW_C; ++c) {
+            for (int c = 0; c < C; ++c) {
                 const int j = j0 + c + 1;
-                const int ls = j * se + (so - se);             // SA.rs:100-104
+                const int ls = j * se + (so - se);             // SA.rs:100-104: X = ls, M = Y = ls + sentinel, prev = GAPINX
                 Mu[c] = ls + sent; Xu[c] = ls; Yu[c] = ls + sent;
-                brow[c] = (j <= lb) ? (int)b[j - 1] : (nl - 1);
+                Hu[c] = __vimax3_s32(Mu[c], Xu[c], Yu[c]); Au[c] = kw_am(Mu[c], Xu[c], Yu[c]);
+                boff[c] = (j <= lb) ? (int)b[j - 1] : (nl - 1);
             }
-            int dM0, dX0, dY0;                                 // diag of column j0 at row 0: cell (0, j0)
-            if (j0 == 0) { dM0 = 0; dX0 = -unit; dY0 = -unit; }            // SA.rs:88-93
-            else { const int ls = j0 * se + (so - se); dM0 = ls + sent; dX0 = ls; dY0 = ls + sent; }
+            int hd0; unsigned ad0;                             // diagonal of column 0 at the next row: cell (row-1, j0)
+            if (j0 == 0) { hd0 = 0; ad0 = 0u; }                // (0,0): M = 0, X = Y = -1 (SA.rs:88-93)
+            else { const int ls = j0 * se + (so - se); hd0 = __vimax3_s32(ls + sent, ls, ls + sent); ad0 = kw_am(ls + sent, ls, ls + sent); }
             int lastM = 0, lastX = 0, lastY = 0;               // this lane's last column, row of the previous step
-            uint8_t *dstrip = DIRS ? dir + P.dir_off + (int64_t)sidx * (la + 31) * KW_SW + lane * KW_C : nullptr;
+            uint8_t *dstrip = DIRS ? dir + P.dir_off + (int64_t)sidx * (la + 31) * SW + lane * C : nullptr;
+            int sb = 0, si = -1, sj = -1;                      // local: this strip's first strict maximum in this lane
+            const int own = lb - 1 - j0;                       // register index of column lb when it is in this lane
 
             const int n_steps = la + 31;
             for (int t = 0; t < n_steps; ++t) {
-                if (wait_prev && (t & 31) == 0 && t < la) {    // rows t+1 .. t+32 are consumed by lane 0 in the next 32 steps
-                    const int need = min(la, t + 32);
-                    if (lane == 0) {
-                        while (ld_volatile(prog + sidx - 1) < need) __nanosleep(32);
-                        __threadfence();
+                if ((t & 31) == 0) {
+                    // Once per 32 steps the warp stages what the next 32 steps consume, so that no global-memory latency
+                    // sits on the per-step critical path: the 32 rows of the previous strip's last column that lane 0 will
+                    // read (one coalesced 512-byte load) and the next 32 residues of `a` (ring of 64: lane l reads index t-l).
+                    if (wait_prev && t < la) {                 // rows t+1 .. t+32 are consumed by lane 0 in the next 32 steps
+                        const int need = min(la, t + 32);
+                        if (lane == 0) {
+                            while (ld_volatile(prog + sidx - 1) < need) __nanosleep(32);
+                            __threadfence();
+                        }
                     }
+                    __syncwarp();
+                    if (sidx > 0 && t + 1 + lane <= la) bnd_sh[wib][lane] = __ldcg(bnd_in + t + 1 + lane);
+                    a_sh[wib][(t + lane) & 63] = (t + lane < la) ? a[t + lane] : (uint8_t)(nl - 1);
                     __syncwarp();
                 }
                 const int i = t - lane + 1;                    // DP row of this lane in this step
@@ -132,39 +162,42 @@ kw_kernel(const uint8_t *__restrict__ a_all, const uint8_t *__restrict__ b_all, 
                 const bool active = (i >= 1 && i <= la);
                 if (lane == 0 && active) {
                     if (sidx == 0) { const int ls = i * se + (so - se); tM = ls + sent; tX = ls + sent; tY = ls; }   // SA.rs:109-113
-                    else { const int4 v = __ldcg(bnd_in + i); tM = v.x; tX = v.y; tY = v.z; }
+                    else { const int4 v = bnd_sh[wib][t & 31]; tM = v.x; tX = v.y; tY = v.z; }
                 }
                 if (active) {
-                    const int ra = (int)a[i - 1] * nl;
-                    const int po = (MODE != SWB_LOCAL && i == la) ? so : o;      // SA.rs:166-167
-                    const int pe = (MODE != SWB_LOCAL && i == la) ? se : e;
-                    int dM = dM0, dX = dX0, dY = dY0;
-                    dM0 = tM; dX0 = tX; dY0 = tY;                                 // next row's diag for column 0
-                    unsigned long long codes = 0ull;
+                    const int *mrow = mat_sh + (int)a_sh[wib][(i - 1) & 63] * nl;
+                    const int po = (MODE == SWB_GLOCAL && i == la) ? so : o;     // SA.rs:166-167 (global: so == o)
+                    const int pe = (MODE == SWB_GLOCAL && i == la) ? se : e;
+                    int hd = hd0; unsigned ad = ad0;
+                    hd0 = __vimax3_s32(tM, tX, tY); ad0 = kw_am(tM, tX, tY);     // next row's diagonal for column 0
+                    codes_t codes = 0;
+                    const int sb_in = sb;
 #pragma unroll
-                    for (int c = 0; c < KW_C; ++c) {
-                        const int j = j0 + c + 1;
-                        const int qo = (MODE != SWB_LOCAL && j == lb) ? so : o;  // SA.rs:169-170
-                        const int qe = (MODE != SWB_LOCAL && j == lb) ? se : e;
-                        const int s = mat_sh[ra + brow[c]];
+                    for (int c = 0; c < C; ++c) {
+                        const int qo = (MODE == SWB_GLOCAL && c == own) ? so : o; // SA.rs:169-170 (column lb)
+                        const int qe = (MODE == SWB_GLOCAL && c == own) ? se : e;
                         int m, x, y; unsigned code;
-                        kw_cell<MODE>(dM, dX, dY, tM, tX, tY, Mu[c], Xu[c], Yu[c], s, po, pe, qo, qe, m, x, y, code);
-                        dM = Mu[c]; dX = Xu[c]; dY = Yu[c];
+                        kw_cell<MODE>(hd, ad, tM, tX, tY, Mu[c], Xu[c], Yu[c], mrow[boff[c]], po, pe, qo, qe, m, x, y, code);
+                        hd = Hu[c]; ad = Au[c];
                         Mu[c] = m; Xu[c] = x; Yu[c] = y;
+                        Hu[c] = __vimax3_s32(m, x, y); Au[c] = kw_am(m, x, y);
                         tM = m; tX = x; tY = y;
-                        codes |= (unsigned long long)code << (8 * c);
-                        if (j <= lb) {
-                            if (MODE == SWB_LOCAL) {
-                                if (m > best || (m == best && m > 0 && i < bi)) { best = m; bi = i; bj = j; }
-                            } else if (i == la && j == lb) {
-                                fin_score = m; fin_state = 0;                     // SA.rs:302-308: first strict max, order M,X,Y
-                                if (x > fin_score) { fin_score = x; fin_state = 1; }
-                                if (y > fin_score) { fin_score = y; fin_state = 2; }
-                                have_fin = true;
-                            }
-                        }
+                        if (DIRS) codes |= (codes_t)code << (8 * c);
+                        // padded columns (j > lb) score PAD: their MATCH is clamped to 0 and can never be a strict maximum
+                        if (MODE == SWB_LOCAL && m > sb) { sb = m; sj = j0 + c + 1; }
                     }
-                    lastM = Mu[KW_C - 1]; lastX = Xu[KW_C - 1]; lastY = Yu[KW_C - 1];
+                    if (MODE == SWB_LOCAL && sb != sb_in) si = i;
+                    if (MODE != SWB_LOCAL && i == la && own >= 0 && own < C) {    // cell (la, lb): SA.rs:302-308, first strict max M,X,Y
+#pragma unroll
+                        for (int c = 0; c < C; ++c)
+                            if (c == own) {
+                                fin_score = Mu[c]; fin_state = 0;
+                                if (Xu[c] > fin_score) { fin_score = Xu[c]; fin_state = 1; }
+                                if (Yu[c] > fin_score) { fin_score = Yu[c]; fin_state = 2; }
+                            }
+                        have_fin = true;
+                    }
+                    lastM = Mu[C - 1]; lastX = Xu[C - 1]; lastY = Yu[C - 1];
                     if (lane == 31 && sidx + 1 < n_strips) {
                         bnd_out[i] = make_int4(lastM, lastX, lastY, 0);
                         if (team_warps > 1 && ((i & 31) == 0 || i == la)) {       // publish rows 1..i of this strip's last column
@@ -172,10 +205,12 @@ kw_kernel(const uint8_t *__restrict__ a_all, const uint8_t *__restrict__ b_all, 
                             *reinterpret_cast<volatile int *>(prog + sidx) = i;
                         }
                     }
-                    if (DIRS) *reinterpret_cast<unsigned long long *>(dstrip + (int64_t)t * KW_SW) = codes;
+                    if (DIRS) *reinterpret_cast<codes_t *>(dstrip + (int64_t)t * SW) = codes;
                 }
             }
             __syncwarp();
+            // fold this strip's candidate into the lane's best: score desc, row asc, column asc (SA.rs:286-294 scan order)
+            if (MODE == SWB_LOCAL && (sb > best || (sb == best && sb > 0 && (si < bi || (si == bi && sj < bj))))) { best = sb; bi = si; bj = sj; }
         }
 
         if (MODE == SWB_LOCAL) {
@@ -229,51 +264,63 @@ kw_kernel(const uint8_t *__restrict__ a_all, const uint8_t *__restrict__ b_all, 
     }
 }
 
-// Host-side plan: team size, grid, scratch offsets.  Fills bnd_off / scr_off of the pairs.
-// Resident blocks per SM, minimum over all instantiations (teams spin on each other, so every block of a team launch
-// must be resident at once; the value is queried from the runtime, not assumed).
-static int kw_blocks_per_sm(const swb_engine *e)
+// Host-side plan: columns per lane, team size, grid, scratch and direction-byte offsets.  Fills bnd_off / scr_off /
+// dir_off of the pairs.  Resident blocks per SM: minimum over all instantiations (teams spin on each other, so every
+// block of a team launch must be resident at once; the value is queried from the runtime, not assumed).
+#define KW_FOR_MODES(X, C) X(SWB_GLOBAL, true, C) X(SWB_GLOBAL, false, C) X(SWB_GLOCAL, true, C) X(SWB_GLOCAL, false, C) \
+    X(SWB_LOCAL, true, C) X(SWB_LOCAL, false, C)
+
+static int kw_blocks_per_sm(const swb_engine *e, int cols)
 {
-    static int cached[64] = {0};
-    const int nl = e->n + 1;
-    if (cached[nl]) return cached[nl];
+    static int cached[2][64] = {{0}};
+    const int nl = e->n + 1, which = (cols == 2) ? 1 : 0;
+    if (cached[which][nl]) return cached[which][nl];
     const size_t smem = (size_t)nl * nl * sizeof(int);
     int best = 1 << 30, v = 0;
-#define KW_OCC(M, D) if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&v, kw_kernel<M, D>, KW_WARPS * 32, smem) == cudaSuccess) best = std::min(best, v); else best = 0;
-    KW_OCC(SWB_GLOBAL, true) KW_OCC(SWB_GLOBAL, false) KW_OCC(SWB_GLOCAL, true) KW_OCC(SWB_GLOCAL, false)
-    KW_OCC(SWB_LOCAL, true) KW_OCC(SWB_LOCAL, false)
+#define KW_OCC(M, D, C) if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&v, kw_kernel<M, D, C>, KW_WARPS * 32, smem) == cudaSuccess) best = std::min(best, v); else best = 0;
+    if (which) { KW_FOR_MODES(KW_OCC, 2) } else { KW_FOR_MODES(KW_OCC, 8) }
 #undef KW_OCC
-    cached[nl] = std::max(1, std::min(best, 8));
-    return cached[nl];
+    cached[which][nl] = std::max(1, std::min(best, 8));
+    return cached[which][nl];
 }
 
-void kw_plan(const swb_engine *e, KWPair *pairs, int n_pairs, KWPlan *plan)
+void kw_plan(const swb_engine *e, KWPair *pairs, int n_pairs, bool with_dirs, KWPlan *plan)
 {
-    const int capacity = e->sm_count * kw_blocks_per_sm(e) * KW_WARPS;   // warps that are guaranteed to be co-resident
+    // narrow strips (2 columns per lane) when even one warp per 256-column strip would leave most of the GPU idle
+    int64_t strips8 = 0;
+    for (int k = 0; k < n_pairs; ++k) strips8 += (pairs[k].lb + 255) / 256;
+    int cols = (n_pairs > 0 && strips8 * 3 < e->sm_count * kw_blocks_per_sm(e, 8) * KW_WARPS) ? 2 : 8;
+    if (const char *f = getenv("SWB_KW_COLS")) { if (atoi(f) == 2) cols = 2; else if (atoi(f) == 8) cols = 8; }   // tests force both widths
+    const int capacity = e->sm_count * kw_blocks_per_sm(e, cols) * KW_WARPS;   // warps that are guaranteed to be co-resident
+    const int sw = 32 * cols;
     int T = 1;
     if (n_pairs > 0 && n_pairs < capacity / 4) {
         int useful = 1;
         for (int k = 0; k < n_pairs; ++k) {
-            const int strips = (pairs[k].lb + KW_SW - 1) / KW_SW;
+            const int strips = (pairs[k].lb + sw - 1) / sw;
             useful = std::max(useful, std::min(strips, std::max(1, pairs[k].la / 128)));
         }
         T = std::max(1, std::min(capacity / n_pairs, useful));
     }
+    plan->cols = cols;
     plan->team_warps = T;
     plan->n_teams = (T == 1) ? n_pairs : std::max(1, std::min(n_pairs, capacity / T));
     const int64_t warps = (int64_t)plan->n_teams * T;
     plan->blocks = (int)((warps + KW_WARPS - 1) / KW_WARPS);
-    int64_t bnd = 0, scr = 0;
+    int64_t bnd = 0, scr = 0, dirb = 0;
     for (int k = 0; k < n_pairs; ++k) {
-        const int strips = (pairs[k].lb + KW_SW - 1) / KW_SW;
+        const int strips = (pairs[k].lb + sw - 1) / sw;
         pairs[k].bnd_off = bnd; pairs[k].scr_off = scr;
+        pairs[k].dir_off = with_dirs ? dirb : -1;
         bnd += (int64_t)std::min(strips, T + 1) * (pairs[k].la + 2);
         scr += 1 + strips + 4 * (int64_t)T;
+        if (with_dirs) dirb += kw_dir_bytes(pairs[k].la, pairs[k].lb, cols);
     }
     plan->bnd_elems = std::max<int64_t>(bnd, 1); plan->scratch_ints = std::max<int64_t>(scr, 1);
+    plan->dir_bytes = dirb;
 }
 
-template <int MODE>
+template <int MODE, int C>
 static cudaError_t kw_launch_mode(const swb_engine *e, const uint8_t *d_a, const uint8_t *d_b, const KWPair *d_pairs,
                                   int n_pairs, const KWPlan &pl, uint8_t *d_dir, int4 *d_bnd, int *d_scratch,
                                   KWResult *d_res, cudaStream_t st)
@@ -283,13 +330,13 @@ static cudaError_t kw_launch_mode(const swb_engine *e, const uint8_t *d_a, const
     cudaError_t err = cudaMemsetAsync(d_scratch, 0, (size_t)pl.scratch_ints * sizeof(int), st);
     if (err != cudaSuccess) return err;
     if (d_dir)
-        kw_kernel<MODE, true><<<pl.blocks, KW_WARPS * 32, smem, st>>>(d_a, d_b, d_pairs, n_pairs, pl.team_warps, pl.n_teams,
-                                                                      e->d_mat, nl, e->o, e->e, e->scale, d_dir, d_bnd,
-                                                                      d_scratch, d_res);
+        kw_kernel<MODE, true, C><<<pl.blocks, KW_WARPS * 32, smem, st>>>(d_a, d_b, d_pairs, n_pairs, pl.team_warps, pl.n_teams,
+                                                                         e->d_mat, nl, e->o, e->e, e->scale, d_dir, d_bnd,
+                                                                         d_scratch, d_res);
     else
-        kw_kernel<MODE, false><<<pl.blocks, KW_WARPS * 32, smem, st>>>(d_a, d_b, d_pairs, n_pairs, pl.team_warps, pl.n_teams,
-                                                                       e->d_mat, nl, e->o, e->e, e->scale, d_dir, d_bnd,
-                                                                       d_scratch, d_res);
+        kw_kernel<MODE, false, C><<<pl.blocks, KW_WARPS * 32, smem, st>>>(d_a, d_b, d_pairs, n_pairs, pl.team_warps, pl.n_teams,
+                                                                          e->d_mat, nl, e->o, e->e, e->scale, d_dir, d_bnd,
+                                                                          d_scratch, d_res);
     return cudaGetLastError();
 }
 
@@ -297,30 +344,33 @@ cudaError_t kw_launch(const swb_engine *e, const uint8_t *d_a, const uint8_t *d_
                       const KWPlan &plan, uint8_t *d_dir, int4 *d_bnd, int *d_scratch, KWResult *d_res, cudaStream_t st)
 {
     if (n_pairs <= 0) return cudaSuccess;
+#define KW_GO(M) (plan.cols == 2 ? kw_launch_mode<M, 2>(e, d_a, d_b, d_pairs, n_pairs, plan, d_dir, d_bnd, d_scratch, d_res, st) \
+                                 : kw_launch_mode<M, 8>(e, d_a, d_b, d_pairs, n_pairs, plan, d_dir, d_bnd, d_scratch, d_res, st))
     switch (e->mode) {
-    case SWB_GLOBAL: return kw_launch_mode<SWB_GLOBAL>(e, d_a, d_b, d_pairs, n_pairs, plan, d_dir, d_bnd, d_scratch, d_res, st);
-    case SWB_GLOCAL: return kw_launch_mode<SWB_GLOCAL>(e, d_a, d_b, d_pairs, n_pairs, plan, d_dir, d_bnd, d_scratch, d_res, st);
-    default: return kw_launch_mode<SWB_LOCAL>(e, d_a, d_b, d_pairs, n_pairs, plan, d_dir, d_bnd, d_scratch, d_res, st);
+    case SWB_GLOBAL: return KW_GO(SWB_GLOBAL);
+    case SWB_GLOCAL: return KW_GO(SWB_GLOCAL);
+    default: return KW_GO(SWB_LOCAL);
     }
+#undef KW_GO
 }
 
 // ------------------------------------------------------------------------------------------------
 // KT: backtrack (SA.rs:346-383).  One thread per pair follows the 2-bit predecessor codes from the
 // start cell and emits the column lists in walk order (end -> start); the host reverses them
 // (SA.rs:384-385).  idx value -1 = gap.  n_cols < 0 reports the reference's panic cases.
-__device__ __forceinline__ unsigned kt_code(const uint8_t *dir, int64_t dir_off, int la, int i, int j, int state)
+__device__ __forceinline__ unsigned kt_code(const uint8_t *dir, int64_t dir_off, int la, int i, int j, int state, int cols)
 {
-    const int jj = j - 1;
-    const int sidx = jj / KW_SW, within = jj - sidx * KW_SW;
-    const int t = (i - 1) + within / KW_C;
-    const uint8_t byte = dir[dir_off + ((int64_t)sidx * (la + 31) + t) * KW_SW + within];
+    const int jj = j - 1, sw = 32 * cols;
+    const int sidx = jj / sw, within = jj - sidx * sw;
+    const int t = (i - 1) + within / cols;
+    const uint8_t byte = dir[dir_off + ((int64_t)sidx * (la + 31) + t) * sw + within];
     return (byte >> (2 * state)) & 3u;
 }
 
 template <int MODE>
 __global__ void kt_kernel(const KWPair *__restrict__ pairs, const KWResult *__restrict__ res, int n_pairs,
                           const uint8_t *__restrict__ dir, const int64_t *__restrict__ out_off,
-                          int32_t *__restrict__ idx_a, int32_t *__restrict__ idx_b, int32_t *__restrict__ ncols, int sent)
+                          int32_t *__restrict__ idx_a, int32_t *__restrict__ idx_b, int32_t *__restrict__ ncols, int sent, int cols)
 {
     const int p = blockIdx.x * blockDim.x + threadIdx.x;
     if (p >= n_pairs) return;
@@ -332,7 +382,7 @@ __global__ void kt_kernel(const KWPair *__restrict__ pairs, const KWResult *__re
     int cx = R.end_i, cy = R.end_j, st = R.state;
     for (;;) {
         unsigned prev;
-        if (cx >= 1 && cy >= 1) prev = kt_code(dir, P.dir_off, P.la, cx, cy, st);
+        if (cx >= 1 && cy >= 1) prev = kt_code(dir, P.dir_off, P.la, cx, cy, st, cols);
         else if (cx == 0 && cy == 0) prev = 0;                     // only reachable when la == lb == 0
         else if (cx == 0) {                                        // row 0: prev = GAPINX for all states (SA.rs:105-107)
             prev = 1;
@@ -359,16 +409,16 @@ __global__ void kt_kernel(const KWPair *__restrict__ pairs, const KWResult *__re
 }
 
 cudaError_t kt_launch(const swb_engine *e, const KWPair *d_pairs, const KWResult *d_res, int n_pairs,
-                      const uint8_t *d_dir, const int64_t *d_out_off, int32_t *d_idx_a, int32_t *d_idx_b,
+                      const uint8_t *d_dir, int cols, const int64_t *d_out_off, int32_t *d_idx_a, int32_t *d_idx_b,
                       int32_t *d_ncols, cudaStream_t st)
 {
     if (n_pairs <= 0) return cudaSuccess;
     const int threads = 32, blocks = (n_pairs + threads - 1) / threads;
     const int sent = 10 * e->o + 10 * e->e;
     switch (e->mode) {
-    case SWB_GLOBAL: kt_kernel<SWB_GLOBAL><<<blocks, threads, 0, st>>>(d_pairs, d_res, n_pairs, d_dir, d_out_off, d_idx_a, d_idx_b, d_ncols, sent); break;
-    case SWB_GLOCAL: kt_kernel<SWB_GLOCAL><<<blocks, threads, 0, st>>>(d_pairs, d_res, n_pairs, d_dir, d_out_off, d_idx_a, d_idx_b, d_ncols, sent); break;
-    default: kt_kernel<SWB_LOCAL><<<blocks, threads, 0, st>>>(d_pairs, d_res, n_pairs, d_dir, d_out_off, d_idx_a, d_idx_b, d_ncols, sent); break;
+    case SWB_GLOBAL: kt_kernel<SWB_GLOBAL><<<blocks, threads, 0, st>>>(d_pairs, d_res, n_pairs, d_dir, d_out_off, d_idx_a, d_idx_b, d_ncols, sent, cols); break;
+    case SWB_GLOCAL: kt_kernel<SWB_GLOCAL><<<blocks, threads, 0, st>>>(d_pairs, d_res, n_pairs, d_dir, d_out_off, d_idx_a, d_idx_b, d_ncols, sent, cols); break;
+    default: kt_kernel<SWB_LOCAL><<<blocks, threads, 0, st>>>(d_pairs, d_res, n_pairs, d_dir, d_out_off, d_idx_a, d_idx_b, d_ncols, sent, cols); break;
     }
     return cudaGetLastError();
 }

@@ -105,12 +105,14 @@ struct KWPair {
     int64_t scr_off;                // offset (in ints) of the pair's team scratch          (filled by kw_plan)
 };
 struct KWPlan {
+    int cols = 8;                   // DP columns per lane (strip width 32*cols): 8, or 2 for a few long pairs
     int team_warps = 1;             // warps that sweep one pair together
     int n_teams = 0, blocks = 0;
     int64_t bnd_elems = 0;          // int4 elements of the boundary rings of all pairs
     int64_t scratch_ints = 0;       // progress counters + candidates of all pairs
+    int64_t dir_bytes = 0;          // direction bytes of all pairs (with_dirs)
 };
-void kw_plan(const swb_engine *e, KWPair *pairs, int n_pairs, KWPlan *plan);
+void kw_plan(const swb_engine *e, KWPair *pairs, int n_pairs, bool with_dirs, KWPlan *plan);   // also assigns dir_off
 struct KWResult {
     int32_t score;                  // scaled
     int32_t end_i, end_j;           // start cell of the traceback (1-based), -1 = empty
@@ -119,10 +121,10 @@ struct KWResult {
 cudaError_t kw_launch(const swb_engine *e, const uint8_t *d_a, const uint8_t *d_b, const KWPair *d_pairs,
                       int n_pairs, const KWPlan &plan, uint8_t *d_dir, int4 *d_bnd, int *d_scratch, KWResult *d_res,
                       cudaStream_t st);
-int64_t kw_dir_bytes(int32_t la, int32_t lb);        // bytes of the skewed direction store of one pair
+int64_t kw_dir_bytes(int32_t la, int32_t lb, int cols);   // bytes of the skewed direction store of one pair
 // KT: pointer walk over the direction bytes; one thread per pair.  Writes reversed column lists.
 cudaError_t kt_launch(const swb_engine *e, const KWPair *d_pairs, const KWResult *d_res, int n_pairs,
-                      const uint8_t *d_dir, const int64_t *d_out_off, int32_t *d_idx_a, int32_t *d_idx_b,
+                      const uint8_t *d_dir, int cols, const int64_t *d_out_off, int32_t *d_idx_a, int32_t *d_idx_b,
                       int32_t *d_ncols, cudaStream_t st);
 
 // K0
