@@ -298,3 +298,99 @@ def test_long_pairs_team_wavefront(mode):
     assert [float(x) for x in sc2] == [o["score"] for o in res]
     assert [int(x) for x in ea] == [o["end_a"] for o in res] and [int(x) for x in eb] == [o["end_b"] for o in res]
     eng.close()
+
+
+def _mutate(rng, base, sub, ins, dele, alphabet=b"ACGT"):
+    a = np.frombuffer(base, np.uint8)
+    al = np.frombuffer(alphabet, np.uint8)
+    b = a.copy()
+    s = rng.random(len(a)) < sub
+    b[s] = al[rng.integers(0, len(al), int(s.sum()))]
+    b = b[rng.random(len(b)) >= dele]
+    pos = np.nonzero(rng.random(len(b)) < ins)[0]
+    return np.insert(b, pos, al[rng.integers(0, len(al), len(pos))]).tobytes()
+
+
+def _rescore(aln_a, aln_b, match, mismatch, go, ge):
+    """Score of an alignment given as strings under the reference's model (SA.rs:139-252): a column that opens a gap
+    run -- also when the previous column was a gap in the OTHER sequence -- costs `go`, a column that continues a
+    run in the same sequence costs `ge`."""
+    a = np.frombuffer(aln_a.encode(), np.uint8); b = np.frombuffer(aln_b.encode(), np.uint8)
+    ga, gb = a == ord("-"), b == ord("-")
+    both = ~ga & ~gb
+    sc = float(np.sum(np.where(a[both] == b[both], match, mismatch)))
+    for g in (ga, gb):
+        prev = np.concatenate(([False], g[:-1]))
+        sc -= go * float(np.sum(g & ~prev)) + ge * float(np.sum(g & prev))
+    return sc
+
+
+@pytest.mark.parametrize("cols", ["2", "8"])
+@pytest.mark.parametrize("mode", [swb.ALIGN_LOCAL, swb.ALIGN_GLOBAL])
+def test_config4_dna_pair_dense_oracle(mode, cols, monkeypatch):
+    """BASELINE configs[3] at 6 kb: +2/-3, open 5 / extend 2, full traceback; strings, score and end cell equal the
+    dense oracle for both strip widths of the wavefront kernel."""
+    monkeypatch.setenv("SWB_KW_COLS", cols)
+    rng = np.random.default_rng(20244)
+    a = _rand_seqs(rng, 1, 6000, 6000, "ACGT")[0]
+    b = _mutate(rng, a, 0.08, 0.02, 0.02)
+    m = swb.SubstitutionMatrix.get_mat_matrix(2.0, -3.0)
+    eng = swb.SequenceAlignment(m, 5.0, 2.0, mode)
+    out = eng.align_raw(a, b, True)
+    r1, r2, sc = O.Engine(_omatrix(m), 5.0, 2.0, mode).align(a.decode(), b.decode(), True)
+    assert out["score"] == sc and out["aln_a"] == "".join(r1) and out["aln_b"] == "".join(r2)
+    eng.close()
+
+
+def test_config4_dna_pair_100kb_properties():
+    """BASELINE configs[3] at full size (100 kb x ~100 kb, 10^10 cells, 10 GB of direction bytes).  The dense oracle
+    cannot hold this; checked instead: (i) the score equals the linear-memory integer oracle's on a 30 kb prefix pair,
+    (ii) at full size the emitted strings re-score to the reported score, spell the inputs, and the global score is
+    not above the local one, (iii) score-only and traceback paths agree."""
+    rng = np.random.default_rng(20244)
+    a = _rand_seqs(rng, 1, 100000, 100000, "ACGT")[0]
+    b = _mutate(rng, a, 0.08, 0.02, 0.02)
+    m = swb.SubstitutionMatrix.get_mat_matrix(2.0, -3.0)
+    om = _omatrix(m)
+    scores = {}
+    for mode in (swb.ALIGN_LOCAL, swb.ALIGN_GLOBAL):
+        eng = swb.SequenceAlignment(m, 5.0, 2.0, mode)
+        out = eng.align_raw(a, b, False)
+        assert out["aln_a"].replace("-", "") in a.decode() and out["aln_b"].replace("-", "") in b.decode()
+        if mode == swb.ALIGN_GLOBAL:
+            assert out["aln_a"].replace("-", "") == a.decode() and out["aln_b"].replace("-", "") == b.decode()
+        assert _rescore(out["aln_a"], out["aln_b"], 2.0, -3.0, 5.0, 2.0) == out["score"]
+        sc, ea, eb = eng.score_batch([a], [b])
+        assert float(sc[0]) == out["score"] and (int(ea[0]), int(eb[0])) == (out["end_a"], out["end_b"])
+        scores[mode] = out["score"]
+        pa, pb = a[:30000], b[:30000]
+        sc, ea, eb = eng.score_batch([pa], [pb])
+        ia, oa = O.pack([om.seq_to_index(pa.decode())]); ib, ob = O.pack([om.seq_to_index(pb.decode())])
+        osc, oi, oj = O.score_batch_int(ia, oa, ib, ob, np.rint(m.scores).astype(np.int32), -5, -2, 1, mode, 1)
+        assert (float(sc[0]), int(ea[0]), int(eb[0])) == (float(osc[0]), int(oi[0]), int(oj[0]))
+        eng.close()
+    assert scores[swb.ALIGN_GLOBAL] <= scores[swb.ALIGN_LOCAL]
+
+
+def test_config5_nw_batch_10kb():
+    """BASELINE configs[4]: Needleman-Wunsch (global) on a batch of 10 kb noisy-read-like DNA pairs with traceback
+    strings: dense oracle on two pairs (strings), linear integer oracle on all (scores), re-scoring on all."""
+    rng = np.random.default_rng(20245)
+    n = 24
+    sa = _rand_seqs(rng, n, 10000, 10000, "ACGT")
+    sb = [_mutate(rng, s, 0.05, 0.05, 0.05) for s in sa]
+    m = swb.SubstitutionMatrix.get_mat_matrix(2.0, -3.0)
+    om = _omatrix(m)
+    eng = swb.SequenceAlignment(m, 5.0, 2.0, swb.ALIGN_GLOBAL)
+    res = eng.align_list(sa, sb, True)
+    ia, oa = O.pack([om.seq_to_index(s.decode()) for s in sa]); ib, ob = O.pack([om.seq_to_index(s.decode()) for s in sb])
+    osc, _, _ = O.score_batch_int(ia, oa, ib, ob, np.rint(m.scores).astype(np.int32), -5, -2, 1, swb.ALIGN_GLOBAL, 8)
+    assert [r["score"] for r in res] == [float(x) for x in osc]
+    for a, b, r in zip(sa, sb, res):
+        assert r["aln_a"].replace("-", "") == a.decode() and r["aln_b"].replace("-", "") == b.decode()
+        assert _rescore(r["aln_a"], r["aln_b"], 2.0, -3.0, 5.0, 2.0) == r["score"]
+    oeng = O.Engine(om, 5.0, 2.0, swb.ALIGN_GLOBAL)
+    for k in (0, n - 1):
+        r1, r2, sc = oeng.align(sa[k].decode(), sb[k].decode(), True)
+        assert (res[k]["aln_a"], res[k]["aln_b"], res[k]["score"]) == ("".join(r1), "".join(r2), sc)
+    eng.close()
