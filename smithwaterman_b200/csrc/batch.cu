@@ -271,6 +271,22 @@ static int batch_upload_impl(swb_engine *e, const char *a_all, const int64_t *of
             e->d_bnd = nullptr; e->bnd_bytes = 0;
             CUDA_TRY(e, cudaMalloc(&e->d_bnd, need));
             e->bnd_bytes = need;
+            // keep the pass-boundary scratch resident in L2: it is rewritten and re-read every pass by the resident warps
+            int max_persist = 0, max_win = 0;
+            cudaDeviceGetAttribute(&max_persist, cudaDevAttrMaxPersistingL2CacheSize, e->device);
+            cudaDeviceGetAttribute(&max_win, cudaDevAttrMaxAccessPolicyWindowSize, e->device);
+            if (max_persist > 0 && max_win > 0) {
+                cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, (size_t)max_persist);
+                cudaStreamAttrValue av = {};
+                av.accessPolicyWindow.base_ptr = e->d_bnd;
+                av.accessPolicyWindow.num_bytes = std::min<size_t>(need, (size_t)std::min(max_win, max_persist));   // the low row blocks
+                av.accessPolicyWindow.hitRatio = 1.0f;
+                av.accessPolicyWindow.hitProp = cudaAccessPropertyPersisting;
+                av.accessPolicyWindow.missProp = cudaAccessPropertyStreaming;
+                cudaStreamSetAttribute(e->stream, cudaStreamAttributeAccessPolicyWindow, &av);
+                if (getenv("SWB_TRACE")) fprintf(stderr, "[swb] L2 persisting window: %zu bytes, max persist %d, hit ratio %.2f\n", av.accessPolicyWindow.num_bytes, max_persist, av.accessPolicyWindow.hitRatio);
+                cudaGetLastError();
+            }
         }
     }
     // ---- pairs for the int32 wavefront kernel
