@@ -13,6 +13,7 @@
 #include "swb_internal.h"
 
 #define K1_MAX_LEN 8192            // longer pairs go to the wavefront kernel
+#define K2_MIN_QUERY 1024           // shared queries at least this long use K2 (its 124-step skew is < 12 % there)
 
 struct BatchDev {                  // device-only members that do not fit the plain struct in the header
     uint8_t *codes_a = nullptr, *codes_b = nullptr;   // encoded residues, caller layout
@@ -24,6 +25,8 @@ struct BatchDev {                  // device-only members that do not fit the pl
     std::vector<KWPair> h_kw; std::vector<int32_t> kw_idx;   // caller index of each KW pair
     std::vector<int32_t> degenerate;                         // caller indices with la==0 or lb==0
     int n_k1 = 0;
+    int n_k2 = 0, n_items = 0;                               // K2 (shared long query): pairs taken, warp work items
+    int32_t *items = nullptr, *sweeps = nullptr;             // device: [n_items][32] caller index per lane (-1 idle), sweeps per item
     int64_t base_a = 0, base_b = 0;                          // caller offset of the first residue held on the device
     int64_t shared_la = -1;                                  // >= 0: all pairs share one `a` (database search)
     K1Result *h_res = nullptr; KWResult *h_kwres = nullptr; int32_t *h_err = nullptr;   // pinned staging (engine arena or own)
@@ -132,7 +135,7 @@ static void batch_release(swb_engine *e, swb_batch *b)
     BatchDev *d = dev_of(b);
     if (d) {
         dev_free(e, d->codes_a); dev_free(e, d->codes_b); dev_free(e, d->off_a); dev_free(e, d->off_b); dev_free(e, d->order);
-        dev_free(e, d->err); dev_free(e, d->kw_pairs); dev_free(e, d->kw_res); dev_free(e, d->kw_bnd); dev_free(e, d->kw_scr);
+        dev_free(e, d->err); dev_free(e, d->items); dev_free(e, d->sweeps); dev_free(e, d->kw_pairs); dev_free(e, d->kw_res); dev_free(e, d->kw_bnd); dev_free(e, d->kw_scr);
         if (d->own_stage) { cudaFreeHost(d->h_res); cudaFreeHost(d->h_kwres); cudaFreeHost(d->h_err); }
         if (d->ev0) cudaEventDestroy(d->ev0);
         if (d->ev1) cudaEventDestroy(d->ev1);
@@ -190,7 +193,9 @@ static int batch_upload_impl(swb_engine *e, const char *a_all, const int64_t *of
 
     // ---- shape sort (counting sort on (passes, la), longest first) and routing
     b->la.resize(n); b->lb.resize(n);
-    std::vector<int32_t> k1_idx;
+    // a long shared query (database search) goes to K2: lanes split the columns, every work item lasts la + 124 row steps
+    const bool use_k2 = use_k1 && shared && shared_la >= K2_MIN_QUERY && shared_la <= 0x0FFFFFFF;
+    std::vector<int32_t> k1_idx, k2_idx;
     k1_idx.reserve(n);
     int la_cap = 0, pass_cap = 0;
     b->cells = 0;
@@ -200,6 +205,7 @@ static int batch_upload_impl(swb_engine *e, const char *a_all, const int64_t *of
         b->la[k] = (int32_t)la; b->lb[k] = (int32_t)lb;
         b->cells += (double)la * (double)lb;
         if (la == 0 || lb == 0) d->degenerate.push_back((int32_t)k);
+        else if (use_k2) k2_idx.push_back((int32_t)k);
         else if (use_k1 && la <= K1_MAX_LEN && lb <= K1_MAX_LEN) {
             k1_idx.push_back((int32_t)k);
             la_cap = std::max(la_cap, (int)la);
@@ -289,6 +295,70 @@ static int batch_upload_impl(swb_engine *e, const char *a_all, const int64_t *of
             }
         }
     }
+    // ---- K2 work items: subjects of >= 32 passes take a warp each (several sweeps), the others are bin-packed
+    //      (first fit, longest first) into warps of 32 lanes, one lane per 32-column pass
+    d->n_k2 = (int)k2_idx.size();
+    if (d->n_k2) {
+        std::vector<std::vector<int32_t>> bucket(32);
+        std::vector<int32_t> longs;
+        for (int32_t k : k2_idx) {
+            const int np = (b->lb[k] + K1_STRIP - 1) / K1_STRIP;
+            if (np >= 32) longs.push_back(k); else bucket[np].push_back(k);
+        }
+        std::sort(longs.begin(), longs.end(), [&](int32_t x, int32_t y) { return b->lb[x] > b->lb[y]; });
+        size_t small_passes = 0; unsigned mask = 0;
+        for (int p = 1; p < 32; ++p) { small_passes += bucket[p].size() * (size_t)p; if (!bucket[p].empty()) mask |= 1u << p; }
+        const size_t cap_items = longs.size() + small_passes / 32 + small_passes / 256 + 64;    // first fit wastes < 12 %
+        int32_t *h_items = nullptr, *h_sweeps = nullptr;
+        const size_t items_bytes = (cap_items * 33) * sizeof(int32_t);
+        if (items_bytes > e->items_bytes) {
+            CUDA_TRY(e, cudaStreamSynchronize(up));
+            if (e->h_items) cudaFreeHost(e->h_items);
+            e->h_items = nullptr; e->items_bytes = 0;
+            CUDA_TRY(e, cudaMallocHost(&e->h_items, items_bytes));
+            e->items_bytes = items_bytes;
+        }
+        else if (e->ev_items) CUDA_TRY(e, cudaEventSynchronize(e->ev_items));   // an earlier chunk's copy out of this buffer
+        h_items = (int32_t *)e->h_items; h_sweeps = h_items + cap_items * 32;
+        size_t ni = 0;
+        for (int32_t k : longs) {
+            for (int l = 0; l < 32; ++l) h_items[ni * 32 + l] = k;
+            h_sweeps[ni++] = ((b->lb[k] + K1_STRIP - 1) / K1_STRIP + 31) / 32;
+        }
+        while (mask) {
+            int cap = 32, l = 0;
+            if (ni >= cap_items) { e->err = "K2 item table overflow"; return SWB_ERR_NOMEM; }
+            while (cap > 0) {
+                const unsigned fit = mask & ((cap >= 31) ? 0xFFFFFFFFu : ((2u << cap) - 1u));
+                if (!fit) break;
+                const int p = 31 - __builtin_clz(fit);
+                const int32_t k = bucket[p].back(); bucket[p].pop_back();
+                if (bucket[p].empty()) mask &= ~(1u << p);
+                for (int t = 0; t < p; ++t) h_items[ni * 32 + l++] = k;
+                cap -= p;
+            }
+            for (; l < 32; ++l) h_items[ni * 32 + l] = -1;
+            h_sweeps[ni++] = 1;
+        }
+        d->n_items = (int)ni;
+        DEV_ALLOC_ON(e, up, d->items, ni * 32 * sizeof(int32_t)); DEV_ALLOC_ON(e, up, d->sweeps, ni * sizeof(int32_t));
+        DEV_ALLOC_ON(e, up, b->d_res, n * sizeof(K1Result));
+        CUDA_TRY(e, cudaMemsetAsync(b->d_res, 0, n * sizeof(K1Result), up));
+        DEV_ALLOC_ON(e, up, b->d_counter, sizeof(int32_t));
+        CUDA_TRY(e, cudaMemcpyAsync(d->items, h_items, ni * 32 * sizeof(int32_t), cudaMemcpyHostToDevice, up));
+        CUDA_TRY(e, cudaMemcpyAsync(d->sweeps, h_sweeps, ni * sizeof(int32_t), cudaMemcpyHostToDevice, up));
+        e->stats.h2d_bytes += (double)ni * 33 * sizeof(int32_t);
+        if (!e->ev_items) CUDA_TRY(e, cudaEventCreateWithFlags(&e->ev_items, cudaEventDisableTiming));
+        CUDA_TRY(e, cudaEventRecord(e->ev_items, up));
+        const size_t need = k2_bnd_bytes(e->sm_count, (int)shared_la);
+        if (need > e->bnd_bytes) {
+            CUDA_TRY(e, cudaDeviceSynchronize());
+            if (e->d_bnd) cudaFree(e->d_bnd);
+            e->d_bnd = nullptr; e->bnd_bytes = 0;
+            CUDA_TRY(e, cudaMalloc(&e->d_bnd, need));
+            e->bnd_bytes = need;
+        }
+    }
     // ---- pairs for the int32 wavefront kernel
     d->n_kw = (int)d->kw_idx.size();
     if (d->n_kw) {
@@ -358,6 +428,11 @@ static int batch_launch(swb_engine *e, swb_batch *b, int64_t *launches)
     BatchDev *d = b->dev;
     CUDA_TRY(e, cudaStreamWaitEvent(e->stream, d->ev_ready, 0));     // upload may have run on the copy stream
     if (d->n_k1) { CUDA_TRY(e, k1_launch(e, b, e->sm_count, e->stream)); ++*launches; }
+    if (d->n_k2) {
+        CUDA_TRY(e, k2_launch(e, d->codes_a, (int)d->shared_la, d->codes_b, d->off_b, d->base_b, d->items, d->sweeps, d->n_items, e->d_bnd,
+                              b->d_counter, b->d_res, e->sm_count, e->stream));
+        ++*launches;
+    }
     if (d->n_kw) {
         CUDA_TRY(e, kw_launch(e, d->codes_a, d->codes_b, d->kw_pairs, d->n_kw, d->kw_plan_, nullptr, d->kw_bnd, d->kw_scr, d->kw_res, e->stream));
         ++*launches;
@@ -414,10 +489,10 @@ extern "C" int swb_batch_run_n(swb_engine *e, swb_batch *b, int steps, float *to
 static int batch_fetch_enqueue(swb_engine *e, swb_batch *b)
 {
     BatchDev *d = b->dev;
-    if (d->n_k1) CUDA_TRY(e, cudaMemcpyAsync(d->h_res, b->d_res, b->n * sizeof(K1Result), cudaMemcpyDeviceToHost, e->stream));
+    if (d->n_k1 || d->n_k2) CUDA_TRY(e, cudaMemcpyAsync(d->h_res, b->d_res, b->n * sizeof(K1Result), cudaMemcpyDeviceToHost, e->stream));
     if (d->n_kw) CUDA_TRY(e, cudaMemcpyAsync(d->h_kwres, d->kw_res, d->n_kw * sizeof(KWResult), cudaMemcpyDeviceToHost, e->stream));
     CUDA_TRY(e, cudaEventRecord(d->ev_done, e->stream));
-    e->stats.d2h_bytes += (d->n_k1 ? (double)b->n * sizeof(K1Result) : 0.0) + (double)d->n_kw * sizeof(KWResult);
+    e->stats.d2h_bytes += ((d->n_k1 || d->n_k2) ? (double)b->n * sizeof(K1Result) : 0.0) + (double)d->n_kw * sizeof(KWResult);
     return SWB_OK;
 }
 
@@ -435,7 +510,7 @@ static int batch_fetch_finish(swb_engine *e, swb_batch *b, float *scores, int64_
     const bool dyadic = (e->scale & (e->scale - 1)) == 0;
     auto to_f = [&](int32_t s) { return dyadic ? (float)s * inv : (float)((double)s / e->scale); };
     std::vector<int32_t> redo;                       // pairs whose s16 lanes overflowed
-    if (d->n_k1) {
+    if (d->n_k1 || d->n_k2) {
         const K1Result *hr = d->h_res;                 // caller order (K1 scatters); non-K1 entries are zero and overwritten below
         for (int64_t k = 0; k < b->n; ++k) {
             const K1Result r = hr[k];

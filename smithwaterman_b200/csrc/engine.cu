@@ -171,6 +171,8 @@ extern "C" void swb_engine_destroy(swb_engine *e)
     if (e->d_code_tab) cudaFree(e->d_code_tab);
     if (e->d_bnd) cudaFree(e->d_bnd);
     if (e->h_stage) cudaFreeHost(e->h_stage);
+    if (e->h_items) cudaFreeHost(e->h_items);
+    if (e->ev_items) cudaEventDestroy(e->ev_items);
     if (e->ev0) cudaEventDestroy(e->ev0);
     if (e->ev1) cudaEventDestroy(e->ev1);
     if (e->stream) cudaStreamDestroy(e->stream);

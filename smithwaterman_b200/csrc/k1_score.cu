@@ -238,3 +238,204 @@ cudaError_t k1_launch(const swb_engine *e, const swb_batch *b, int n_blocks, cud
         reinterpret_cast<uint4 *>(e->d_bnd), k1_bnd_blocks(b->la_max), b->d_counter, b->d_order, b->d_res);
     return cudaGetLastError();
 }
+
+// ------------------------------------------------------------------------------------------------------------------
+// K2 -- the same packed recurrence with the LANES OF A WARP SPLITTING THE COLUMNS of a pair: database search with a
+// long shared query (SA-main.rs:35-45 all-vs-all loop with one fixed `a`; per-pair semantics of align_partial(..,
+// score_only), SA.rs:438-467).
+//
+// With one thread per pair (K1) a work item lasts la * ceil(lb/32) row steps: 5000 x 157 for a 5000-aa query against a
+// 5000-aa subject, i.e. hundreds of milliseconds for one warp, which leaves most of the GPU (and most of a multi-GPU
+// box) waiting for the longest subjects.  Here every lane owns ONE 32-column pass of some subject; the passes of a
+// subject sit in consecutive lanes (a "segment") and run skewed by one 4-row block per lane, so that the last column
+// of a pass reaches the next lane by four __shfl_up per row block instead of through memory.  Subjects of up to 32
+// passes are bin-packed into warps by the host; every item then lasts (la + 4*31) row steps regardless of the subject
+// lengths.  A subject of more than 32 passes takes a whole warp for several sweeps of 1024 columns, handing the last
+// column of a sweep to lane 0 of the next one through a small global buffer.  Rows before a lane's start and after its
+// end are PAD rows, which leave the DP state equivalent to the initial one (H = 0; E, F <= 0), so all lanes run the same
+// instruction stream.
+__global__ void __launch_bounds__(K1_THREADS * 2, 1)
+k2_search_kernel(const unsigned *__restrict__ a_words, int la, const uint8_t *__restrict__ codes_b,
+                 const int64_t *__restrict__ off_b, long long base_b, const int32_t *__restrict__ item_pairs,
+                 const int32_t *__restrict__ item_sweeps, int n_items, const int32_t *__restrict__ mat, int nl, int open,
+                 int ext, int limit_ho, uint4 *__restrict__ gbnd, int gb_blocks, int *counter, K1Result *__restrict__ res)
+{
+    extern __shared__ unsigned T_sh[];               // [nl*nl][32 lanes]: (s - open) & 0xFFFF
+    __shared__ int cand_sh[K1_THREADS * 2 / 32][32][4];
+    for (int idx = threadIdx.x; idx < nl * nl * 32; idx += blockDim.x)
+        T_sh[idx] = (unsigned)(mat[idx >> 5] - open) & 0xFFFFu;
+    __syncthreads();
+
+    const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
+    const int wslot = blockIdx.x * (blockDim.x >> 5) + wib;
+    uint4 *mybnd = gbnd + (size_t)wslot * (size_t)gb_blocks;          // one uint4 per row block (a single lane uses it)
+    const unsigned tbase = (unsigned)__cvta_generic_to_shared(T_sh) + lane * 4;
+    const unsigned rowstride = (unsigned)nl * 128u;
+    const unsigned open2 = pack2(open, open), ext2 = pack2(ext, ext);
+    const unsigned pad = (unsigned)(nl - 1), pad4 = pad * 0x01010101u;
+    const int nblk = (la + 1 + 3) >> 2;              // row blocks of a pass (one step past la finishes the high half)
+    const int nwords = (la + 3) >> 2;                // query words that hold real rows
+
+    for (;;) {
+        int g = 0;
+        if (lane == 0) g = atomicAdd(counter, 1);
+        g = __shfl_sync(0xffffffffu, g, 0);
+        if (g >= n_items) break;
+        const int pair = item_pairs[(size_t)g * 32 + lane];           // caller index of this lane's subject, -1 = idle
+        const int sweeps = item_sweeps[g];
+        const int prev_pair = __shfl_up_sync(0xffffffffu, pair, 1);
+        const bool head = (lane == 0) || (pair != prev_pair);
+        const unsigned heads = __ballot_sync(0xffffffffu, head);
+        const int head_lane = 31 - __clz(heads & (0xffffffffu >> (31 - lane)));
+        const int pos = lane - head_lane;                             // pass index of this lane within its subject
+        const unsigned next_heads = heads & ~((2u << lane) - 1u);     // heads above this lane
+        const int seg_end = next_heads ? (__ffs(next_heads) - 1) : 32;   // one past the last lane of this segment
+        long long ob = 0; int lb = 0;
+        if (pair >= 0) { ob = off_b[pair] - base_b; lb = (int)(off_b[pair + 1] - off_b[pair]); }
+        int pmax = pos;
+#pragma unroll
+        for (int d = 16; d >= 1; d >>= 1) pmax = max(pmax, __shfl_xor_sync(0xffffffffu, pmax, d));
+        const int n_gb = nblk + pmax;                                 // global row blocks: every lane finishes its rows
+        int bestHo = open, bi = -1, bj = -1, ovf = 0;
+        int tb = open;                                                // best of the SUBJECT known to this lane: the exact path is
+                                                                      // entered only by rows that reach it (ties included)
+
+        for (int sw = 0; sw < sweeps; ++sw) {
+            const int jbase = (sw * 32 + pos) * K1_STRIP;
+            unsigned cb_lo[K1_HALF], cb_hi[K1_HALF], Ho[K1_HALF], F[K1_HALF];
+#pragma unroll
+            for (int k = 0; k < K1_HALF; ++k) {
+                const int j1 = jbase + k, j2 = jbase + K1_HALF + k;
+                const unsigned c1 = (j1 < lb) ? (unsigned)codes_b[ob + j1] : pad;
+                const unsigned c2 = (j2 < lb) ? (unsigned)codes_b[ob + j2] : pad;
+                cb_lo[k] = tbase + c1 * 128u; cb_hi[k] = tbase + c2 * 128u;
+                Ho[k] = open2; F[k] = 0u;
+            }
+            const bool first = (pos == 0 && sw == 0);                 // left boundary = column 0: H = 0
+            const bool from_g = (pos == 0 && sw > 0);                 // left boundary = last column of the previous sweep
+            const bool to_g = (lane == 31 && sw + 1 < sweeps);
+            unsigned HoD = open2, r_prev = pad, lo15_Ho = open2, lo15_E = open2;
+            unsigned thr2 = pack2(tb - 1, tb - 1);
+            unsigned c1 = open2, c2 = open2, c3 = open2;              // this lane's boundary words of the previous block
+            int bl = -pos;                                            // this lane's row block
+            unsigned word_next = (bl >= 0 && bl < nwords) ? a_words[bl] : pad4;
+            uint4 g_next = make_uint4(open2, open2, open2, open2);
+            if (from_g) g_next = mybnd[0];
+
+#pragma unroll 1
+            for (int gbk = 0; gbk < n_gb; ++gbk, ++bl) {
+                const int i0 = bl * 4;                            // low-half rows i0+1 .. i0+4 (negative before the start)
+                const unsigned word = word_next;
+                const uint4 g4 = g_next;
+                word_next = (bl + 1 >= 0 && bl + 1 < nwords) ? a_words[bl + 1] : pad4;
+                if (from_g && bl + 1 < nblk) g_next = mybnd[bl + 1];
+                // rows i0+1..i0+3 of the left boundary: the left lane's words of ITS previous block (it runs one block ahead)
+                const unsigned s1 = __shfl_up_sync(0xffffffffu, c1, 1), s2 = __shfl_up_sync(0xffffffffu, c2, 1),
+                               s3 = __shfl_up_sync(0xffffffffu, c3, 1);
+                unsigned bq[4];
+                bq[0] = first ? open2 : (from_g ? g4.x : s1);
+                bq[1] = first ? open2 : (from_g ? g4.y : s2);
+                bq[2] = first ? open2 : (from_g ? g4.z : s3);
+                bq[3] = open2;
+                unsigned wout[4];
+#pragma unroll
+                for (int t = 0; t < 4; ++t) {
+                    const int i = i0 + t + 1;                    // low lane row; high lane row = i-1
+                    const unsigned r = (word >> (t * 8)) & 0xFFu;
+                    const unsigned roff_lo = r * rowstride, roff_hi = r_prev * rowstride;
+                    r_prev = r;
+                    unsigned GoP = __byte_perm(bq[t], lo15_Ho, 0x5410);
+                    unsigned E = __byte_perm(bq[t], lo15_E, 0x5432);
+                    const unsigned HoD_next = GoP;
+                    K1_CELL(0) K1_CELL(1) K1_CELL(2) K1_CELL(3) K1_CELL(4) K1_CELL(5) K1_CELL(6) K1_CELL(7)
+                    K1_CELL(8) K1_CELL(9) K1_CELL(10) K1_CELL(11) K1_CELL(12) K1_CELL(13) K1_CELL(14) K1_CELL(15)
+                    wout[t] = __byte_perm(Ho[15], E, 0x7632);    // column 32q+31 at row i-1
+                    if (t == 0) {
+                        // row i0+4 of the left boundary is the left lane's first word of THIS block
+                        const unsigned s0 = __shfl_up_sync(0xffffffffu, wout[0], 1);
+                        bq[3] = first ? open2 : (from_g ? g4.w : s0);
+                        if (to_g && bl > 0) mybnd[bl - 1] = make_uint4(c1, c2, c3, wout[0]);
+                    }
+                    lo15_Ho = Ho[15]; lo15_E = E;
+                    HoD = HoD_next;
+                    unsigned rm = __vimax3_s16x2(Ho[0], Ho[1], Ho[2]);
+                    rm = __vimax3_s16x2(rm, Ho[3], Ho[4]);
+                    rm = __vimax3_s16x2(rm, Ho[5], Ho[6]);
+                    rm = __vimax3_s16x2(rm, Ho[7], Ho[8]);
+                    rm = __vimax3_s16x2(rm, Ho[9], Ho[10]);
+                    rm = __vimax3_s16x2(rm, Ho[11], Ho[12]);
+                    rm = __vimax3_s16x2(rm, Ho[13], Ho[14]);
+                    rm = __vmaxs2(rm, Ho[15]);
+                    if (__vmaxs2(thr2, rm) != thr2) {
+                        const int rlo = lo16(rm), rhi = hi16(rm);
+                        if (i >= 1 && i <= la && (rlo > bestHo || (rlo == bestHo && rlo > open && i < bi))) {
+                            int kk = 0;
+#pragma unroll
+                            for (int k = K1_HALF - 1; k >= 0; --k)
+                                if (lo16(Ho[k]) == rlo) kk = k;
+                            bestHo = rlo; bi = i; bj = jbase + kk + 1;
+                            if (rlo >= limit_ho) ovf = 1;
+                        }
+                        if (i >= 2 && i - 1 <= la && (rhi > bestHo || (rhi == bestHo && rhi > open && i - 1 < bi))) {
+                            int kk = 0;
+#pragma unroll
+                            for (int k = K1_HALF - 1; k >= 0; --k)
+                                if (hi16(Ho[k]) == rhi) kk = k;
+                            bestHo = rhi; bi = i - 1; bj = jbase + K1_HALF + kk + 1;
+                            if (rhi >= limit_ho) ovf = 1;
+                        }
+                        tb = max(tb, bestHo);
+                        thr2 = pack2(tb - 1, tb - 1);
+                    }
+                }
+                c1 = wout[1]; c2 = wout[2]; c3 = wout[3];
+                {   // the subject's best diffuses along the segment, one lane per row block in both directions
+                    const int up = __shfl_up_sync(0xffffffffu, tb, 1), dn = __shfl_down_sync(0xffffffffu, tb, 1);
+                    int nb = tb;
+                    if (!head) nb = max(nb, up);
+                    if (lane + 1 < seg_end) nb = max(nb, dn);
+                    if (nb != tb) { tb = nb; thr2 = pack2(tb - 1, tb - 1); }
+                }
+            }
+            if (to_g) mybnd[nblk - 1] = make_uint4(c1, c2, c3, open2);
+            __syncwarp();
+        }
+
+        // per-lane candidates -> the segment's head lane: score desc, row asc, column asc (SA.rs:286-294 scan order)
+        cand_sh[wib][lane][0] = bestHo; cand_sh[wib][lane][1] = bi; cand_sh[wib][lane][2] = bj; cand_sh[wib][lane][3] = ovf;
+        __syncwarp();
+        if (head && pair >= 0) {
+            for (int l2 = lane + 1; l2 < seg_end; ++l2) {
+                const int ob_ = cand_sh[wib][l2][0], oi = cand_sh[wib][l2][1], oj = cand_sh[wib][l2][2];
+                ovf |= cand_sh[wib][l2][3];
+                if (ob_ > bestHo || (ob_ == bestHo && ob_ > open && (oi < bi || (oi == bi && oj < bj)))) { bestHo = ob_; bi = oi; bj = oj; }
+            }
+            K1Result r;
+            r.score = bestHo - open;
+            r.end_i = (bestHo > open) ? bi : -1;
+            r.end_j = (bestHo > open) ? bj : -1;
+            r.flags = ovf;
+            res[pair] = r;
+        }
+        __syncwarp();
+    }
+}
+
+size_t k2_bnd_bytes(int n_blocks, int la) { return (size_t)n_blocks * (K1_THREADS * 2 / 32) * (size_t)((la + 1 + 3) / 4 + 2) * sizeof(uint4); }
+
+cudaError_t k2_launch(const swb_engine *e, const uint8_t *d_query, int la, const uint8_t *d_codes_b, const int64_t *d_off_b,
+                      int64_t base_b, const int32_t *d_item_pairs, const int32_t *d_item_sweeps, int n_items, void *d_gbnd,
+                      int *d_counter, K1Result *d_res, int n_blocks, cudaStream_t st)
+{
+    const int nl = e->n + 1;
+    const size_t smem = (size_t)nl * nl * 32 * sizeof(unsigned);
+    cudaError_t err = cudaFuncSetAttribute(k2_search_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (err != cudaSuccess) return err;
+    err = cudaMemsetAsync(d_counter, 0, sizeof(int32_t), st);
+    if (err != cudaSuccess) return err;
+    const int limit_ho = 32767 - 2 * e->smax + e->o - 1;
+    k2_search_kernel<<<n_blocks, K1_THREADS * 2, smem, st>>>(
+        reinterpret_cast<const unsigned *>(d_query), la, d_codes_b, d_off_b, (long long)base_b, d_item_pairs, d_item_sweeps,
+        n_items, e->d_mat, nl, e->o, e->e, limit_ho, reinterpret_cast<uint4 *>(d_gbnd), (la + 1 + 3) / 4 + 2, d_counter, d_res);
+    return cudaGetLastError();
+}

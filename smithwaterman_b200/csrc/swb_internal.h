@@ -51,6 +51,7 @@ struct swb_engine {
     int16_t *d_code_tab = nullptr;  // byte -> residue code (device copy of code_of)
     // scratch owned by the engine, grown on demand
     void *d_bnd = nullptr; size_t bnd_bytes = 0;
+    void *h_items = nullptr; size_t items_bytes = 0; cudaEvent_t ev_items = nullptr;   // pinned K2 work-item table
     void *h_stage = nullptr; size_t stage_bytes = 0, stage_used = 0;   // pinned results arena of swb_score_batch
     swb_stats stats = {};
     std::string err;
@@ -95,6 +96,11 @@ struct swb_batch {
 cudaError_t k1_launch(const swb_engine *e, const swb_batch *b, int n_blocks, cudaStream_t st);
 size_t k1_bnd_bytes(int n_blocks, int la_max);
 int k1_blocks_per_sm(const swb_engine *e);
+// K2: shared long query, lanes split the columns (database search).
+size_t k2_bnd_bytes(int n_blocks, int la);
+cudaError_t k2_launch(const swb_engine *e, const uint8_t *d_query, int la, const uint8_t *d_codes_b, const int64_t *d_off_b,
+                      int64_t base_b, const int32_t *d_item_pairs, const int32_t *d_item_sweeps, int n_items, void *d_gbnd,
+                      int *d_counter, K1Result *d_res, int n_blocks, cudaStream_t st);
 
 // KW: one warp per pair, exact 3-state int32 recurrence (all modes), optional direction bytes.
 struct KWPair {

@@ -61,8 +61,15 @@ def shard_indices(lengths, world_size):
 
 def topk_records(scores, idx, end_q, end_t, k):
     """Top-k by (score desc, database index asc) -> structured array."""
-    rec = np.empty(len(scores), dtype=[("score", np.float32), ("idx", np.int64), ("end_q", np.int64), ("end_t", np.int64)])
-    rec["score"], rec["idx"], rec["end_q"], rec["end_t"] = scores, idx, end_q, end_t
+    scores = np.asarray(scores, np.float32)
+    n = len(scores)
+    if n > 4 * k > 0:                                         # linear-time selection first: everything scoring >= the k-th value
+        kth = np.partition(scores, n - k)[n - k]
+        sel = np.nonzero(scores >= kth)[0]
+    else:
+        sel = np.arange(n)
+    rec = np.empty(len(sel), dtype=[("score", np.float32), ("idx", np.int64), ("end_q", np.int64), ("end_t", np.int64)])
+    rec["score"], rec["idx"], rec["end_q"], rec["end_t"] = scores[sel], np.asarray(idx)[sel], np.asarray(end_q)[sel], np.asarray(end_t)[sel]
     order = np.lexsort((rec["idx"], -rec["score"].astype(np.float64)))
     return rec[order[:k]]
 

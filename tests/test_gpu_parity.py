@@ -394,3 +394,38 @@ def test_config5_nw_batch_10kb():
         r1, r2, sc = oeng.align(sa[k].decode(), sb[k].decode(), True)
         assert (res[k]["aln_a"], res[k]["aln_b"], res[k]["score"]) == ("".join(r1), "".join(r2), sc)
     eng.close()
+
+
+def test_database_search_long_query_k2():
+    """configs[2] with a long query: the K2 path (lanes of a warp split the columns; subjects bin-packed into warps,
+    subjects of more than 1024 residues swept in several passes of the warp).  Scores and end cells equal the
+    integer oracle; the per-pair K1 path and the top-k alignments agree."""
+    from smithwaterman_b200 import search as S
+    rng = np.random.default_rng(20246)
+    m = swb.SubstitutionMatrix.get_blosum62_matrix()
+    eng = swb.SequenceAlignment(m, 10.0, 0.5, swb.ALIGN_LOCAL)
+    query = _rand_seqs(rng, 1, 1500, 1500)[0]
+    seqs = _rand_seqs(rng, 900, 20, 700) + _rand_seqs(rng, 12, 1025, 3300) + _rand_seqs(rng, 40, 1, 40) + [b"", b"A"]
+    for k in range(0, 900, 45):                                    # planted homologs
+        lo = int(rng.integers(0, 1000)); w = bytearray(query[lo:lo + int(rng.integers(100, 450))])
+        for p in rng.integers(0, len(w), len(w) // 4):
+            w[p] = ord(AA[rng.integers(0, 20)])
+        seqs[k] = bytes(w)
+    seqs[905] = seqs[905][:700] + query[200:1400] + seqs[905][700:]   # a long subject with a long exact match (> 1024 columns)
+    seqs[46] = seqs[45]
+    perm = rng.permutation(len(seqs))
+    seqs = [seqs[k] for k in perm]
+    db = S.Database.from_sequences(seqs)
+    sc, eq, et = S.search_scores(eng, query, db)
+    assert eng.stats()["launches"] >= 1
+    osc, oi, oj = _oracle_scores(m, [query] * len(seqs), seqs, 10.0, 0.5, swb.ALIGN_LOCAL)
+    assert np.array_equal(np.rint(sc.astype(np.float64) * 2).astype(np.int64), osc)
+    nz = osc > 0
+    assert np.array_equal(eq[nz], oi[nz]) and np.array_equal(et[nz], oj[nz])
+    assert (eq[~nz] == -1).all() and (et[~nz] == -1).all()
+    sc2, eq2, et2 = eng.score_batch([query] * len(seqs), seqs)
+    assert np.array_equal(sc, sc2) and np.array_equal(eq, eq2) and np.array_equal(et, et2)
+    hits = S.search(eng, query, db, topk=25, traceback=True, retain_all=False)
+    order = np.lexsort((np.arange(len(seqs)), -osc))[:25]
+    assert [h["idx"] for h in hits] == order.tolist()
+    eng.close()
