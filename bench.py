@@ -225,19 +225,20 @@ def main():
         pass
     hbm_peak = peaks.get("hbm_gbs", 6650.0)
     alg_bytes = float(oa[-1] + ob[-1]) + 16.0 * n                 # residues read once + 16 B result per pair
-    traffic = None                                                # DRAM bytes per K1 launch from the committed ncu capture
+    traffic = None; traffic_detail = None                         # DRAM bytes per K1 launch from the committed ncu capture
     try:
         tr = json.load(open(os.path.join(ROOT, "profiles", "k1_traffic.json")))
         if args.pairs == 1_000_000:
-            traffic = {"bytes_per_launch": tr["dram_bytes_per_launch"], "algorithmic_bytes": alg_bytes, "source": tr["source"],
-                       "note": "the excess over the algorithmic bytes is the 4-byte-per-row pass-boundary column (0.17 B/cell), "
-                               "written and re-read once per 32-column pass; 12 % of HBM peak, not the bound"}
+            traffic = tr["dram_bytes_per_launch"]
+            traffic_detail = {"algorithmic_bytes": alg_bytes, "source": tr["source"],
+                              "note": "the excess over the algorithmic bytes is the 4-byte-per-row pass-boundary column "
+                                      "(0.125 B/cell written + re-read once per 32-column pass); 12 % of HBM peak, not the bound"}
     except Exception:
         pass
     roofline = {"bound": "dpx-int (ALU pipe); see DESIGN.md: the score-only path moves 0.007 B/cell, HBM is not the bound",
                 "achieved": per_gpu, "peak": roof_gcups, "unit": "GCUPS/GPU", "frac": per_gpu / roof_gcups,
                 "peak_source": "K0 micro-benchmark in this run: VIADDMNMX.S16x2 %.2f T thread-instr/s / 2 DPX instr per cell" % (dpx_rate / 1e12),
-                "traffic": traffic,
+                "traffic": traffic, "traffic_detail": traffic_detail,
                 "hbm": {"achieved": alg_bytes / (ms_step * 1e-3) / 1e9, "peak": hbm_peak, "unit": "GB/s",
                         "frac": alg_bytes / (ms_step * 1e-3) / 1e9 / hbm_peak,
                         "peak_source": "MEASURED_PEAKS.json" if peaks else "fallback"}}
