@@ -10,6 +10,7 @@
  *   swb_engine_create      SequenceAlignment::new            SA.rs:26-45   (OCL.rs:103 new)
  *   swb_engine_destroy     Drop of SequenceAlignment / OpenCLSequenceAlignment
  *   swb_align              SequenceAlignment::align          SA.rs:389-392 (OCL.rs:796 align)
+ *   swb_align_pssm         align over a PositionSpecificMatrix  SA.rs:583-623 (ScoringMatrix trait SA.rs:574-580)
  *   swb_align_batch        the serial loop of `sa_opencl -list`  OCL-main.rs:295-316 (one call, n pairs)
  *   swb_score_batch        align_partial(.., score_only=true) per pair  SA.rs:393-467
  *   swb_search_scores      the all-vs-all loops of the CLIs with one fixed query (SA-main.rs:35-45), n subjects per call
@@ -103,6 +104,11 @@ int swb_device_count(void);
 /* One pair with traceback (SA.rs:389).  out is filled on SWB_OK. */
 int swb_align(swb_engine *e, const char *a, int64_t la, const char *b, int64_t lb, int retain_all,
               swb_alignment *out);
+/* One pair scored by a PositionSpecificMatrix (SA.rs:583-623; psm_test SA.rs:1057-1086): the score of (position i of a,
+ * position j of b) is scores[i + j*la] (f32, la*lb values on the engine's penalty grid); the engine's matrix is not used,
+ * the letters only spell the output strings.  Gap penalties and mode are the engine's. */
+int swb_align_pssm(swb_engine *e, const float *scores, const char *a, int64_t la, const char *b, int64_t lb,
+                   int retain_all, swb_alignment *out);
 /* n pairs with traceback; sequences k = a_all[off_a[k]..off_a[k+1]), same for b; outs[n]. */
 int swb_align_batch(swb_engine *e, const char *a_all, const int64_t *off_a, const char *b_all,
                     const int64_t *off_b, int64_t n, unsigned flags, swb_alignment *outs);

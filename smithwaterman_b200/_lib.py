@@ -78,6 +78,7 @@ def lib():
         "swb_get_stats": (c.c_int, [vp, c.POINTER(Stats)]),
         "swb_device_count": (c.c_int, []),
         "swb_align": (c.c_int, [vp, vp, i64, vp, i64, c.c_int, c.POINTER(Alignment)]),
+        "swb_align_pssm": (c.c_int, [vp, vp, vp, i64, vp, i64, c.c_int, c.POINTER(Alignment)]),
         "swb_align_batch": (c.c_int, [vp, vp, vp, vp, vp, i64, c.c_uint, c.POINTER(Alignment)]),
         "swb_alignment_free": (None, [c.POINTER(Alignment)]),
         "swb_score_batch": (c.c_int, [vp, vp, vp, vp, vp, i64, vp, vp, vp]),

@@ -1,6 +1,7 @@
 // Traceback path: swb_align / swb_align_batch.  Mirrors align_partial (SA.rs:393-551): encode ->
 // fill (KW with direction bytes) -> backtrack (KT) -> strings with the retain_all padding rules.
 #include <algorithm>
+#include <cmath>
 #include <cstdlib>
 #include <cstring>
 
@@ -66,8 +67,8 @@ extern "C" void swb_alignment_free(swb_alignment *a)
     memset(a, 0, sizeof(*a));
 }
 
-extern "C" int swb_align_batch(swb_engine *e, const char *a_all, const int64_t *off_a, const char *b_all,
-                               const int64_t *off_b, int64_t n, unsigned flags, swb_alignment *outs)
+static int align_batch_impl(swb_engine *e, const char *a_all, const int64_t *off_a, const char *b_all,
+                            const int64_t *off_b, int64_t n, unsigned flags, swb_alignment *outs, const float *pssm)
 {
     if (!e) return SWB_ERR_ARG;
     if (n < 0 || (n > 0 && (!off_a || !off_b || !outs))) { e->err = "bad argument"; return SWB_ERR_ARG; }
@@ -82,8 +83,8 @@ extern "C" int swb_align_batch(swb_engine *e, const char *a_all, const int64_t *
     // encode on the host (small inputs on this path); unknown letters as SA.rs:669-679
     const int64_t na = n ? off_a[n] : 0, nb = n ? off_b[n] : 0;
     std::vector<uint8_t> ca(na + 16), cb(nb + 16);
-    for (int64_t k = 0; k < na; ++k) { int c = e->code_of[(unsigned char)a_all[k]]; if (c < 0) { e->err = std::string("unknown letter ") + a_all[k] + ". please set X to allow scoring for undefined letter pair."; return SWB_ERR_LETTER; } ca[k] = (uint8_t)c; }
-    for (int64_t k = 0; k < nb; ++k) { int c = e->code_of[(unsigned char)b_all[k]]; if (c < 0) { e->err = std::string("unknown letter ") + b_all[k] + ". please set X to allow scoring for undefined letter pair."; return SWB_ERR_LETTER; } cb[k] = (uint8_t)c; }
+    for (int64_t k = 0; k < na && !pssm; ++k) { int c = e->code_of[(unsigned char)a_all[k]]; if (c < 0) { e->err = std::string("unknown letter ") + a_all[k] + ". please set X to allow scoring for undefined letter pair."; return SWB_ERR_LETTER; } ca[k] = (uint8_t)c; }
+    for (int64_t k = 0; k < nb && !pssm; ++k) { int c = e->code_of[(unsigned char)b_all[k]]; if (c < 0) { e->err = std::string("unknown letter ") + b_all[k] + ". please set X to allow scoring for undefined letter pair."; return SWB_ERR_LETTER; } cb[k] = (uint8_t)c; }
 
     std::vector<int64_t> work;                       // pairs that need the device
     for (int64_t k = 0; k < n; ++k) {
@@ -107,7 +108,19 @@ extern "C" int swb_align_batch(swb_engine *e, const char *a_all, const int64_t *
     }
     if (work.empty()) return SWB_OK;
 
-    DevBuf d_a, d_b;
+    DevBuf d_a, d_b, d_pssm;
+    if (pssm) {                                      // PositionSpecificMatrix (SA.rs:583-623): scores[a + b*a_length] on the engine's grid
+        const size_t np_ = (size_t)na * (size_t)nb;
+        std::vector<int32_t> ps(np_ ? np_ : 1);
+        for (size_t k = 0; k < np_; ++k) {
+            const double v = (double)pssm[k] * e->scale, r = std::nearbyint(v);
+            if (std::fabs(v - r) > 1e-4 * e->scale || std::fabs(r) > 8000) { e->err = "position-specific scores are not on the engine's integer grid (or exceed 8000)"; return SWB_ERR_SCALE; }
+            ps[k] = (int32_t)r;
+        }
+        CUDA_TRY(e, cudaMalloc(&d_pssm.p, ps.size() * sizeof(int32_t)));
+        CUDA_TRY(e, cudaMemcpy(d_pssm.p, ps.data(), ps.size() * sizeof(int32_t), cudaMemcpyHostToDevice));
+        e->stats.h2d_bytes += (double)ps.size() * sizeof(int32_t);
+    }
     CUDA_TRY(e, cudaMalloc(&d_a.p, ca.size())); CUDA_TRY(e, cudaMalloc(&d_b.p, cb.size()));
     CUDA_TRY(e, cudaMemcpyAsync(d_a.p, ca.data(), ca.size(), cudaMemcpyHostToDevice, e->stream));
     CUDA_TRY(e, cudaMemcpyAsync(d_b.p, cb.data(), cb.size(), cudaMemcpyHostToDevice, e->stream));
@@ -124,7 +137,7 @@ extern "C" int swb_align_batch(swb_engine *e, const char *a_all, const int64_t *
             const int32_t la = (int32_t)(off_a[k + 1] - off_a[k]), lb = (int32_t)(off_b[k + 1] - off_b[k]);
             const int64_t db = kw_dir_bytes(la, lb, 8);              // upper bound over both strip widths
             if (!hp.empty() && dir_total + db > DIR_BUDGET_BYTES) break;
-            KWPair P; P.a_off = off_a[k]; P.b_off = off_b[k]; P.la = la; P.lb = lb; P.dir_off = dir_total; P.bnd_off = 0; P.scr_off = 0;
+            KWPair P; P.a_off = off_a[k]; P.b_off = off_b[k]; P.la = la; P.lb = lb; P.dir_off = dir_total; P.bnd_off = 0; P.scr_off = 0; P.pssm_off = pssm ? 0 : -1;
             hp.push_back(P); out_off.push_back(out_total);
             dir_total += db; out_total += (int64_t)la + lb + 1;
             ++end;
@@ -143,7 +156,7 @@ extern "C" int swb_align_batch(swb_engine *e, const char *a_all, const int64_t *
         CUDA_TRY(e, cudaMemcpyAsync(d_off.p, out_off.data(), np * sizeof(int64_t), cudaMemcpyHostToDevice, e->stream));
         CUDA_TRY(e, cudaEventRecord(e->ev0, e->stream));
         CUDA_TRY(e, kw_launch(e, d_a.as<uint8_t>(), d_b.as<uint8_t>(), d_pairs.as<KWPair>(), np, plan, d_dir.as<uint8_t>(),
-                              d_bnd.as<int4>(), d_scr.as<int>(), d_res.as<KWResult>(), e->stream));
+                              d_bnd.as<int4>(), d_scr.as<int>(), d_res.as<KWResult>(), e->stream, d_pssm.as<int32_t>()));
         CUDA_TRY(e, kt_launch(e, d_pairs.as<KWPair>(), d_res.as<KWResult>(), np, d_dir.as<uint8_t>(), plan.cols, d_off.as<int64_t>(),
                               d_xa.as<int32_t>(), d_xb.as<int32_t>(), d_nc.as<int32_t>(), e->stream));
         CUDA_TRY(e, cudaEventRecord(e->ev1, e->stream));
@@ -173,6 +186,23 @@ extern "C" int swb_align_batch(swb_engine *e, const char *a_all, const int64_t *
         pos = end;
     }
     return SWB_OK;
+}
+
+extern "C" int swb_align_batch(swb_engine *e, const char *a_all, const int64_t *off_a, const char *b_all,
+                               const int64_t *off_b, int64_t n, unsigned flags, swb_alignment *outs)
+{
+    return align_batch_impl(e, a_all, off_a, b_all, off_b, n, flags, outs, nullptr);
+}
+
+// align() of an engine built over a PositionSpecificMatrix (SA.rs:583-623, KAT psm_test SA.rs:1057-1086): the score of
+// (position i of a, position j of b) is scores[i + j*la]; the letters are only used for the output strings.
+extern "C" int swb_align_pssm(swb_engine *e, const float *scores, const char *a, int64_t la, const char *b, int64_t lb,
+                              int retain_all, swb_alignment *out)
+{
+    if (!e) return SWB_ERR_ARG;
+    if (!out || !scores || la < 1 || lb < 1 || !a || !b) { e->err = "bad argument (position-specific alignment needs two non-empty sequences)"; return SWB_ERR_ARG; }
+    const int64_t oa[2] = {0, la}, ob[2] = {0, lb};
+    return align_batch_impl(e, a, oa, b, ob, 1, retain_all ? SWB_RETAIN_ALL : 0u, out, scores);
 }
 
 extern "C" int swb_align(swb_engine *e, const char *a, int64_t la, const char *b, int64_t lb, int retain_all,

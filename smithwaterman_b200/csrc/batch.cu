@@ -367,7 +367,7 @@ static int batch_upload_impl(swb_engine *e, const char *a_all, const int64_t *of
             const int32_t k = d->kw_idx[t];
             KWPair &P = d->h_kw[t];
             P.a_off = shared ? 0 : off_a[k] - d->base_a; P.b_off = off_b[k] - d->base_b; P.la = b->la[k]; P.lb = b->lb[k];
-            P.dir_off = -1;
+            P.dir_off = -1; P.pssm_off = -1;
         }
         kw_plan(e, d->h_kw.data(), d->n_kw, false, &d->kw_plan_);
         DEV_ALLOC_ON(e, up, d->kw_pairs, d->n_kw * sizeof(KWPair));
@@ -541,7 +541,7 @@ static int batch_fetch_finish(swb_engine *e, swb_batch *b, float *scores, int64_
         for (int t = 0; t < nr; ++t) {
             const int32_t k = redo[t];
             hp[t].a_off = d->shared_la >= 0 ? 0 : oa[k] - d->base_a; hp[t].b_off = ob[k] - d->base_b; hp[t].la = b->la[k]; hp[t].lb = b->lb[k];
-            hp[t].dir_off = -1;
+            hp[t].dir_off = -1; hp[t].pssm_off = -1;
         }
         KWPlan pl; kw_plan(e, hp.data(), nr, false, &pl);
         KWPair *dp = nullptr; KWResult *dr = nullptr; int4 *db = nullptr; int *ds = nullptr;

@@ -80,7 +80,8 @@ template <int MODE, bool DIRS, int C>
 __global__ void __launch_bounds__(KW_WARPS * 32)
 kw_kernel(const uint8_t *__restrict__ a_all, const uint8_t *__restrict__ b_all, const KWPair *__restrict__ pairs,
           int n_pairs, int team_warps, int n_teams, const int32_t *__restrict__ mat, int nl, int o, int e, int unit,
-          uint8_t *__restrict__ dir, int4 *__restrict__ bnd, int *__restrict__ scratch, KWResult *__restrict__ res)
+          uint8_t *__restrict__ dir, int4 *__restrict__ bnd, int *__restrict__ scratch, KWResult *__restrict__ res,
+          const int32_t *__restrict__ pssm_all)
 {
     constexpr int SW = 32 * C;
     typedef typename KWCodes<C>::T codes_t;
@@ -103,6 +104,8 @@ kw_kernel(const uint8_t *__restrict__ a_all, const uint8_t *__restrict__ b_all, 
         const KWPair P = pairs[pidx];
         const uint8_t *a = a_all + P.a_off, *b = b_all + P.b_off;
         const int la = P.la, lb = P.lb;
+        // PositionSpecificMatrix (SA.rs:583-623): score of (row i, column j) = scores[(i-1) + (j-1)*la]
+        const int32_t *pssm = (pssm_all != nullptr && P.pssm_off >= 0) ? pssm_all + P.pssm_off : nullptr;
         const int n_strips = (lb + SW - 1) / SW;
         const int nbuf = min(n_strips, team_warps + 1);
         int *counter = scratch + P.scr_off;                    // [0] arrivals, [1..n_strips] rows published per strip,
@@ -127,7 +130,7 @@ kw_kernel(const uint8_t *__restrict__ a_all, const uint8_t *__restrict__ b_all, 
                 const int ls = j * se + (so - se);             // SA.rs:100-104: X = ls, M = Y = ls + sentinel, prev = GAPINX
                 Mu[c] = ls + sent; Xu[c] = ls; Yu[c] = ls + sent;
                 Hu[c] = __vimax3_s32(Mu[c], Xu[c], Yu[c]); Au[c] = kw_am(Mu[c], Xu[c], Yu[c]);
-                boff[c] = (j <= lb) ? (int)b[j - 1] : (nl - 1);
+                boff[c] = (j <= lb) ? (pssm ? 0 : (int)b[j - 1]) : (nl - 1);
             }
             int hd0; unsigned ad0;                             // diagonal of column 0 at the next row: cell (row-1, j0)
             if (j0 == 0) { hd0 = 0; ad0 = 0u; }                // (0,0): M = 0, X = Y = -1 (SA.rs:88-93)
@@ -172,12 +175,21 @@ kw_kernel(const uint8_t *__restrict__ a_all, const uint8_t *__restrict__ b_all, 
                     hd0 = __vimax3_s32(tM, tX, tY); ad0 = kw_am(tM, tX, tY);     // next row's diagonal for column 0
                     codes_t codes = 0;
                     const int sb_in = sb;
+                    int sv[C];
+                    if (pssm) {
+#pragma unroll
+                        for (int c = 0; c < C; ++c)
+                            sv[c] = (boff[c] != nl - 1) ? __ldg(pssm + (i - 1) + (int64_t)(j0 + c) * la) : NEG_INF_I32;
+                    } else {
+#pragma unroll
+                        for (int c = 0; c < C; ++c) sv[c] = mrow[boff[c]];
+                    }
 #pragma unroll
                     for (int c = 0; c < C; ++c) {
                         const int qo = (MODE == SWB_GLOCAL && c == own) ? so : o; // SA.rs:169-170 (column lb)
                         const int qe = (MODE == SWB_GLOCAL && c == own) ? se : e;
                         int m, x, y; unsigned code;
-                        kw_cell<MODE>(hd, ad, tM, tX, tY, Mu[c], Xu[c], Yu[c], mrow[boff[c]], po, pe, qo, qe, m, x, y, code);
+                        kw_cell<MODE>(hd, ad, tM, tX, tY, Mu[c], Xu[c], Yu[c], sv[c], po, pe, qo, qe, m, x, y, code);
                         hd = Hu[c]; ad = Au[c];
                         Mu[c] = m; Xu[c] = x; Yu[c] = y;
                         Hu[c] = __vimax3_s32(m, x, y); Au[c] = kw_am(m, x, y);
@@ -323,7 +335,7 @@ void kw_plan(const swb_engine *e, KWPair *pairs, int n_pairs, bool with_dirs, KW
 template <int MODE, int C>
 static cudaError_t kw_launch_mode(const swb_engine *e, const uint8_t *d_a, const uint8_t *d_b, const KWPair *d_pairs,
                                   int n_pairs, const KWPlan &pl, uint8_t *d_dir, int4 *d_bnd, int *d_scratch,
-                                  KWResult *d_res, cudaStream_t st)
+                                  KWResult *d_res, cudaStream_t st, const int32_t *d_pssm)
 {
     const int nl = e->n + 1;
     const size_t smem = (size_t)nl * nl * sizeof(int);
@@ -332,20 +344,21 @@ static cudaError_t kw_launch_mode(const swb_engine *e, const uint8_t *d_a, const
     if (d_dir)
         kw_kernel<MODE, true, C><<<pl.blocks, KW_WARPS * 32, smem, st>>>(d_a, d_b, d_pairs, n_pairs, pl.team_warps, pl.n_teams,
                                                                          e->d_mat, nl, e->o, e->e, e->scale, d_dir, d_bnd,
-                                                                         d_scratch, d_res);
+                                                                         d_scratch, d_res, d_pssm);
     else
         kw_kernel<MODE, false, C><<<pl.blocks, KW_WARPS * 32, smem, st>>>(d_a, d_b, d_pairs, n_pairs, pl.team_warps, pl.n_teams,
                                                                           e->d_mat, nl, e->o, e->e, e->scale, d_dir, d_bnd,
-                                                                          d_scratch, d_res);
+                                                                          d_scratch, d_res, d_pssm);
     return cudaGetLastError();
 }
 
 cudaError_t kw_launch(const swb_engine *e, const uint8_t *d_a, const uint8_t *d_b, const KWPair *d_pairs, int n_pairs,
-                      const KWPlan &plan, uint8_t *d_dir, int4 *d_bnd, int *d_scratch, KWResult *d_res, cudaStream_t st)
+                      const KWPlan &plan, uint8_t *d_dir, int4 *d_bnd, int *d_scratch, KWResult *d_res, cudaStream_t st,
+                      const int32_t *d_pssm)
 {
     if (n_pairs <= 0) return cudaSuccess;
-#define KW_GO(M) (plan.cols == 2 ? kw_launch_mode<M, 2>(e, d_a, d_b, d_pairs, n_pairs, plan, d_dir, d_bnd, d_scratch, d_res, st) \
-                                 : kw_launch_mode<M, 8>(e, d_a, d_b, d_pairs, n_pairs, plan, d_dir, d_bnd, d_scratch, d_res, st))
+#define KW_GO(M) (plan.cols == 2 ? kw_launch_mode<M, 2>(e, d_a, d_b, d_pairs, n_pairs, plan, d_dir, d_bnd, d_scratch, d_res, st, d_pssm) \
+                                 : kw_launch_mode<M, 8>(e, d_a, d_b, d_pairs, n_pairs, plan, d_dir, d_bnd, d_scratch, d_res, st, d_pssm))
     switch (e->mode) {
     case SWB_GLOBAL: return KW_GO(SWB_GLOBAL);
     case SWB_GLOCAL: return KW_GO(SWB_GLOCAL);

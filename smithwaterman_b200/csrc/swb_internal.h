@@ -109,6 +109,7 @@ struct KWPair {
     int64_t dir_off;                // offset of this pair's direction bytes (skewed layout), -1 = none
     int64_t bnd_off;                // offset (in int4 units) of the strip-boundary ring   (filled by kw_plan)
     int64_t scr_off;                // offset (in ints) of the pair's team scratch          (filled by kw_plan)
+    int64_t pssm_off;               // offset (in ints) of the pair's position-specific scores [b][a], -1 = use the matrix
 };
 struct KWPlan {
     int cols = 8;                   // DP columns per lane (strip width 32*cols): 8, or 2 for a few long pairs
@@ -126,7 +127,7 @@ struct KWResult {
 };
 cudaError_t kw_launch(const swb_engine *e, const uint8_t *d_a, const uint8_t *d_b, const KWPair *d_pairs,
                       int n_pairs, const KWPlan &plan, uint8_t *d_dir, int4 *d_bnd, int *d_scratch, KWResult *d_res,
-                      cudaStream_t st);
+                      cudaStream_t st, const int32_t *d_pssm = nullptr);
 int64_t kw_dir_bytes(int32_t la, int32_t lb, int cols);   // bytes of the skewed direction store of one pair
 // KT: pointer walk over the direction bytes; one thread per pair.  Writes reversed column lists.
 cudaError_t kt_launch(const swb_engine *e, const KWPair *d_pairs, const KWResult *d_res, int n_pairs,

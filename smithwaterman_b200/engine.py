@@ -94,6 +94,27 @@ class SubstitutionMatrix:
         return float(self.scores[a, b])
 
 
+class PositionSpecificMatrix:
+    """PositionSpecificMatrix of SA.rs:583-623: scores[a + b*a_length] for position a of seq1 and b of seq2."""
+
+    def __init__(self):
+        self.scores, self.a_length, self.b_length = np.zeros(0, np.float32), 0, 0
+
+    def prepare(self, a, b):                                  # SA.rs:604-610
+        self.a_length, self.b_length = len(_as_seq_bytes(a)), len(_as_seq_bytes(b))
+        if self.a_length * self.b_length > len(self.scores):
+            self.scores = np.zeros(self.a_length * self.b_length, np.float32)
+
+    def get_score(self, a, b):                                # SA.rs:593-595
+        return float(self.scores[a + b * self.a_length])
+
+    def set_score(self, a, b, s):                             # SA.rs:601-603
+        self.scores[a + b * self.a_length] = s
+
+    def get_score_str(self, a, b):                            # SA.rs:590-592
+        raise NotImplementedError("not implemented")
+
+
 class SeqData:
     """name, desc, seq (list of one-letter strings); SA.rs:799-803."""
 
@@ -161,9 +182,13 @@ class SequenceAlignment:
         self._h = None
         self.L = _lib.lib()
         self.scoring_matrix, self.alignment_type = ss, int(alignment_type)
-        letters = "".join(ss.index_to_string).encode("latin-1")
+        self._pssm = isinstance(ss, PositionSpecificMatrix)
+        if self._pssm:                                        # the engine only carries penalties and mode; a 1-letter dummy matrix
+            letters, scores = b"X", np.zeros(1, np.float32)
+        else:
+            letters, scores = "".join(ss.index_to_string).encode("latin-1"), ss.scores
         self._letters = ctypes.create_string_buffer(letters, len(letters))
-        self._scores = np.ascontiguousarray(ss.scores, np.float32)
+        self._scores = np.ascontiguousarray(scores, np.float32)
         m = _lib.Matrix(len(letters), ctypes.cast(self._letters, ctypes.c_char_p),
                         self._scores.ctypes.data_as(ctypes.POINTER(ctypes.c_float)))
         h = ctypes.c_void_p()
@@ -192,6 +217,10 @@ class SequenceAlignment:
         self._check(self.L.swb_get_stats(self._h, ctypes.byref(st)))
         return {k: getattr(st, k) for k, _ in st._fields_}
 
+    def prepare(self, s1, s2):                                # SA.rs:47-50: sizes the position-specific matrix
+        if self._pssm:
+            self.scoring_matrix.prepare(s1, s2)
+
     # -- single pair, SA.rs:389-551 -------------------------------------------------------------
     def align(self, s1, s2, retain_all=True):
         return self.align_partial(s1, s2, retain_all, None, False)
@@ -209,7 +238,14 @@ class SequenceAlignment:
     def align_raw(self, a, b, retain_all=True):
         a, b = _as_seq_bytes(a), _as_seq_bytes(b)
         out = _lib.Alignment()
-        self._check(self.L.swb_align(self._h, a, len(a), b, len(b), int(bool(retain_all)), ctypes.byref(out)))
+        if self._pssm:
+            pm = self.scoring_matrix
+            if (pm.a_length, pm.b_length) != (len(a), len(b)):
+                raise SwbError(1, "PositionSpecificMatrix was prepared for other lengths (SA.rs:604-610)")
+            sc = np.ascontiguousarray(pm.scores[:len(a) * len(b)], np.float32)
+            self._check(self.L.swb_align_pssm(self._h, sc.ctypes.data, a, len(a), b, len(b), int(bool(retain_all)), ctypes.byref(out)))
+        else:
+            self._check(self.L.swb_align(self._h, a, len(a), b, len(b), int(bool(retain_all)), ctypes.byref(out)))
         try:
             return self._unpack(out)
         finally:

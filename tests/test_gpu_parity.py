@@ -25,10 +25,22 @@ def _omatrix(m):
 
 
 def test_rust_kats(rust_kats):
-    """SA.rs:921-1221 / OCL.rs:1292-1448 known answers (the PSSM case is a 'next' row)."""
-    done = 0
+    """SA.rs:921-1221 / OCL.rs:1292-1448 known answers, including the position-specific-matrix case."""
+    done = 0; n_pssm = 0
     for c in rust_kats:
-        if c["pssm"]:
+        if c["pssm"]:                                              # psm_test SA.rs:1057-1086: PositionSpecificMatrix filled from BLOSUM62
+            sm = _matrix(c["matrix"])
+            pm = swb.PositionSpecificMatrix()
+            eng = swb.SequenceAlignment(pm, c["go"], c["ge"], c["mode"])
+            eng.prepare(c["seq1"], c["seq2"])
+            i1 = [sm.string_to_index.get(x, sm.string_to_index["X"]) for x in c["seq1"]]
+            i2 = [sm.string_to_index.get(x, sm.string_to_index["X"]) for x in c["seq2"]]
+            pm.scores[:len(i1) * len(i2)] = sm.scores[np.ix_(i2, i1)].reshape(-1)      # scores[a + b*a_length]
+            assert pm.get_score(3, 5) == sm.scores[i1[3], i2[5]]
+            r1, r2, sc = eng.align(c["seq1"], c["seq2"], c["retain_all"])
+            assert (sc, "".join(r1), "".join(r2)) == (c["score"], c["r1"], c["r2"]), c["test"]
+            eng.close()
+            n_pssm += 1
             continue
         eng = swb.SequenceAlignment(_matrix(c["matrix"]), c["go"], c["ge"], c["mode"])
         r1, r2, sc = eng.align(swb.SeqData.create("", "", c["seq1"]), swb.SeqData.create("", "", c["seq2"]), c["retain_all"])
@@ -39,7 +51,7 @@ def test_rust_kats(rust_kats):
             assert "".join(r2) == c["r2"], c["test"]
         done += 1
         eng.close()
-    assert done == 25
+    assert done == 25 and n_pssm == 1
 
 
 @pytest.mark.parametrize("mode,key", [(swb.ALIGN_LOCAL, "local"), (swb.ALIGN_GLOCAL, "glocal"), (swb.ALIGN_GLOBAL, "global")])
