@@ -441,3 +441,31 @@ def test_database_search_long_query_k2():
     order = np.lexsort((np.arange(len(seqs)), -osc))[:25]
     assert [h["idx"] for h in hits] == order.tolist()
     eng.close()
+
+
+@pytest.mark.parametrize("flag,key", [("-local", "local"), ("-glocal", "glocal"), ("-global", "global")])
+def test_cli_list_mode_vs_emboss(emboss, flag, key, tmp_path):
+    """The reference's harness in one test (test/run_rust_list.pl + check_results.pl): `sa_opencl [-mode] -list L` over
+    FASTA files, stdout records parsed and compared with test/emboss_results (strings; local after trimTerminal)."""
+    import io
+    from smithwaterman_b200 import cli
+    recs = emboss[:40]
+    lines = []
+    for r in recs:
+        f1, f2 = tmp_path / ("seq%s.1.fas" % r["id"]), tmp_path / ("seq%s.2.fas" % r["id"])
+        f1.write_text(">a%s some description\n%s\n" % (r["id"], "\n".join(r["seq1"][k:k + 60] for k in range(0, len(r["seq1"]), 60))))
+        f2.write_text(">b%s\n%s\n" % (r["id"], r["seq2"]))
+        lines.append("%s\t%s" % (f1, f2))
+    (tmp_path / "list.txt").write_text("\n".join(lines) + "\n")
+    out = io.StringIO()
+    assert cli.main([flag, "-list", str(tmp_path / "list.txt")], out) == 0
+    blocks = out.getvalue().split("#score:")[1:]
+    assert len(blocks) == len(recs)
+    for r, blk in zip(recs, blocks):
+        ln = blk.split("\n")
+        assert ln[1] == "#type:%s alignment" % key.capitalize() and ln[2] == ">a%s" % r["id"] and ln[5] == ">b%s" % r["id"]
+        s1, s2 = ln[3], ln[6]
+        if key == "local":
+            s1, s2 = trim_terminal(s1, s2)
+        assert (s1, s2) == (r[key]["s1"], r[key]["s2"]), r["id"]
+        assert float(ln[0]) == r[key]["score"]
