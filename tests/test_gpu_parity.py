@@ -469,3 +469,43 @@ def test_cli_list_mode_vs_emboss(emboss, flag, key, tmp_path):
             s1, s2 = trim_terminal(s1, s2)
         assert (s1, s2) == (r[key]["s1"], r[key]["s2"]), r["id"]
         assert float(ln[0]) == r[key]["score"]
+
+
+@pytest.mark.parametrize("seed", range(6))
+def test_fuzz_random_models(seed):
+    """Random scoring models (random integer / half-integer matrices over a random alphabet with X, random penalties
+    including open < extend, which K1 must hand to the exact 3-state kernel), all three modes, lengths 0..90 with
+    low-complexity sequences (many ties): score batch and full alignments vs the oracle."""
+    rng = np.random.default_rng(9000 + seed)
+    nlet = int(rng.integers(3, 12))
+    letters = "X" + "".join(rng.choice(list("ACDEFGHIKLMNPQRSTVWY"), nlet - 1, replace=False))
+    step = [1.0, 0.5][seed % 2]
+    sym = rng.integers(-8, 9, (nlet, nlet)).astype(np.float32) * step
+    sym = np.triu(sym) + np.triu(sym, 1).T
+    sym[np.arange(nlet), np.arange(nlet)] = np.abs(sym[np.arange(nlet), np.arange(nlet)]) + step
+    m = swb.SubstitutionMatrix(letters, sym)
+    go = float(rng.integers(1, 24)) * step
+    ge = float(rng.integers(0, 8)) * step if seed != 3 else go + 2 * step     # seed 3: extend dearer than open
+    om = _omatrix(m)
+    scale = 1 if step == 1.0 and float(go).is_integer() and float(ge).is_integer() else 2
+    alpha = letters[1:] + "xb"                                              # unknown letters -> X
+    for mode in (swb.ALIGN_LOCAL, swb.ALIGN_GLOCAL, swb.ALIGN_GLOBAL):
+        eng = swb.SequenceAlignment(m, go, ge, mode)
+        assert eng.stats()["scale"] == scale
+        sa = _rand_seqs(rng, 260, 0, 90, alpha) + [b"", b"", bytes(alpha[0], "ascii") * 40]
+        sb = _rand_seqs(rng, 260, 0, 90, alpha[:3] + alpha[:2]) + [b"", bytes(alpha[1], "ascii") * 7, bytes(alpha[0], "ascii") * 33]
+        keep = [k for k in range(len(sa)) if mode == swb.ALIGN_LOCAL or len(sa[k]) + len(sb[k]) > 0]
+        sa, sb = [sa[k] for k in keep], [sb[k] for k in keep]
+        sc, ea, eb = eng.score_batch(sa, sb)
+        a, oa = O.pack([om.seq_to_index(s.decode()) for s in sa]); b, ob = O.pack([om.seq_to_index(s.decode()) for s in sb])
+        osc, oi, oj = O.score_batch_int(a, oa, b, ob, np.rint(m.scores * scale).astype(np.int32), -int(round(go * scale)),
+                                        -int(round(ge * scale)), scale, mode, 8)
+        assert np.array_equal(np.rint(sc.astype(np.float64) * scale).astype(np.int64), osc), (seed, mode)
+        assert np.array_equal(ea, oi) and np.array_equal(eb, oj), (seed, mode)
+        oeng = O.Engine(om, go, ge, mode)
+        sel = [k for k in range(0, len(sa), 4) if not (go + ge == 0 and (len(sa[k]) == 0 or len(sb[k]) == 0))]
+        res = eng.align_list([sa[k] for k in sel], [sb[k] for k in sel], bool(seed & 1))
+        for k, out in zip(sel, res):
+            r1, r2, s = oeng.align(sa[k].decode(), sb[k].decode(), bool(seed & 1))
+            assert (out["aln_a"], out["aln_b"], out["score"]) == ("".join(r1), "".join(r2), s), (seed, mode, k)
+        eng.close()
