@@ -109,6 +109,48 @@ def _idx(m, raw):
     return lut[raw]
 
 
+def other_configs(swb, dev):
+    """configs[2] (5000-aa query vs 1e8-residue database, score stage through swb_search_scores, host buffers),
+    configs[3] (one 50 kb x 50 kb DNA pair, +2/-3 5/2, local, full traceback) and configs[4] (64 x 10 kb global DNA
+    pairs with strings) -- wall-clock GCUPS of the public calls after one warm-up call each."""
+    sys.path.insert(0, os.path.join(ROOT, "tools"))
+    import search_bench as SB
+    from smithwaterman_b200 import search as S
+    out = {}
+    q, res, off = SB.make_db(5000, int(1e8))
+    db = S.Database(res, off)
+    eng = swb.SequenceAlignment(swb.SubstitutionMatrix.get_blosum62_matrix(), 10.0, 0.5, swb.ALIGN_LOCAL, device=dev)
+    S.search_scores(eng, q, db)
+    t0 = time.perf_counter(); sc, _, _ = S.search_scores(eng, q, db); dt = time.perf_counter() - t0
+    out["configs[2] search 5000 aa x 1e8 residues, score stage"] = {"gcups": 5000.0 * float(off[-1]) / dt / 1e9, "seconds": dt,
+                                                                    "device_ms": eng.stats()["kernel_ms"], "top_score": float(sc.max())}
+    eng.close()
+    rng = np.random.default_rng(SEED + 3)
+    nt = np.frombuffer(b"ACGT", np.uint8)
+
+    def noisy(n, length, sub, indel):
+        sa, sb = [], []
+        for _ in range(n):
+            a = nt[rng.integers(0, 4, length)]
+            b = a.copy(); m = rng.random(length) < sub; b[m] = nt[rng.integers(0, 4, int(m.sum()))]
+            b = b[rng.random(length) >= indel]
+            pos = np.nonzero(rng.random(len(b)) < indel)[0]
+            b = np.insert(b, pos, nt[rng.integers(0, 4, len(pos))])
+            sa.append(a.tobytes()); sb.append(b.tobytes())
+        return sa, sb
+    dna = swb.SubstitutionMatrix.get_mat_matrix(2.0, -3.0)
+    for tag, mode, n, length, sub, indel in (("configs[3] 50 kb x 50 kb DNA pair, local, full traceback", swb.ALIGN_LOCAL, 1, 50000, 0.08, 0.02),
+                                             ("configs[4] 64 x 10 kb DNA pairs, global, strings", swb.ALIGN_GLOBAL, 64, 10000, 0.05, 0.05)):
+        sa, sb = noisy(n, length, sub, indel)
+        eng = swb.SequenceAlignment(dna, 5.0, 2.0, mode, device=dev)
+        eng.align_list(sa[:1], sb[:1], True)
+        t0 = time.perf_counter(); r = eng.align_list(sa, sb, True); dt = time.perf_counter() - t0
+        cells = float(sum(len(x) * len(y) for x, y in zip(sa, sb)))
+        out[tag] = {"gcups": cells / dt / 1e9, "seconds": dt, "device_ms": eng.stats()["kernel_ms"], "score0": r[0]["score"]}
+        eng.close()
+    return out
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -117,6 +159,7 @@ def main():
     ap.add_argument("--pairs", type=int, default=1_000_000)
     ap.add_argument("--impl", default="swb200")
     ap.add_argument("--cpu-seconds", type=float, default=10.0)
+    ap.add_argument("--no-extras", action="store_true", help="skip the side measurements of configs[2..4]")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
@@ -248,13 +291,20 @@ def main():
         g, k, ccells, dt = cpu_reference_gcups(a, oa, b, ob, args.cpu_seconds, threads)
         cpu = {"value": g, "unit": "GCUPS", "cores": threads, "kind": "port",
                "sample": "first %d pairs of the workload (%.3g cells, %.1f s): dense f32 fill + score scan of the reference, OpenMP over pairs" % (k, ccells, dt)}
+    # ---- the other BASELINE configs, bounded sizes, N = 1 only: reported beside the headline, not part of it
+    extras = None
+    if world == 1 and not args.no_extras:
+        try:
+            extras = other_configs(swb, local_rank)
+        except Exception as ex:                                   # never lose the bench line over the side measurements
+            extras = {"error": repr(ex)}
     line = {"metric": "GCUPS", "value": value, "unit": "GCUPS", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "s16x2 (int32 re-run)",
             "data": "synthetic", "config": config, "clocks": sampler.summary(),
             "e2e": {"value": e2e_val, "unit": "GCUPS", "h2d_bytes_per_step": st["h2d_bytes"], "d2h_bytes_per_step": st["d2h_bytes"],
                     "ms_per_step": e2e_ms, "steps": e2e_steps},
             "gpu_launches": int(launches), "roofline": roofline, "cpu_baseline": cpu,
-            "i32_reruns": int(reruns), "cells_per_step": tot_cells}
+            "i32_reruns": int(reruns), "cells_per_step": tot_cells, "other_configs": extras}
     print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()
