@@ -24,6 +24,7 @@
 #include "swb_internal.h"
 
 #define KW_WARPS 8
+#define KT_AHEAD 16
 #define NEG_INF_I32 (-(1 << 29))
 
 int64_t kw_dir_bytes(int32_t la, int32_t lb, int cols)
@@ -371,19 +372,20 @@ cudaError_t kw_launch(const swb_engine *e, const uint8_t *d_a, const uint8_t *d_
 // KT: backtrack (SA.rs:346-383).  One thread per pair follows the 2-bit predecessor codes from the
 // start cell and emits the column lists in walk order (end -> start); the host reverses them
 // (SA.rs:384-385).  idx value -1 = gap.  n_cols < 0 reports the reference's panic cases.
-__device__ __forceinline__ unsigned kt_code(const uint8_t *dir, int64_t dir_off, int la, int i, int j, int state, int cols)
+template <int COLS>
+__device__ __forceinline__ int64_t kt_addr(int64_t dir_off, int la, int i, int j)
 {
-    const int jj = j - 1, sw = 32 * cols;
-    const int sidx = jj / sw, within = jj - sidx * sw;
-    const int t = (i - 1) + within / cols;
-    const uint8_t byte = dir[dir_off + ((int64_t)sidx * (la + 31) + t) * sw + within];
-    return (byte >> (2 * state)) & 3u;
+    constexpr int SW = 32 * COLS;                       // compile-time strip geometry: shifts, no divisions, in the walk
+    const int jj = j - 1;
+    const int sidx = jj / SW, within = jj % SW;
+    const int t = (i - 1) + within / COLS;
+    return dir_off + ((int64_t)sidx * (la + 31) + t) * SW + within;
 }
 
-template <int MODE>
+template <int MODE, int COLS>
 __global__ void kt_kernel(const KWPair *__restrict__ pairs, const KWResult *__restrict__ res, int n_pairs,
                           const uint8_t *__restrict__ dir, const int64_t *__restrict__ out_off,
-                          int32_t *__restrict__ idx_a, int32_t *__restrict__ idx_b, int32_t *__restrict__ ncols, int sent, int cols)
+                          int32_t *__restrict__ idx_a, int32_t *__restrict__ idx_b, int32_t *__restrict__ ncols, int sent)
 {
     const int p = blockIdx.x * blockDim.x + threadIdx.x;
     if (p >= n_pairs) return;
@@ -395,7 +397,12 @@ __global__ void kt_kernel(const KWPair *__restrict__ pairs, const KWResult *__re
     int cx = R.end_i, cy = R.end_j, st = R.state;
     for (;;) {
         unsigned prev;
-        if (cx >= 1 && cy >= 1) prev = kt_code(dir, P.dir_off, P.la, cx, cy, st, cols);
+        if (cx >= 1 && cy >= 1) {
+            // the walk is a chain of dependent loads; touch the line the path reaches KT_AHEAD diagonal steps from now
+            if (cx > KT_AHEAD && cy > KT_AHEAD)
+                asm volatile("prefetch.global.L1 [%0];" ::"l"(dir + kt_addr<COLS>(P.dir_off, P.la, cx - KT_AHEAD, cy - KT_AHEAD)));
+            prev = ((unsigned)dir[kt_addr<COLS>(P.dir_off, P.la, cx, cy)] >> (2 * st)) & 3u;
+        }
         else if (cx == 0 && cy == 0) prev = 0;                     // only reachable when la == lb == 0
         else if (cx == 0) {                                        // row 0: prev = GAPINX for all states (SA.rs:105-107)
             prev = 1;
@@ -428,10 +435,13 @@ cudaError_t kt_launch(const swb_engine *e, const KWPair *d_pairs, const KWResult
     if (n_pairs <= 0) return cudaSuccess;
     const int threads = 32, blocks = (n_pairs + threads - 1) / threads;
     const int sent = 10 * e->o + 10 * e->e;
+#define KT_GO(M) do { if (cols == 2) kt_kernel<M, 2><<<blocks, threads, 0, st>>>(d_pairs, d_res, n_pairs, d_dir, d_out_off, d_idx_a, d_idx_b, d_ncols, sent); \
+                      else kt_kernel<M, 8><<<blocks, threads, 0, st>>>(d_pairs, d_res, n_pairs, d_dir, d_out_off, d_idx_a, d_idx_b, d_ncols, sent); } while (0)
     switch (e->mode) {
-    case SWB_GLOBAL: kt_kernel<SWB_GLOBAL><<<blocks, threads, 0, st>>>(d_pairs, d_res, n_pairs, d_dir, d_out_off, d_idx_a, d_idx_b, d_ncols, sent, cols); break;
-    case SWB_GLOCAL: kt_kernel<SWB_GLOCAL><<<blocks, threads, 0, st>>>(d_pairs, d_res, n_pairs, d_dir, d_out_off, d_idx_a, d_idx_b, d_ncols, sent, cols); break;
-    default: kt_kernel<SWB_LOCAL><<<blocks, threads, 0, st>>>(d_pairs, d_res, n_pairs, d_dir, d_out_off, d_idx_a, d_idx_b, d_ncols, sent, cols); break;
+    case SWB_GLOBAL: KT_GO(SWB_GLOBAL); break;
+    case SWB_GLOCAL: KT_GO(SWB_GLOCAL); break;
+    default: KT_GO(SWB_LOCAL); break;
     }
+#undef KT_GO
     return cudaGetLastError();
 }
