@@ -1,17 +1,20 @@
 // Traceback path: swb_align / swb_align_batch.  Mirrors align_partial (SA.rs:393-551): encode ->
 // fill (KW with direction bytes) -> backtrack (KT) -> strings with the retain_all padding rules.
 #include <algorithm>
+#include <atomic>
 #include <cmath>
+#include <thread>
 #include <cstdlib>
 #include <cstring>
 
 #include "swb_internal.h"
 
-#define DIR_BUDGET_BYTES (24ll << 30)      // direction bytes resident per chunk of pairs
+#define DIR_BUDGET_BYTES (24ll << 30)      // direction bytes resident per chunk of pairs (one pair may exceed it)
 
-struct DevBuf {                            // frees on scope exit
-    void *p = nullptr;
-    ~DevBuf() { if (p) cudaFree(p); }
+struct DevBuf {                            // stream-ordered allocation from the engine's pool, freed on scope exit
+    void *p = nullptr; cudaStream_t st = nullptr;
+    cudaError_t alloc(size_t bytes, cudaStream_t s) { st = s; return cudaMallocAsync(&p, bytes ? bytes : 16, s); }
+    ~DevBuf() { if (p) cudaFreeAsync(p, st); }
     template <class T> T *as() { return reinterpret_cast<T *>(p); }
 };
 
@@ -117,11 +120,12 @@ static int align_batch_impl(swb_engine *e, const char *a_all, const int64_t *off
             if (std::fabs(v - r) > 1e-4 * e->scale || std::fabs(r) > 8000) { e->err = "position-specific scores are not on the engine's integer grid (or exceed 8000)"; return SWB_ERR_SCALE; }
             ps[k] = (int32_t)r;
         }
-        CUDA_TRY(e, cudaMalloc(&d_pssm.p, ps.size() * sizeof(int32_t)));
-        CUDA_TRY(e, cudaMemcpy(d_pssm.p, ps.data(), ps.size() * sizeof(int32_t), cudaMemcpyHostToDevice));
+        CUDA_TRY(e, d_pssm.alloc(ps.size() * sizeof(int32_t), e->stream));
+        CUDA_TRY(e, cudaMemcpyAsync(d_pssm.p, ps.data(), ps.size() * sizeof(int32_t), cudaMemcpyHostToDevice, e->stream));
+        CUDA_TRY(e, cudaStreamSynchronize(e->stream));      // ps is a local pageable vector
         e->stats.h2d_bytes += (double)ps.size() * sizeof(int32_t);
     }
-    CUDA_TRY(e, cudaMalloc(&d_a.p, ca.size())); CUDA_TRY(e, cudaMalloc(&d_b.p, cb.size()));
+    CUDA_TRY(e, d_a.alloc(ca.size(), e->stream)); CUDA_TRY(e, d_b.alloc(cb.size(), e->stream));
     CUDA_TRY(e, cudaMemcpyAsync(d_a.p, ca.data(), ca.size(), cudaMemcpyHostToDevice, e->stream));
     CUDA_TRY(e, cudaMemcpyAsync(d_b.p, cb.data(), cb.size(), cudaMemcpyHostToDevice, e->stream));
     e->stats.h2d_bytes += (double)ca.size() + (double)cb.size();
@@ -145,44 +149,73 @@ static int align_batch_impl(swb_engine *e, const char *a_all, const int64_t *off
         const int np = (int)hp.size();
         KWPlan plan; kw_plan(e, hp.data(), np, true, &plan);       // assigns the direction-byte offsets
         dir_total = plan.dir_bytes;
-        DevBuf d_pairs, d_res, d_dir, d_bnd, d_scr, d_off, d_xa, d_xb, d_nc;
-        CUDA_TRY(e, cudaMalloc(&d_pairs.p, np * sizeof(KWPair))); CUDA_TRY(e, cudaMalloc(&d_res.p, np * sizeof(KWResult)));
-        CUDA_TRY(e, cudaMalloc(&d_dir.p, dir_total + 16)); CUDA_TRY(e, cudaMalloc(&d_bnd.p, plan.bnd_elems * sizeof(int4)));
-        CUDA_TRY(e, cudaMalloc(&d_scr.p, plan.scratch_ints * sizeof(int)));
-        CUDA_TRY(e, cudaMalloc(&d_off.p, np * sizeof(int64_t)));
-        CUDA_TRY(e, cudaMalloc(&d_xa.p, out_total * sizeof(int32_t))); CUDA_TRY(e, cudaMalloc(&d_xb.p, out_total * sizeof(int32_t)));
-        CUDA_TRY(e, cudaMalloc(&d_nc.p, np * sizeof(int32_t)));
+        DevBuf d_pairs, d_res, d_bnd, d_scr, d_off, d_xa, d_xb, d_nc;
+        if ((size_t)dir_total + 16 > e->dir_bytes) {           // engine-owned direction store, grown on demand and kept
+            CUDA_TRY(e, cudaStreamSynchronize(e->stream));
+            if (e->d_dir) cudaFree(e->d_dir);
+            e->d_dir = nullptr; e->dir_bytes = 0;
+            CUDA_TRY(e, cudaMalloc(&e->d_dir, (size_t)dir_total + 16));
+            e->dir_bytes = (size_t)dir_total + 16;
+        }
+        CUDA_TRY(e, d_pairs.alloc(np * sizeof(KWPair), e->stream)); CUDA_TRY(e, d_res.alloc(np * sizeof(KWResult), e->stream));
+        CUDA_TRY(e, d_bnd.alloc(plan.bnd_elems * sizeof(int4), e->stream));
+        CUDA_TRY(e, d_scr.alloc(plan.scratch_ints * sizeof(int), e->stream));
+        CUDA_TRY(e, d_off.alloc(np * sizeof(int64_t), e->stream));
+        CUDA_TRY(e, d_xa.alloc(out_total * sizeof(int32_t), e->stream)); CUDA_TRY(e, d_xb.alloc(out_total * sizeof(int32_t), e->stream));
+        CUDA_TRY(e, d_nc.alloc(np * sizeof(int32_t), e->stream));
         CUDA_TRY(e, cudaMemcpyAsync(d_pairs.p, hp.data(), np * sizeof(KWPair), cudaMemcpyHostToDevice, e->stream));
         CUDA_TRY(e, cudaMemcpyAsync(d_off.p, out_off.data(), np * sizeof(int64_t), cudaMemcpyHostToDevice, e->stream));
         CUDA_TRY(e, cudaEventRecord(e->ev0, e->stream));
-        CUDA_TRY(e, kw_launch(e, d_a.as<uint8_t>(), d_b.as<uint8_t>(), d_pairs.as<KWPair>(), np, plan, d_dir.as<uint8_t>(),
+        CUDA_TRY(e, kw_launch(e, d_a.as<uint8_t>(), d_b.as<uint8_t>(), d_pairs.as<KWPair>(), np, plan, (uint8_t *)e->d_dir,
                               d_bnd.as<int4>(), d_scr.as<int>(), d_res.as<KWResult>(), e->stream, d_pssm.as<int32_t>()));
-        CUDA_TRY(e, kt_launch(e, d_pairs.as<KWPair>(), d_res.as<KWResult>(), np, d_dir.as<uint8_t>(), plan.cols, d_off.as<int64_t>(),
+        CUDA_TRY(e, kt_launch(e, d_pairs.as<KWPair>(), d_res.as<KWResult>(), np, (const uint8_t *)e->d_dir, plan.cols, d_off.as<int64_t>(),
                               d_xa.as<int32_t>(), d_xb.as<int32_t>(), d_nc.as<int32_t>(), e->stream));
         CUDA_TRY(e, cudaEventRecord(e->ev1, e->stream));
-        std::vector<KWResult> hr(np); std::vector<int32_t> hnc(np), hxa(out_total), hxb(out_total);
-        CUDA_TRY(e, cudaMemcpyAsync(hr.data(), d_res.p, np * sizeof(KWResult), cudaMemcpyDeviceToHost, e->stream));
-        CUDA_TRY(e, cudaMemcpyAsync(hnc.data(), d_nc.p, np * sizeof(int32_t), cudaMemcpyDeviceToHost, e->stream));
-        CUDA_TRY(e, cudaMemcpyAsync(hxa.data(), d_xa.p, out_total * sizeof(int32_t), cudaMemcpyDeviceToHost, e->stream));
-        CUDA_TRY(e, cudaMemcpyAsync(hxb.data(), d_xb.p, out_total * sizeof(int32_t), cudaMemcpyDeviceToHost, e->stream));
+        // results land in the engine's pinned traceback arena (a pageable destination would stage and block)
+        const size_t tb_need = (size_t)np * (sizeof(KWResult) + sizeof(int32_t)) + 2 * (size_t)out_total * sizeof(int32_t) + 64;
+        if (tb_need > e->tb_bytes) {
+            if (e->h_tb) cudaFreeHost(e->h_tb);
+            e->h_tb = nullptr; e->tb_bytes = 0;
+            CUDA_TRY(e, cudaMallocHost(&e->h_tb, tb_need));
+            e->tb_bytes = tb_need;
+        }
+        KWResult *hr = (KWResult *)e->h_tb;
+        int32_t *hnc = (int32_t *)(hr + np), *hxa = hnc + np, *hxb = hxa + out_total;
+        CUDA_TRY(e, cudaMemcpyAsync(hr, d_res.p, np * sizeof(KWResult), cudaMemcpyDeviceToHost, e->stream));
+        CUDA_TRY(e, cudaMemcpyAsync(hnc, d_nc.p, np * sizeof(int32_t), cudaMemcpyDeviceToHost, e->stream));
+        CUDA_TRY(e, cudaMemcpyAsync(hxa, d_xa.p, out_total * sizeof(int32_t), cudaMemcpyDeviceToHost, e->stream));
+        CUDA_TRY(e, cudaMemcpyAsync(hxb, d_xb.p, out_total * sizeof(int32_t), cudaMemcpyDeviceToHost, e->stream));
         CUDA_TRY(e, cudaStreamSynchronize(e->stream));
         float ms = 0; cudaEventElapsedTime(&ms, e->ev0, e->ev1);
         e->stats.kernel_ms += ms; e->stats.launches += 2;
         e->stats.h2d_bytes += (double)np * (sizeof(KWPair) + sizeof(int64_t));
         e->stats.d2h_bytes += (double)np * (sizeof(KWResult) + 4) + 8.0 * out_total;
-        for (int t = 0; t < np; ++t) {
-            const int64_t k = work[pos + t];
-            if (hnc[t] < 0) { e->err = "traceback left the matrix (the reference panics here, SA.rs:360-371)"; return SWB_ERR_EMPTY; }
-            const int64_t nc = hnc[t];
-            std::vector<int64_t> xa(nc), xb(nc);
-            for (int64_t c = 0; c < nc; ++c) {                  // reverse (SA.rs:384-385)
-                xa[c] = hxa[out_off[t] + nc - 1 - c]; xb[c] = hxb[out_off[t] + nc - 1 - c];
+        // reverse + string inflation per pair: independent, spread over host threads for large batches
+        std::atomic<int> next(0), fail(SWB_OK);
+        auto worker = [&]() {
+            for (;;) {
+                const int t = next.fetch_add(1);
+                if (t >= np || fail.load() != SWB_OK) return;
+                const int64_t k = work[pos + t];
+                if (hnc[t] < 0) { fail.store(SWB_ERR_EMPTY); return; }
+                const int64_t nc = hnc[t];
+                std::vector<int64_t> xa(nc), xb(nc);
+                for (int64_t c = 0; c < nc; ++c) {              // reverse (SA.rs:384-385)
+                    xa[c] = hxa[out_off[t] + nc - 1 - c]; xb[c] = hxb[out_off[t] + nc - 1 - c];
+                }
+                std::string ra, rb;
+                inflate(a_all + off_a[k], hp[t].la, b_all + off_b[k], hp[t].lb, xa.data(), xb.data(), nc, e->mode, retain_all, ra, rb);
+                if (fill_out(&outs[k], to_f(hr[t].score), hr[t].end_i, hr[t].end_j, xa, xb, ra, rb) != SWB_OK) { fail.store(SWB_ERR_NOMEM); return; }
             }
-            std::string ra, rb;
-            inflate(a_all + off_a[k], hp[t].la, b_all + off_b[k], hp[t].lb, xa.data(), xb.data(), nc, e->mode, retain_all, ra, rb);
-            int rc = fill_out(&outs[k], to_f(hr[t].score), hr[t].end_i, hr[t].end_j, xa, xb, ra, rb);
-            if (rc != SWB_OK) { e->err = "out of memory"; return rc; }
-        }
+        };
+        const int n_thr = (np >= 8) ? (int)std::min<unsigned>(std::max(1u, std::thread::hardware_concurrency()), 16u) : 1;
+        if (n_thr > 1) {
+            std::vector<std::thread> pool;
+            for (int w = 0; w < n_thr; ++w) pool.emplace_back(worker);
+            for (auto &th : pool) th.join();
+        } else worker();
+        if (fail.load() == SWB_ERR_EMPTY) { e->err = "traceback left the matrix (the reference panics here, SA.rs:360-371)"; return SWB_ERR_EMPTY; }
+        if (fail.load() != SWB_OK) { e->err = "out of memory"; return fail.load(); }
         pos = end;
     }
     return SWB_OK;

@@ -170,8 +170,10 @@ extern "C" void swb_engine_destroy(swb_engine *e)
     if (e->d_mat) cudaFree(e->d_mat);
     if (e->d_code_tab) cudaFree(e->d_code_tab);
     if (e->d_bnd) cudaFree(e->d_bnd);
+    if (e->d_dir) cudaFree(e->d_dir);
     if (e->h_stage) cudaFreeHost(e->h_stage);
     if (e->h_items) cudaFreeHost(e->h_items);
+    if (e->h_tb) cudaFreeHost(e->h_tb);
     if (e->ev_items) cudaEventDestroy(e->ev_items);
     if (e->ev0) cudaEventDestroy(e->ev0);
     if (e->ev1) cudaEventDestroy(e->ev1);

@@ -51,6 +51,8 @@ struct swb_engine {
     int16_t *d_code_tab = nullptr;  // byte -> residue code (device copy of code_of)
     // scratch owned by the engine, grown on demand
     void *d_bnd = nullptr; size_t bnd_bytes = 0;
+    void *d_dir = nullptr; size_t dir_bytes = 0;                        // direction bytes of the traceback path (align.cu)
+    void *h_tb = nullptr; size_t tb_bytes = 0;                          // pinned arena of the traceback results (align.cu)
     void *h_items = nullptr; size_t items_bytes = 0; cudaEvent_t ev_items = nullptr;   // pinned K2 work-item table
     void *h_stage = nullptr; size_t stage_bytes = 0, stage_used = 0;   // pinned results arena of swb_score_batch
     swb_stats stats = {};

@@ -84,8 +84,8 @@ def case_pairs(n, length, mode, alphabet, go, ge, match, mismatch, sub, indel, t
     m = swb.SubstitutionMatrix.get_mat_matrix(match, mismatch) if match is not None else swb.SubstitutionMatrix.get_blosum62_matrix()
     eng = swb.SequenceAlignment(m, go, ge, mode)
     cells = float(sum(len(x) * len(y) for x, y in zip(sa, sb)))
-    if traceback:                                             # warm-up: module load of the kernel instantiations
-        eng.align_list(sa[:1], sb[:1], True)
+    if traceback:                                             # warm-up: module load, scratch and direction-store growth
+        eng.align_list(sa, sb, True)
     else:
         eng.score_batch(sa[:1], sb[:1])
     t0 = time.perf_counter()
