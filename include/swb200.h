@@ -143,7 +143,8 @@ int swb_batch_run_n(swb_engine *e, swb_batch *b, int steps, float *total_ms, int
 
 /* DPX / integer-pipe micro-benchmark (kernel K0): thread-instructions per second of the given
  * instruction mix on the whole chip; which: 0 VIADDMNMX.S16x2, 1 VIMNMX3.S16x2, 2 VIADD.16x2,
- * 3 the 4-op Gotoh cell mix, 4 VIADDMNMX (s32), 5 IMAD, 6 mix + IMAD interleaved. */
+ * 3 the 4-op Gotoh cell mix, 4 VIADDMNMX (s32), 5 IMAD, 6 mix + IMAD interleaved, 7 HMNMX2, 8 HFMA2,
+ * 9 VIADDMNMX + HMNMX2, 10 VIADDMNMX + HFMA2, 11 VIADDMNMX + IMAD (pipe-sharing probes). */
 int swb_dpx_peak(int device, int which, double *thread_instr_per_s);
 
 #ifdef __cplusplus

@@ -2,6 +2,8 @@
 // (SURVEY.md 8d).  Every thread runs 8 independent dependency chains of the chosen instruction so
 // that the issue rate, not the 4-cycle ALU latency, is the limit; all SMs are filled with 2048
 // threads.  Reported: thread-instructions per second (warp-instructions * 32 / elapsed).
+#include <cuda_fp16.h>
+
 #include "swb_internal.h"
 
 #define K0_ITERS 4096
@@ -38,6 +40,31 @@ __global__ void __launch_bounds__(1024) k0_kernel(unsigned *out, unsigned seed)
                 unsigned a0 = E * k2 + F, a1 = F * k2 + T, a2 = a0 * 65536u + a1;
                 unsigned H = __viaddmax_s16x2_relu(v[c], a2, T);
                 v[c] = __vadd2(H, k1); w[c] = E;
+            }
+            else if (WHICH == 7) {      // packed fp16 max (HMNMX2): which pipe?
+                __half2 a = *reinterpret_cast<__half2 *>(&v[c]), b = *reinterpret_cast<__half2 *>(&w[c]);
+                a = __hmax2(a, b); v[c] = *reinterpret_cast<unsigned *>(&a);
+            }
+            else if (WHICH == 8) {      // packed fp16 fused multiply-add (HFMA2, FMA pipe)
+                __half2 a = *reinterpret_cast<__half2 *>(&v[c]), b = *reinterpret_cast<__half2 *>(&w[c]);
+                const __half2 kk = *reinterpret_cast<const __half2 *>(&k1);
+                a = __hfma2(a, kk, b); v[c] = *reinterpret_cast<unsigned *>(&a);
+            }
+            else if (WHICH == 9) {      // one DPX op and one HMNMX2 on independent chains: do they share a pipe?
+                v[c] = __viaddmax_s16x2(v[c], k1, k2);
+                __half2 b = *reinterpret_cast<__half2 *>(&w[c]);
+                const __half2 kk = *reinterpret_cast<const __half2 *>(&k1);
+                b = __hmax2(b, kk); w[c] = *reinterpret_cast<unsigned *>(&b);
+            }
+            else if (WHICH == 10) {     // one DPX op and one HFMA2 on independent chains
+                v[c] = __viaddmax_s16x2(v[c], k1, k2);
+                __half2 b = *reinterpret_cast<__half2 *>(&w[c]);
+                const __half2 kk = *reinterpret_cast<const __half2 *>(&k1);
+                b = __hfma2(b, kk, kk); w[c] = *reinterpret_cast<unsigned *>(&b);
+            }
+            else if (WHICH == 11) {     // one DPX op and one IMAD on independent chains
+                v[c] = __viaddmax_s16x2(v[c], k1, k2);
+                w[c] = w[c] * k1 + k2;
             }
         }
     }
@@ -83,6 +110,11 @@ cudaError_t k0_run(int which, int sm_count, double *rate)
     case 4: return k0_time<4>(sm_count, 1, rate);
     case 5: return k0_time<5>(sm_count, 1, rate);
     case 6: return k0_time<6>(sm_count, 8, rate);
+    case 7: return k0_time<7>(sm_count, 1, rate);
+    case 8: return k0_time<8>(sm_count, 1, rate);
+    case 9: return k0_time<9>(sm_count, 2, rate);
+    case 10: return k0_time<10>(sm_count, 2, rate);
+    case 11: return k0_time<11>(sm_count, 2, rate);
     default: return cudaErrorInvalidValue;
     }
 }
