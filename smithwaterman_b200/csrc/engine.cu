@@ -142,6 +142,7 @@ extern "C" int swb_engine_create(const swb_matrix *m, float gap_open, float gap_
     for (int i = 0; i < e->n; ++i) for (int j = 0; j < e->n; ++j) tab[(size_t)i * nl + j] = e->mat[(size_t)i * e->n + j];
     if ((ce = cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking)) != cudaSuccess ||
         (ce = cudaStreamCreateWithFlags(&e->stream_up, cudaStreamNonBlocking)) != cudaSuccess ||
+        (ce = cudaStreamCreateWithFlags(&e->stream2, cudaStreamNonBlocking)) != cudaSuccess ||
         (ce = cudaEventCreate(&e->ev0)) != cudaSuccess || (ce = cudaEventCreate(&e->ev1)) != cudaSuccess ||
         (ce = cudaMalloc(&e->d_mat, tab.size() * sizeof(int32_t))) != cudaSuccess ||
         (ce = cudaMemcpy(e->d_mat, tab.data(), tab.size() * sizeof(int32_t), cudaMemcpyHostToDevice)) != cudaSuccess ||
@@ -179,6 +180,7 @@ extern "C" void swb_engine_destroy(swb_engine *e)
     if (e->ev1) cudaEventDestroy(e->ev1);
     if (e->stream) cudaStreamDestroy(e->stream);
     if (e->stream_up) cudaStreamDestroy(e->stream_up);
+    if (e->stream2) cudaStreamDestroy(e->stream2);
     delete e;
 }
 

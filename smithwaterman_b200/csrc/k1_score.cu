@@ -27,6 +27,8 @@
 // has an equal-valued cell before it in that order.  Per row step only a packed row maximum is
 // kept (VIMNMX3, half an instruction per cell); the column is recovered by a register scan in
 // the (rare) steps where the running best improves.
+#include <cstdlib>
+
 #include "swb_internal.h"
 
 __device__ __forceinline__ unsigned lds32(unsigned addr)
@@ -77,7 +79,9 @@ __device__ __forceinline__ unsigned pack2(int lo, int hi) { return ((unsigned)lo
         F[k] = Fk;                                                                                   \
     }
 
-__global__ void __launch_bounds__(K1_THREADS * 2, 1)
+// (120 registers, not the 128 that 512 threads would allow: the 4096 left over hold one 128-thread helper block of the
+// upload / result path per SM, see batch.cu SWB_HELPER; the kernel needs 119)
+__global__ void __maxnreg__(120)
 k1_local_kernel(const uint8_t *__restrict__ a_pk, const uint8_t *__restrict__ b_pk,
                 const K1Group *__restrict__ groups, int n_groups, const int32_t *__restrict__ la_arr,
                 const int32_t *__restrict__ lb_arr, const int32_t *__restrict__ mat, int nl, int open, int ext,
@@ -223,7 +227,7 @@ size_t k1_bnd_bytes(int n_blocks, int la_max)
     return (size_t)n_blocks * (K1_THREADS * 2 / 32) * (size_t)k1_bnd_blocks(la_max) * 32 * sizeof(uint4);
 }
 
-cudaError_t k1_launch(const swb_engine *e, const swb_batch *b, int n_blocks, cudaStream_t st)
+cudaError_t k1_launch(const swb_engine *e, const swb_batch *b, int n_blocks, void *d_bnd, cudaStream_t st)
 {
     const int nl = e->n + 1;
     const size_t smem = (size_t)nl * nl * 32 * sizeof(unsigned);
@@ -234,8 +238,8 @@ cudaError_t k1_launch(const swb_engine *e, const swb_batch *b, int n_blocks, cud
     // Ho must stay below 32767 - smax so that Ho_diag + (s - open) cannot wrap.
     const int limit_ho = 32767 - 2 * e->smax + e->o - 1;
     k1_local_kernel<<<n_blocks, K1_THREADS * 2, smem, st>>>(
-        b->d_a, b->d_b, b->d_groups, (int)b->groups.size(), b->d_la, b->d_lb, e->d_mat, nl, e->o, e->e, limit_ho,
-        reinterpret_cast<uint4 *>(e->d_bnd), k1_bnd_blocks(b->la_max), b->d_counter, b->d_order, b->d_res);
+        b->d_a, b->d_b, b->d_groups, b->n_groups, b->d_la, b->d_lb, e->d_mat, nl, e->o, e->e, limit_ho,
+        reinterpret_cast<uint4 *>(d_bnd), k1_bnd_blocks(b->la_max), b->d_counter, b->d_order, b->d_res);
     return cudaGetLastError();
 }
 

@@ -44,13 +44,14 @@ struct swb_engine {
     std::vector<int32_t> mat;       // n*n scaled
     std::vector<float> matf;        // n*n as given
     cudaStream_t stream = nullptr;      // compute stream (kernels, result D2H)
-    cudaStream_t stream_up = nullptr;   // copy stream of the pipelined host-buffer path (H2D, encode, pack)
+    cudaStream_t stream2 = nullptr;     // second compute stream: odd chunks of the pipelined host-buffer path
+    cudaStream_t stream_up = nullptr;   // upload stream of the pipelined host-buffer path (allocations, H2D, encode, sort, pack)
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     int sm_count = 0;
     int32_t *d_mat = nullptr;       // (n+1)*(n+1) int32 scaled, PAD row/col included
     int16_t *d_code_tab = nullptr;  // byte -> residue code (device copy of code_of)
     // scratch owned by the engine, grown on demand
-    void *d_bnd = nullptr; size_t bnd_bytes = 0;
+    void *d_bnd = nullptr; size_t bnd_bytes = 0;                        // two slots of bnd_bytes each (batch.cu ensure_bnd)
     void *d_dir = nullptr; size_t dir_bytes = 0;                        // direction bytes of the traceback path (align.cu)
     void *h_tb = nullptr; size_t tb_bytes = 0;                          // pinned arena of the traceback results (align.cu)
     void *h_items = nullptr; size_t items_bytes = 0; cudaEvent_t ev_items = nullptr;   // pinned K2 work-item table
@@ -62,26 +63,21 @@ struct swb_engine {
 struct BatchDev;
 struct swb_batch {
     int64_t n = 0;
+    int slot = 0;                   // compute stream / boundary-scratch slot this batch runs on
     BatchDev *dev = nullptr;        // device-side part owned by batch.cu
-    std::vector<int32_t> order;     // sorted position -> caller's pair index
     std::vector<int32_t> la, lb;    // per caller index
-    std::vector<K1Group> groups;
-    // device
+    // device (K1 work items are sorted and built on the device, batch.cu)
     uint8_t *d_a = nullptr, *d_b = nullptr;
     K1Group *d_groups = nullptr;
+    int32_t n_groups = 0;
     int32_t *d_la = nullptr, *d_lb = nullptr;   // sorted order
     K1Result *d_res = nullptr;                  // indexed by the caller's pair index within the batch (K1 scatters)
-    const int32_t *d_order = nullptr;           // sorted position -> caller index (device copy)
+    const int32_t *d_order = nullptr;           // sorted position -> caller index
     int32_t *d_counter = nullptr;
-    size_t a_bytes = 0, b_bytes = 0;
+    size_t a_bytes = 0, b_bytes = 0;            // upper bounds of the packed residue blocks
     int32_t la_max = 0;
-    // generic (int32, 3-state) path for what K1 does not take: codes in caller order
-    std::vector<int32_t> generic_idx;           // caller indices routed to the generic kernel
-    std::vector<uint8_t> h_codes_a, h_codes_b;  // encoded residues, concatenated (caller order)
-    std::vector<int64_t> off_a, off_b;
     float last_ms = 0; int64_t last_launches = 0;
     double cells = 0;
-    std::vector<K1Result> h_res;    // pinned staging is overkill for 16 B/pair; plain vector
 };
 
 #define CUDA_TRY(e_, call)                                                                      \
@@ -95,7 +91,7 @@ struct swb_batch {
 
 // ---- kernel launchers (defined in the .cu files) ----------------------------------------------
 // K1: local, score + first-maximum cell, packed s16x2, one thread per pair.
-cudaError_t k1_launch(const swb_engine *e, const swb_batch *b, int n_blocks, cudaStream_t st);
+cudaError_t k1_launch(const swb_engine *e, const swb_batch *b, int n_blocks, void *d_bnd, cudaStream_t st);
 size_t k1_bnd_bytes(int n_blocks, int la_max);
 int k1_blocks_per_sm(const swb_engine *e);
 // K2: shared long query, lanes split the columns (database search).

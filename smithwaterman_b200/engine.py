@@ -280,12 +280,16 @@ class SequenceAlignment:
         b, ob = pack_sequences(seqs_b)
         return self.score_packed(a, oa, b, ob)
 
-    def score_packed(self, a, oa, b, ob):
-        """Host buffers in, host buffers out (H2D + kernels + D2H inside the call)."""
+    def score_packed(self, a, oa, b, ob, out=None):
+        """Host buffers in, host buffers out (H2D + kernels + D2H inside the call).  `out` = (scores f32[n], end_a
+        i64[n], end_b i64[n]) to fill, e.g. pinned arrays: the device then writes the results straight into them."""
         n = len(oa) - 1
-        sc = np.empty(n, np.float32)
-        ea = np.empty(n, np.int64)
-        eb = np.empty(n, np.int64)
+        if out is not None:
+            sc, ea, eb = out
+        else:
+            sc = np.empty(n, np.float32)
+            ea = np.empty(n, np.int64)
+            eb = np.empty(n, np.int64)
         self._check(self.L.swb_score_batch(self._h, _ptr(a), _ptr(oa), _ptr(b), _ptr(ob), n, _ptr(sc), _ptr(ea), _ptr(eb)))
         return sc, ea, eb
 
