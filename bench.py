@@ -151,6 +151,26 @@ def other_configs(swb, dev):
     return out
 
 
+def bind_to_gpu_numa(local_rank):
+    """Pin this rank to the CPUs nearest its GPU (NVML's ideal affinity) before any host buffer is allocated, so that
+    the pinned input / result arrays sit on the NUMA node the GPU's PCIe root hangs off.  Best effort: returns the
+    number of CPUs bound to, or None when NVML / the cpuset does not allow it."""
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        h = pynvml.nvmlDeviceGetHandleByIndex(local_rank)
+        allowed = os.sched_getaffinity(0)
+        words = pynvml.nvmlDeviceGetCpuAffinity(h, (os.cpu_count() + 63) // 64)
+        ideal = {64 * w + b for w, m in enumerate(words) for b in range(64) if (m >> b) & 1}
+        cpus = ideal & allowed
+        if not cpus:
+            return None
+        os.sched_setaffinity(0, cpus)
+        return len(cpus)
+    except Exception:
+        return None
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -199,6 +219,7 @@ def main():
     if not torch.cuda.is_available():
         raise SystemExit("bench.py needs a CUDA device (no CPU fallback)")
     torch.cuda.set_device(local_rank)
+    numa = bind_to_gpu_numa(local_rank) if world > 1 else None   # pinned buffers are first-touched on the GPU's own NUMA node
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
 
@@ -250,9 +271,12 @@ def main():
     if world > 1:
         tmax = t.clone(); dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
         tsum = t.clone(); dist.all_reduce(tsum, op=dist.ReduceOp.SUM)
+        per_rank = [torch.zeros_like(t) for _ in range(world)]; dist.all_gather(per_rank, t)
+        e2e_ranks = [round(x[1].item(), 2) for x in per_rank]
         ms_step, e2e_ms, tot_cells = tmax[0].item(), tmax[1].item(), tsum[2].item()
     else:
         ms_step, e2e_ms, tot_cells = t[0].item(), t[1].item(), cells
+        e2e_ranks = [round(e2e_ms, 2)]
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
@@ -305,7 +329,7 @@ def main():
             "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "s16x2 (int32 re-run)",
             "data": "synthetic", "config": config, "clocks": sampler.summary(),
             "e2e": {"value": e2e_val, "unit": "GCUPS", "h2d_bytes_per_step": st["h2d_bytes"], "d2h_bytes_per_step": st["d2h_bytes"],
-                    "ms_per_step": e2e_ms, "steps": e2e_steps},
+                    "ms_per_step": e2e_ms, "steps": e2e_steps, "ms_per_rank": e2e_ranks, "numa_bound_cpus": numa},
             "gpu_launches": int(launches), "roofline": roofline, "cpu_baseline": cpu,
             "i32_reruns": int(reruns), "cells_per_step": tot_cells, "other_configs": extras}
     print(json.dumps(line))
