@@ -12,6 +12,7 @@
  *   swb_align              SequenceAlignment::align          SA.rs:389-392 (OCL.rs:796 align)
  *   swb_align_pssm         align over a PositionSpecificMatrix  SA.rs:583-623 (ScoringMatrix trait SA.rs:574-580)
  *   swb_align_batch        the serial loop of `sa_opencl -list`  OCL-main.rs:295-316 (one call, n pairs)
+ *   swb_align_stats_batch  align + the identity / coverage counts of `sa_opencl -cluster`  OCL-main.rs:187-243
  *   swb_score_batch        align_partial(.., score_only=true) per pair  SA.rs:393-467
  *   swb_search_scores      the all-vs-all loops of the CLIs with one fixed query (SA-main.rs:35-45), n subjects per call
  *   swb_batch_*            the same as swb_score_batch, split into upload / run / fetch so that a
@@ -113,6 +114,22 @@ int swb_align_pssm(swb_engine *e, const float *scores, const char *a, int64_t la
 int swb_align_batch(swb_engine *e, const char *a_all, const int64_t *off_a, const char *b_all,
                     const int64_t *off_b, int64_t n, unsigned flags, swb_alignment *outs);
 void swb_alignment_free(swb_alignment *a);
+
+/* What the clustering loop of `sa_opencl -cluster` reads off an alignment (OCL-main.rs:205-233: the non-gap letters of
+ * each aligned string, the columns with two equal letters, the string length), without building the strings: the
+ * traceback walk counts on the device and 48 bytes per pair come back.  Values are those of the strings
+ * swb_align_batch would return for the same `flags`. */
+typedef struct swb_aln_stats {
+    float score;
+    int32_t status;          /* 0, or SWB_ERR_EMPTY where the reference panics on this pair */
+    int64_t end_a, end_b;    /* as swb_alignment */
+    int64_t aln_len;         /* strlen(aln_a) */
+    int64_t a_letters;       /* characters of aln_a that are not '-' */
+    int64_t b_letters;
+    int64_t matches;         /* columns k with aln_a[k] == aln_b[k], neither a gap (compared as given, not as encoded) */
+} swb_aln_stats;
+int swb_align_stats_batch(swb_engine *e, const char *a_all, const int64_t *off_a, const char *b_all,
+                          const int64_t *off_b, int64_t n, unsigned flags, swb_aln_stats *outs);
 
 /* Score + end cell of n pairs, HOST buffers in and out (H2D, kernels, D2H inside the call).
  * scores[k] as the reference's f32; end_a/end_b: first-maximum cell (local, SA.rs:286-294;

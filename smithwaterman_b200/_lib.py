@@ -50,6 +50,11 @@ class Alignment(ctypes.Structure):
                 ("aln_a", ctypes.c_void_p), ("aln_b", ctypes.c_void_p)]
 
 
+# swb_aln_stats as a numpy record (48 bytes, the C layout)
+ALN_STATS_DTYPE = [("score", "<f4"), ("status", "<i4"), ("end_a", "<i8"), ("end_b", "<i8"), ("aln_len", "<i8"),
+                   ("a_letters", "<i8"), ("b_letters", "<i8"), ("matches", "<i8")]
+
+
 class Stats(ctypes.Structure):
     _fields_ = [("cells", ctypes.c_double), ("kernel_ms", ctypes.c_double), ("h2d_bytes", ctypes.c_double),
                 ("d2h_bytes", ctypes.c_double), ("launches", ctypes.c_int64), ("i32_reruns", ctypes.c_int64),
@@ -81,6 +86,7 @@ def lib():
         "swb_align_pssm": (c.c_int, [vp, vp, vp, i64, vp, i64, c.c_int, c.POINTER(Alignment)]),
         "swb_align_batch": (c.c_int, [vp, vp, vp, vp, vp, i64, c.c_uint, c.POINTER(Alignment)]),
         "swb_alignment_free": (None, [c.POINTER(Alignment)]),
+        "swb_align_stats_batch": (c.c_int, [vp, vp, vp, vp, vp, i64, c.c_uint, vp]),
         "swb_score_batch": (c.c_int, [vp, vp, vp, vp, vp, i64, vp, vp, vp]),
         "swb_search_scores": (c.c_int, [vp, vp, i64, vp, vp, i64, vp, vp, vp]),
         "swb_batch_upload": (c.c_int, [vp, vp, vp, vp, vp, i64, c.POINTER(vp)]),

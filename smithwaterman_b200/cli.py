@@ -102,10 +102,13 @@ def align_files(engine, filelist, out=sys.stdout, outfile=None):
     return len(res)
 
 
-def cluster(seqs, align_many, identity=0.8, coverage_short=0.8, coverage_long=0.8, out=sys.stdout):
+def cluster(seqs, align_many, identity=0.8, coverage_short=0.8, coverage_long=0.8, out=sys.stdout, stats_many=None):
     """Greedy length-sorted clustering of OCL-main.rs:149-243.
 
     seqs: list of SeqData; align_many(rep, candidates) -> list of (aln_a, aln_b) strings of align(rep, cand, false).
+    stats_many(rep, candidates) -> list of (a_letters, b_letters, matches, aln_len), the four numbers the loop reads off
+    those strings (OCL-main.rs:205-233); when given it is used instead of align_many (the device counts them during
+    the traceback walk, `swb_align_stats_batch`).
     Returns (sorted sequences, cluster_of, members) exactly as the reference's loop leaves them.
     """
     seq1 = sorted(seqs, key=lambda s: -len(s.seq))                      # stable, longest first (OCL-main.rs:151)
@@ -134,7 +137,15 @@ def cluster(seqs, align_many, identity=0.8, coverage_short=0.8, coverage_long=0.
         members[ii].extend(identical_members[ii]); identical_members[ii] = []
         cand = [jj for jj in range(ii + 1, n) if cluster_of[jj] == jj and identical[jj] == jj]
         need = [jj for jj in cand if strs[jj] not in strs[ii]]
-        alns = dict(zip(need, align_many(seq1[ii], [seq1[jj] for jj in need]))) if need else {}
+        if not need:
+            alns = {}
+        elif stats_many is not None:
+            alns = dict(zip(need, stats_many(seq1[ii], [seq1[jj] for jj in need])))
+        else:
+            alns = {}
+            for jj, (ra, rb) in zip(need, align_many(seq1[ii], [seq1[jj] for jj in need])):
+                alns[jj] = (sum(1 for c in ra if c != "-"), sum(1 for c in rb if c != "-"),
+                            sum(1 for x, y in zip(ra, rb) if x != "-" and y != "-" and x == y), len(ra))
         for jj in range(ii + 1, n):
             if cluster_of[jj] == jj and identical[jj] == jj:
                 if jj not in alns:                                      # si.contains(sj)
@@ -142,12 +153,10 @@ def cluster(seqs, align_many, identity=0.8, coverage_short=0.8, coverage_long=0.
                         cluster_of[jj] = ii
                         members[ii].extend(identical_members[jj]); identical_members[jj] = []
                 else:
-                    ra, rb = alns[jj]
-                    alen = sum(1 for c in ra if c != "-"); blen_ = sum(1 for c in rb if c != "-")
-                    matchnum = sum(1 for x, y in zip(ra, rb) if x != "-" and y != "-" and x == y)
+                    alen, blen_, matchnum, ncol = alns[jj]
                     lcov = alen / len(seq1[ii].seq) if len(seq1[ii].seq) else float("nan")
                     scov = blen_ / len(seq1[jj].seq) if len(seq1[jj].seq) else float("nan")
-                    ident = matchnum / len(ra) if len(ra) else float("nan")
+                    ident = matchnum / ncol if ncol else float("nan")
                     if lcov >= coverage_long and scov >= coverage_short and ident >= identity:
                         cluster_of[jj] = ii
                         members[ii].extend(identical_members[jj]); identical_members[jj] = []
@@ -185,10 +194,17 @@ def main(argv=None, out=sys.stdout):
             def align_many(rep, cands):
                 res = engine.align_list([rep] * len(cands), cands, False)
                 return [(r["aln_a"], r["aln_b"]) for r in res]
+
+            def stats_many(rep, cands):
+                st = engine.align_stats([rep] * len(cands), cands, False)
+                if (st["status"] != 0).any():
+                    raise RuntimeError("the traceback left the matrix (the reference panics here, SA.rs:360-371)")
+                return list(zip(st["a_letters"].tolist(), st["b_letters"].tolist(), st["matches"].tolist(), st["aln_len"].tolist()))
             seq1, cluster_of, members = cluster(seqs, align_many,
                                                 opp.c_identity if opp.c_identity is not None else 0.8,
                                                 opp.c_coverage_short if opp.c_coverage_short is not None else 0.8,
-                                                opp.c_coverage_long if opp.c_coverage_long is not None else 0.8, out)
+                                                opp.c_coverage_long if opp.c_coverage_long is not None else 0.8, out,
+                                                stats_many=stats_many)
             write_clusters(opp.outfilename, seq1, cluster_of, members)
         else:
             filelist = read_list(opp.file1, out) if opp.list else [(opp.file1, opp.file2)]

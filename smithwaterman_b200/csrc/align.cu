@@ -70,14 +70,30 @@ extern "C" void swb_alignment_free(swb_alignment *a)
     memset(a, 0, sizeof(*a));
 }
 
+// The strings' statistics from the core alignment's counts (inflate() above without building anything).
+static void compose_stats(swb_aln_stats *o, int mode, bool retain_all, int64_t la, int64_t lb, const KTStats &S)
+{
+    if (mode == SWB_LOCAL && !retain_all) {                                               // SA.rs:502-504
+        o->aln_len = S.ncols; o->a_letters = S.na; o->b_letters = S.nb; o->matches = S.match;
+        return;
+    }
+    o->a_letters = la; o->b_letters = lb;
+    if (S.s1 < 0 || S.s2 < 0) { o->aln_len = la + lb; o->matches = 0; return; }           // SA.rs:512-524
+    o->aln_len = (int64_t)S.s1 + S.s2 + S.ncols + (la - S.e1 - 1) + (lb - S.e2 - 1);      // SA.rs:530-549
+    o->matches = S.match;
+}
+
+// outs: full alignments (lists + strings); souts: the counting form (swb_align_stats_batch).  Exactly one is non-null.
 static int align_batch_impl(swb_engine *e, const char *a_all, const int64_t *off_a, const char *b_all,
-                            const int64_t *off_b, int64_t n, unsigned flags, swb_alignment *outs, const float *pssm)
+                            const int64_t *off_b, int64_t n, unsigned flags, swb_alignment *outs, const float *pssm,
+                            swb_aln_stats *souts = nullptr)
 {
     if (!e) return SWB_ERR_ARG;
-    if (n < 0 || (n > 0 && (!off_a || !off_b || !outs))) { e->err = "bad argument"; return SWB_ERR_ARG; }
+    if (n < 0 || (n > 0 && (!off_a || !off_b || (!outs && !souts)))) { e->err = "bad argument"; return SWB_ERR_ARG; }
     CUDA_TRY(e, cudaSetDevice(e->device));
     const bool retain_all = (flags & SWB_RETAIN_ALL) != 0;
-    memset(outs, 0, sizeof(swb_alignment) * (size_t)n);
+    if (outs) memset(outs, 0, sizeof(swb_alignment) * (size_t)n);
+    if (souts) memset(souts, 0, sizeof(swb_aln_stats) * (size_t)n);
     const float inv = 1.0f / (float)e->scale;
     const bool dyadic = (e->scale & (e->scale - 1)) == 0;
     auto to_f = [&](int64_t s) { return dyadic ? (float)s * inv : (float)((double)s / e->scale); };
@@ -105,6 +121,14 @@ static int align_batch_impl(swb_engine *e, const char *a_all, const int64_t *off
             for (int64_t t = 0; t < la; ++t) { xa.push_back(t); xb.push_back(-1); }
             for (int64_t t = 0; t < lb; ++t) { xa.push_back(-1); xb.push_back(t); }
         }
+        if (souts) {
+            KTStats S; S.ncols = (int32_t)xa.size(); S.na = (int32_t)la; S.nb = (int32_t)lb; S.match = 0;
+            S.s1 = la ? 0 : -1; S.e1 = (int32_t)la - 1; S.s2 = lb ? 0 : -1; S.e2 = (int32_t)lb - 1;
+            if (e->mode == SWB_LOCAL) { S.ncols = 0; S.na = 0; S.nb = 0; S.s1 = S.s2 = S.e1 = S.e2 = -1; }
+            souts[k].score = score; souts[k].end_a = ei; souts[k].end_b = ej;
+            compose_stats(&souts[k], e->mode, retain_all, la, lb, S);
+            continue;
+        }
         inflate(a_all + off_a[k], la, b_all + off_b[k], lb, xa.data(), xb.data(), (int64_t)xa.size(), e->mode, retain_all, ra, rb);
         int rc = fill_out(&outs[k], score, ei, ej, xa, xb, ra, rb);
         if (rc != SWB_OK) { e->err = "out of memory"; return rc; }
@@ -129,6 +153,13 @@ static int align_batch_impl(swb_engine *e, const char *a_all, const int64_t *off
     CUDA_TRY(e, cudaMemcpyAsync(d_a.p, ca.data(), ca.size(), cudaMemcpyHostToDevice, e->stream));
     CUDA_TRY(e, cudaMemcpyAsync(d_b.p, cb.data(), cb.size(), cudaMemcpyHostToDevice, e->stream));
     e->stats.h2d_bytes += (double)ca.size() + (double)cb.size();
+    DevBuf d_ra, d_rb;                                // the letters as given: the equal-letter test of the counting form
+    if (souts) {
+        CUDA_TRY(e, d_ra.alloc((size_t)na + 16, e->stream)); CUDA_TRY(e, d_rb.alloc((size_t)nb + 16, e->stream));
+        if (na) CUDA_TRY(e, cudaMemcpyAsync(d_ra.p, a_all, na, cudaMemcpyHostToDevice, e->stream));
+        if (nb) CUDA_TRY(e, cudaMemcpyAsync(d_rb.p, b_all, nb, cudaMemcpyHostToDevice, e->stream));
+        e->stats.h2d_bytes += (double)na + (double)nb;
+    }
 
     size_t pos = 0;
     while (pos < work.size()) {
@@ -160,19 +191,28 @@ static int align_batch_impl(swb_engine *e, const char *a_all, const int64_t *off
         CUDA_TRY(e, d_pairs.alloc(np * sizeof(KWPair), e->stream)); CUDA_TRY(e, d_res.alloc(np * sizeof(KWResult), e->stream));
         CUDA_TRY(e, d_bnd.alloc(plan.bnd_elems * sizeof(int4), e->stream));
         CUDA_TRY(e, d_scr.alloc(plan.scratch_ints * sizeof(int), e->stream));
-        CUDA_TRY(e, d_off.alloc(np * sizeof(int64_t), e->stream));
-        CUDA_TRY(e, d_xa.alloc(out_total * sizeof(int32_t), e->stream)); CUDA_TRY(e, d_xb.alloc(out_total * sizeof(int32_t), e->stream));
-        CUDA_TRY(e, d_nc.alloc(np * sizeof(int32_t), e->stream));
+        DevBuf d_st;
+        if (souts) out_total = 0;                                  // no column lists in the counting form
+        if (souts) CUDA_TRY(e, d_st.alloc(np * sizeof(KTStats), e->stream));
+        else {
+            CUDA_TRY(e, d_off.alloc(np * sizeof(int64_t), e->stream));
+            CUDA_TRY(e, d_xa.alloc(out_total * sizeof(int32_t), e->stream)); CUDA_TRY(e, d_xb.alloc(out_total * sizeof(int32_t), e->stream));
+            CUDA_TRY(e, d_nc.alloc(np * sizeof(int32_t), e->stream));
+            CUDA_TRY(e, cudaMemcpyAsync(d_off.p, out_off.data(), np * sizeof(int64_t), cudaMemcpyHostToDevice, e->stream));
+        }
         CUDA_TRY(e, cudaMemcpyAsync(d_pairs.p, hp.data(), np * sizeof(KWPair), cudaMemcpyHostToDevice, e->stream));
-        CUDA_TRY(e, cudaMemcpyAsync(d_off.p, out_off.data(), np * sizeof(int64_t), cudaMemcpyHostToDevice, e->stream));
         CUDA_TRY(e, cudaEventRecord(e->ev0, e->stream));
         CUDA_TRY(e, kw_launch(e, d_a.as<uint8_t>(), d_b.as<uint8_t>(), d_pairs.as<KWPair>(), np, plan, (uint8_t *)e->d_dir,
                               d_bnd.as<int4>(), d_scr.as<int>(), d_res.as<KWResult>(), e->stream, d_pssm.as<int32_t>()));
-        CUDA_TRY(e, kt_launch(e, d_pairs.as<KWPair>(), d_res.as<KWResult>(), np, (const uint8_t *)e->d_dir, plan.cols, d_off.as<int64_t>(),
-                              d_xa.as<int32_t>(), d_xb.as<int32_t>(), d_nc.as<int32_t>(), e->stream));
+        if (souts)
+            CUDA_TRY(e, kt_stats_launch(e, d_pairs.as<KWPair>(), d_res.as<KWResult>(), np, (const uint8_t *)e->d_dir, plan.cols,
+                                        d_ra.as<uint8_t>(), d_rb.as<uint8_t>(), d_st.as<KTStats>(), e->stream));
+        else
+            CUDA_TRY(e, kt_launch(e, d_pairs.as<KWPair>(), d_res.as<KWResult>(), np, (const uint8_t *)e->d_dir, plan.cols, d_off.as<int64_t>(),
+                                  d_xa.as<int32_t>(), d_xb.as<int32_t>(), d_nc.as<int32_t>(), e->stream));
         CUDA_TRY(e, cudaEventRecord(e->ev1, e->stream));
         // results land in the engine's pinned traceback arena (a pageable destination would stage and block)
-        const size_t tb_need = (size_t)np * (sizeof(KWResult) + sizeof(int32_t)) + 2 * (size_t)out_total * sizeof(int32_t) + 64;
+        const size_t tb_need = (size_t)np * (sizeof(KWResult) + sizeof(int32_t) + sizeof(KTStats)) + 2 * (size_t)out_total * sizeof(int32_t) + 64;
         if (tb_need > e->tb_bytes) {
             if (e->h_tb) cudaFreeHost(e->h_tb);
             e->h_tb = nullptr; e->tb_bytes = 0;
@@ -182,14 +222,29 @@ static int align_batch_impl(swb_engine *e, const char *a_all, const int64_t *off
         KWResult *hr = (KWResult *)e->h_tb;
         int32_t *hnc = (int32_t *)(hr + np), *hxa = hnc + np, *hxb = hxa + out_total;
         CUDA_TRY(e, cudaMemcpyAsync(hr, d_res.p, np * sizeof(KWResult), cudaMemcpyDeviceToHost, e->stream));
-        CUDA_TRY(e, cudaMemcpyAsync(hnc, d_nc.p, np * sizeof(int32_t), cudaMemcpyDeviceToHost, e->stream));
-        CUDA_TRY(e, cudaMemcpyAsync(hxa, d_xa.p, out_total * sizeof(int32_t), cudaMemcpyDeviceToHost, e->stream));
-        CUDA_TRY(e, cudaMemcpyAsync(hxb, d_xb.p, out_total * sizeof(int32_t), cudaMemcpyDeviceToHost, e->stream));
+        KTStats *hst = (KTStats *)(hxb + out_total);
+        if (souts) CUDA_TRY(e, cudaMemcpyAsync(hst, d_st.p, np * sizeof(KTStats), cudaMemcpyDeviceToHost, e->stream));
+        else {
+            CUDA_TRY(e, cudaMemcpyAsync(hnc, d_nc.p, np * sizeof(int32_t), cudaMemcpyDeviceToHost, e->stream));
+            CUDA_TRY(e, cudaMemcpyAsync(hxa, d_xa.p, out_total * sizeof(int32_t), cudaMemcpyDeviceToHost, e->stream));
+            CUDA_TRY(e, cudaMemcpyAsync(hxb, d_xb.p, out_total * sizeof(int32_t), cudaMemcpyDeviceToHost, e->stream));
+        }
         CUDA_TRY(e, cudaStreamSynchronize(e->stream));
         float ms = 0; cudaEventElapsedTime(&ms, e->ev0, e->ev1);
         e->stats.kernel_ms += ms; e->stats.launches += 2;
         e->stats.h2d_bytes += (double)np * (sizeof(KWPair) + sizeof(int64_t));
-        e->stats.d2h_bytes += (double)np * (sizeof(KWResult) + 4) + 8.0 * out_total;
+        e->stats.d2h_bytes += (double)np * (sizeof(KWResult) + (souts ? sizeof(KTStats) : 4)) + 8.0 * out_total;
+        if (souts) {
+            for (int t = 0; t < np; ++t) {
+                const int64_t k = work[pos + t];
+                swb_aln_stats *o = &souts[k];
+                o->score = to_f(hr[t].score); o->end_a = hr[t].end_i; o->end_b = hr[t].end_j;
+                if (hst[t].ncols < 0) { o->status = SWB_ERR_EMPTY; continue; }      // the reference panics on this pair (SA.rs:360-371)
+                compose_stats(o, e->mode, retain_all, hp[t].la, hp[t].lb, hst[t]);
+            }
+            pos = end;
+            continue;
+        }
         // reverse + string inflation per pair: independent, spread over host threads for large batches
         std::atomic<int> next(0), fail(SWB_OK);
         auto worker = [&]() {
@@ -224,7 +279,17 @@ static int align_batch_impl(swb_engine *e, const char *a_all, const int64_t *off
 extern "C" int swb_align_batch(swb_engine *e, const char *a_all, const int64_t *off_a, const char *b_all,
                                const int64_t *off_b, int64_t n, unsigned flags, swb_alignment *outs)
 {
+    if (e && n > 0 && !outs) { e->err = "bad argument"; return SWB_ERR_ARG; }
     return align_batch_impl(e, a_all, off_a, b_all, off_b, n, flags, outs, nullptr);
+}
+
+// align(.., retain_all) of n pairs, reduced on the device to what the clustering loop reads off the strings
+// (OCL-main.rs:205-233): no column lists cross PCIe and no strings are built.
+extern "C" int swb_align_stats_batch(swb_engine *e, const char *a_all, const int64_t *off_a, const char *b_all,
+                                     const int64_t *off_b, int64_t n, unsigned flags, swb_aln_stats *outs)
+{
+    if (e && n > 0 && !outs) { e->err = "bad argument"; return SWB_ERR_ARG; }
+    return align_batch_impl(e, a_all, off_a, b_all, off_b, n, flags, nullptr, nullptr, outs);
 }
 
 // align() of an engine built over a PositionSpecificMatrix (SA.rs:583-623, KAT psm_test SA.rs:1057-1086): the score of

@@ -382,18 +382,22 @@ __device__ __forceinline__ int64_t kt_addr(int64_t dir_off, int la, int i, int j
     return dir_off + ((int64_t)sidx * (la + 31) + t) * SW + within;
 }
 
-template <int MODE, int COLS>
+// STATS: count instead of listing (KTStats; raw_a / raw_b = the sequences as given, for the equal-letter test).
+template <int MODE, int COLS, bool STATS>
 __global__ void kt_kernel(const KWPair *__restrict__ pairs, const KWResult *__restrict__ res, int n_pairs,
                           const uint8_t *__restrict__ dir, const int64_t *__restrict__ out_off,
-                          int32_t *__restrict__ idx_a, int32_t *__restrict__ idx_b, int32_t *__restrict__ ncols, int sent)
+                          int32_t *__restrict__ idx_a, int32_t *__restrict__ idx_b, int32_t *__restrict__ ncols, int sent,
+                          const uint8_t *__restrict__ raw_a, const uint8_t *__restrict__ raw_b, KTStats *__restrict__ stats)
 {
     const int p = blockIdx.x * blockDim.x + threadIdx.x;
     if (p >= n_pairs) return;
     const KWPair P = pairs[p];
     const KWResult R = res[p];
-    int32_t *xa = idx_a + out_off[p], *xb = idx_b + out_off[p];
+    int32_t *xa = STATS ? nullptr : idx_a + out_off[p], *xb = STATS ? nullptr : idx_b + out_off[p];
+    const uint8_t *ra = STATS ? raw_a + P.a_off : nullptr, *rb = STATS ? raw_b + P.b_off : nullptr;
+    KTStats S; S.ncols = 0; S.na = 0; S.nb = 0; S.match = 0; S.s1 = -1; S.e1 = -1; S.s2 = -1; S.e2 = -1;
     int n = 0;
-    if (R.end_i < 0) { ncols[p] = 0; return; }                     // SA.rs:346-348
+    if (R.end_i < 0) { if (STATS) stats[p] = S; else ncols[p] = 0; return; }   // SA.rs:346-348
     int cx = R.end_i, cy = R.end_j, st = R.state;
     for (;;) {
         unsigned prev;
@@ -412,20 +416,32 @@ __global__ void kt_kernel(const KWPair *__restrict__ pairs, const KWResult *__re
             if (MODE == SWB_LOCAL && (st == 2 || sent == 0)) prev = 3;
         }
         if (MODE == SWB_LOCAL && prev == 3) break;
+        // (the walk runs end -> start: the first index seen is the last of the alignment)
         if (st == 0) {
             if (cx == 0 || cy == 0) { n = -2; break; }             // reference underflows / panics
-            xa[n] = cx - 1; xb[n] = cy - 1; ++n; --cx; --cy;
+            if (STATS) {
+                if (S.e1 < 0) S.e1 = cx - 1;
+                if (S.e2 < 0) S.e2 = cy - 1;
+                S.s1 = cx - 1; S.s2 = cy - 1; ++S.na; ++S.nb;
+                S.match += (ra[cx - 1] == rb[cy - 1]) ? 1 : 0;
+            } else { xa[n] = cx - 1; xb[n] = cy - 1; }
+            ++n; --cx; --cy;
         } else if (st == 1) {
             if (cy == 0) { n = -2; break; }
-            xa[n] = -1; xb[n] = cy - 1; ++n; --cy;
+            if (STATS) { if (S.e2 < 0) S.e2 = cy - 1; S.s2 = cy - 1; ++S.nb; }
+            else { xa[n] = -1; xb[n] = cy - 1; }
+            ++n; --cy;
         } else {
             if (cx == 0) { n = -2; break; }                        // SA.rs:369-371
-            xa[n] = cx - 1; xb[n] = -1; ++n; --cx;
+            if (STATS) { if (S.e1 < 0) S.e1 = cx - 1; S.s1 = cx - 1; ++S.na; }
+            else { xa[n] = cx - 1; xb[n] = -1; }
+            ++n; --cx;
         }
         if (cx == 0 && cy == 0) break;
         st = (int)prev;
     }
-    ncols[p] = n;
+    if (STATS) { S.ncols = n; stats[p] = S; }
+    else ncols[p] = n;
 }
 
 cudaError_t kt_launch(const swb_engine *e, const KWPair *d_pairs, const KWResult *d_res, int n_pairs,
@@ -435,8 +451,26 @@ cudaError_t kt_launch(const swb_engine *e, const KWPair *d_pairs, const KWResult
     if (n_pairs <= 0) return cudaSuccess;
     const int threads = 32, blocks = (n_pairs + threads - 1) / threads;
     const int sent = 10 * e->o + 10 * e->e;
-#define KT_GO(M) do { if (cols == 2) kt_kernel<M, 2><<<blocks, threads, 0, st>>>(d_pairs, d_res, n_pairs, d_dir, d_out_off, d_idx_a, d_idx_b, d_ncols, sent); \
-                      else kt_kernel<M, 8><<<blocks, threads, 0, st>>>(d_pairs, d_res, n_pairs, d_dir, d_out_off, d_idx_a, d_idx_b, d_ncols, sent); } while (0)
+#define KT_GO(M) do { if (cols == 2) kt_kernel<M, 2, false><<<blocks, threads, 0, st>>>(d_pairs, d_res, n_pairs, d_dir, d_out_off, d_idx_a, d_idx_b, d_ncols, sent, nullptr, nullptr, nullptr); \
+                      else kt_kernel<M, 8, false><<<blocks, threads, 0, st>>>(d_pairs, d_res, n_pairs, d_dir, d_out_off, d_idx_a, d_idx_b, d_ncols, sent, nullptr, nullptr, nullptr); } while (0)
+    switch (e->mode) {
+    case SWB_GLOBAL: KT_GO(SWB_GLOBAL); break;
+    case SWB_GLOCAL: KT_GO(SWB_GLOCAL); break;
+    default: KT_GO(SWB_LOCAL); break;
+    }
+#undef KT_GO
+    return cudaGetLastError();
+}
+
+cudaError_t kt_stats_launch(const swb_engine *e, const KWPair *d_pairs, const KWResult *d_res, int n_pairs,
+                            const uint8_t *d_dir, int cols, const uint8_t *d_raw_a, const uint8_t *d_raw_b,
+                            KTStats *d_stats, cudaStream_t st)
+{
+    if (n_pairs <= 0) return cudaSuccess;
+    const int threads = 32, blocks = (n_pairs + threads - 1) / threads;
+    const int sent = 10 * e->o + 10 * e->e;
+#define KT_GO(M) do { if (cols == 2) kt_kernel<M, 2, true><<<blocks, threads, 0, st>>>(d_pairs, d_res, n_pairs, d_dir, nullptr, nullptr, nullptr, nullptr, sent, d_raw_a, d_raw_b, d_stats); \
+                      else kt_kernel<M, 8, true><<<blocks, threads, 0, st>>>(d_pairs, d_res, n_pairs, d_dir, nullptr, nullptr, nullptr, nullptr, sent, d_raw_a, d_raw_b, d_stats); } while (0)
     switch (e->mode) {
     case SWB_GLOBAL: KT_GO(SWB_GLOBAL); break;
     case SWB_GLOCAL: KT_GO(SWB_GLOCAL); break;

@@ -132,5 +132,16 @@ cudaError_t kt_launch(const swb_engine *e, const KWPair *d_pairs, const KWResult
                       const uint8_t *d_dir, int cols, const int64_t *d_out_off, int32_t *d_idx_a, int32_t *d_idx_b,
                       int32_t *d_ncols, cudaStream_t st);
 
+// KT, counting form: the same walk, but instead of the column lists it returns what the clustering loop needs.
+struct KTStats {
+    int32_t ncols;                  // columns of the core alignment; < 0 = the reference's panic cases
+    int32_t na, nb;                 // letters of a / b in the core
+    int32_t match;                  // columns with two equal letters (raw bytes)
+    int32_t s1, e1, s2, e2;         // first / last residue index of a and of b in the core, -1 = none
+};
+cudaError_t kt_stats_launch(const swb_engine *e, const KWPair *d_pairs, const KWResult *d_res, int n_pairs,
+                            const uint8_t *d_dir, int cols, const uint8_t *d_raw_a, const uint8_t *d_raw_b,
+                            KTStats *d_stats, cudaStream_t st);
+
 // K0
 cudaError_t k0_run(int which, int sm_count, double *thread_instr_per_s);

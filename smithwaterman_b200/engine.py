@@ -275,6 +275,18 @@ class SequenceAlignment:
             for k in range(n):
                 self.L.swb_alignment_free(ctypes.byref(outs[k]))
 
+    def align_stats(self, seqs_a, seqs_b, retain_all=False):
+        """align(a, b, retain_all) of n pairs reduced on the device to the counts the clustering loop reads off the
+        strings (OCL-main.rs:205-233) -> numpy record array (score, status, end_a, end_b, aln_len, a_letters,
+        b_letters, matches); no strings are built and 48 bytes per pair come back."""
+        a, oa = pack_sequences(seqs_a)
+        b, ob = pack_sequences(seqs_b)
+        n = len(oa) - 1
+        out = np.zeros(max(n, 1), dtype=_lib.ALN_STATS_DTYPE)
+        self._check(self.L.swb_align_stats_batch(self._h, a.ctypes.data, oa.ctypes.data, b.ctypes.data, ob.ctypes.data, n,
+                                                 1 if retain_all else 0, out.ctypes.data))
+        return out[:n]
+
     def score_batch(self, seqs_a, seqs_b):
         a, oa = pack_sequences(seqs_a)
         b, ob = pack_sequences(seqs_b)

@@ -509,3 +509,65 @@ def test_fuzz_random_models(seed):
             r1, r2, s = oeng.align(sa[k].decode(), sb[k].decode(), bool(seed & 1))
             assert (out["aln_a"], out["aln_b"], out["score"]) == ("".join(r1), "".join(r2), s), (seed, mode, k)
         eng.close()
+
+
+def _string_counts(r):
+    ra, rb = r["aln_a"], r["aln_b"]
+    return (sum(1 for c in ra if c != "-"), sum(1 for c in rb if c != "-"),
+            sum(1 for x, y in zip(ra, rb) if x != "-" and y != "-" and x == y), len(ra))
+
+
+@pytest.mark.parametrize("retain_all", [False, True])
+@pytest.mark.parametrize("mode", [swb.ALIGN_LOCAL, swb.ALIGN_GLOCAL, swb.ALIGN_GLOBAL])
+def test_align_stats_equal_the_strings(mode, retain_all):
+    """swb_align_stats_batch (counts taken during the traceback walk on the device) == the same counts read off the
+    strings of swb_align_batch, which is what the clustering loop of the reference does (OCL-main.rs:205-233).
+    Letters the matrix does not know (J, O, U -> scored as X) must not count as equal unless they ARE equal."""
+    rng = np.random.default_rng(77 + mode * 2 + int(retain_all))
+    m = swb.SubstitutionMatrix.get_blosum62_matrix()
+    eng = swb.SequenceAlignment(m, 10.0, 0.5, mode)
+    base = _rand_seqs(rng, 30, 30, 400)
+    sa, sb = [], []
+    for s in base:
+        for _ in range(3):
+            sa.append(s); sb.append(_mutate(rng, s, 0.15, 0.03, 0.03, alphabet=AA.encode()))
+    sa += _rand_seqs(rng, 40, 1, 300); sb += _rand_seqs(rng, 40, 1, 300)           # unrelated pairs, short ones included
+    sa += [b"JJJJOUJOUWWWW", b"ACDEFGHIKL", b"", b"AAAA"]; sb += [b"OJJJOUJUUWWWW", b"ACDEFGHIKL", b"ACD", b""]
+    st = eng.align_stats(sa, sb, retain_all)
+    res = eng.align_list(sa, sb, retain_all)
+    assert (st["status"] == 0).all()
+    for k, r in enumerate(res):
+        assert (int(st["a_letters"][k]), int(st["b_letters"][k]), int(st["matches"][k]), int(st["aln_len"][k])) == _string_counts(r), k
+        assert float(st["score"][k]) == r["score"] and (int(st["end_a"][k]), int(st["end_b"][k])) == (r["end_a"], r["end_b"]), k
+    eng.close()
+
+
+def test_cluster_with_device_counts_equals_strings():
+    """`-cluster` driven by swb_align_stats_batch makes the decisions of the string-reading loop (OCL-main.rs:149-243)."""
+    import io
+    from smithwaterman_b200 import cli
+    rng = np.random.default_rng(4242)
+    seqs = []
+    for f, s in enumerate(_rand_seqs(rng, 12, 80, 300)):
+        seqs.append(swb.SeqData.create("f%d_0" % f, "", s.decode()))
+        for v in range(1, 6):
+            t = _mutate(rng, s, 0.02 * v * v, 0.01 * v, 0.01 * v, alphabet=AA.encode())
+            if v == 5:
+                t = t[: len(t) // 2]                                 # a fragment: fails the coverage of the long sequence
+            seqs.append(swb.SeqData.create("f%d_%d" % (f, v), "", t.decode()))
+    seqs.append(swb.SeqData.create("dup", "", "".join(seqs[0].seq)))
+    seqs = [seqs[k] for k in rng.permutation(len(seqs))]
+    eng = swb.SequenceAlignment(swb.SubstitutionMatrix.get_blosum62_matrix(), 10.0, 0.5, swb.ALIGN_LOCAL)
+
+    def align_many(rep, cands):
+        return [(r["aln_a"], r["aln_b"]) for r in eng.align_list([rep] * len(cands), cands, False)]
+
+    def stats_many(rep, cands):
+        st = eng.align_stats([rep] * len(cands), cands, False)
+        return list(zip(st["a_letters"].tolist(), st["b_letters"].tolist(), st["matches"].tolist(), st["aln_len"].tolist()))
+    s1, c1, m1 = cli.cluster(seqs, align_many, 0.8, 0.8, 0.8, io.StringIO())
+    s2, c2, m2 = cli.cluster(seqs, None, 0.8, 0.8, 0.8, io.StringIO(), stats_many=stats_many)
+    assert [s.name for s in s1] == [s.name for s in s2] and c1 == c2 and m1 == m2
+    n_clusters = sum(1 for k, c in enumerate(c1) if c == k)
+    assert 12 <= n_clusters < len(seqs)
+    eng.close()
