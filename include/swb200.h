@@ -13,6 +13,7 @@
  *   swb_align_pssm         align over a PositionSpecificMatrix  SA.rs:583-623 (ScoringMatrix trait SA.rs:574-580)
  *   swb_align_batch        the serial loop of `sa_opencl -list`  OCL-main.rs:295-316 (one call, n pairs)
  *   swb_align_stats_batch  align + the identity / coverage counts of `sa_opencl -cluster`  OCL-main.rs:187-243
+ *   swb_cluster            the clustering loop of `sa_opencl -cluster`  OCL-main.rs:149-243
  *   swb_score_batch        align_partial(.., score_only=true) per pair  SA.rs:393-467
  *   swb_search_scores      the all-vs-all loops of the CLIs with one fixed query (SA-main.rs:35-45), n subjects per call
  *   swb_batch_*            the same as swb_score_batch, split into upload / run / fetch so that a
@@ -130,6 +131,18 @@ typedef struct swb_aln_stats {
 } swb_aln_stats;
 int swb_align_stats_batch(swb_engine *e, const char *a_all, const int64_t *off_a, const char *b_all,
                           const int64_t *off_b, int64_t n, unsigned flags, swb_aln_stats *outs);
+
+/* The clustering loop of `sa_opencl -cluster` itself (OCL-main.rs:149-243): sequences sorted longest first (stable),
+ * exact duplicates folded, then every still-unclustered sequence becomes a representative and takes the later ones that
+ * it contains (length ratio >= coverage_long) or that align to it with coverage of the long / short sequence and
+ * identity at or above the thresholds (f64 ratios of the counts of align(rep, cand, false), as the reference).  The
+ * sequences stay on the device for the whole run; one batch per representative.  Outputs, all of length n and indexed
+ * by SORTED position: order[p] = input index of the sequence at position p; cluster_of[p] = position of its
+ * representative (p itself for representatives and, as in the reference, for folded duplicates); identical[p] =
+ * position of the first exact copy (p if none before it).  n_alignments (may be NULL): alignments computed. */
+int swb_cluster(swb_engine *e, const char *seq_all, const int64_t *off, int64_t n, double identity,
+                double coverage_short, double coverage_long, int64_t *order, int64_t *cluster_of, int64_t *identical,
+                int64_t *n_alignments);
 
 /* Score + end cell of n pairs, HOST buffers in and out (H2D, kernels, D2H inside the call).
  * scores[k] as the reference's f32; end_a/end_b: first-maximum cell (local, SA.rs:286-294;

@@ -87,6 +87,7 @@ def lib():
         "swb_align_batch": (c.c_int, [vp, vp, vp, vp, vp, i64, c.c_uint, c.POINTER(Alignment)]),
         "swb_alignment_free": (None, [c.POINTER(Alignment)]),
         "swb_align_stats_batch": (c.c_int, [vp, vp, vp, vp, vp, i64, c.c_uint, vp]),
+        "swb_cluster": (c.c_int, [vp, vp, vp, i64, c.c_double, c.c_double, c.c_double, vp, vp, vp, vp]),
         "swb_score_batch": (c.c_int, [vp, vp, vp, vp, vp, i64, vp, vp, vp]),
         "swb_search_scores": (c.c_int, [vp, vp, i64, vp, vp, i64, vp, vp, vp]),
         "swb_batch_upload": (c.c_int, [vp, vp, vp, vp, vp, i64, c.POINTER(vp)]),

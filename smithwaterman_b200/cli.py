@@ -108,13 +108,14 @@ def cluster(seqs, align_many, identity=0.8, coverage_short=0.8, coverage_long=0.
     seqs: list of SeqData; align_many(rep, candidates) -> list of (aln_a, aln_b) strings of align(rep, cand, false).
     stats_many(rep, candidates) -> list of (a_letters, b_letters, matches, aln_len), the four numbers the loop reads off
     those strings (OCL-main.rs:205-233); when given it is used instead of align_many (the device counts them during
-    the traceback walk, `swb_align_stats_batch`).
+    the traceback walk, `swb_align_stats_batch`) and receives the sequences as bytes, converted once.
     Returns (sorted sequences, cluster_of, members) exactly as the reference's loop leaves them.
     """
     seq1 = sorted(seqs, key=lambda s: -len(s.seq))                      # stable, longest first (OCL-main.rs:151)
     n = len(seq1)
     strs = ["".join(s.seq) for s in seq1]
     blen = [len(s.encode("utf-8")) for s in strs]                         # String::len() is a byte length
+    raw = [s.as_bytes() for s in seq1] if stats_many is not None else None
     cluster_of, identical = list(range(n)), list(range(n))
     members = [[] for _ in range(n)]
     identical_members = [[] for _ in range(n)]
@@ -140,7 +141,7 @@ def cluster(seqs, align_many, identity=0.8, coverage_short=0.8, coverage_long=0.
         if not need:
             alns = {}
         elif stats_many is not None:
-            alns = dict(zip(need, stats_many(seq1[ii], [seq1[jj] for jj in need])))
+            alns = dict(zip(need, stats_many(raw[ii], [raw[jj] for jj in need])))
         else:
             alns = {}
             for jj, (ra, rb) in zip(need, align_many(seq1[ii], [seq1[jj] for jj in need])):
@@ -168,6 +169,27 @@ def cluster(seqs, align_many, identity=0.8, coverage_short=0.8, coverage_long=0.
     return seq1, cluster_of, members
 
 
+def cluster_native(engine, seqs, identity=0.8, coverage_short=0.8, coverage_long=0.8, out=sys.stdout):
+    """The same loop run by the library (`swb_cluster`: sequences resident on the device, one batch per
+    representative).  Returns what cluster() returns; the member lists are rebuilt in the order the reference appends
+    them (a representative and its exact copies first, then every sequence that joined, each followed by its copies)."""
+    order, cl, ident, _ = engine.cluster(seqs, identity, coverage_short, coverage_long)
+    n = len(order)
+    seq1 = [seqs[k] for k in order.tolist()]
+    cluster_of, identical = cl.tolist(), ident.tolist()
+    copies = [[] for _ in range(n)]
+    for p in range(n):
+        copies[identical[p]].append(p)                                   # the first copy heads its own list
+    members = [[] for _ in range(n)]
+    for p in range(n):
+        if identical[p] == p:
+            members[cluster_of[p]].extend(copies[p])
+    for p in range(n):                                                   # progress lines of OCL-main.rs:240-242
+        if cluster_of[p] == p and identical[p] == p and (p + 1) % 10 == 0:
+            out.write("%d sequences were processed.\n" % (p + 1))
+    return seq1, cluster_of, members
+
+
 def write_clusters(outfilename, seq1, cluster_of, members):
     """Representative FASTA + .clstr member lists, OCL-main.rs:244-265."""
     with open(outfilename, "w") as f:
@@ -191,20 +213,10 @@ def main(argv=None, out=sys.stdout):
         if opp.clustering:
             seqs = SeqData.load_fasta(opp.file1, False)
 
-            def align_many(rep, cands):
-                res = engine.align_list([rep] * len(cands), cands, False)
-                return [(r["aln_a"], r["aln_b"]) for r in res]
-
-            def stats_many(rep, cands):
-                st = engine.align_stats([rep] * len(cands), cands, False)
-                if (st["status"] != 0).any():
-                    raise RuntimeError("the traceback left the matrix (the reference panics here, SA.rs:360-371)")
-                return list(zip(st["a_letters"].tolist(), st["b_letters"].tolist(), st["matches"].tolist(), st["aln_len"].tolist()))
-            seq1, cluster_of, members = cluster(seqs, align_many,
-                                                opp.c_identity if opp.c_identity is not None else 0.8,
-                                                opp.c_coverage_short if opp.c_coverage_short is not None else 0.8,
-                                                opp.c_coverage_long if opp.c_coverage_long is not None else 0.8, out,
-                                                stats_many=stats_many)
+            seq1, cluster_of, members = cluster_native(engine, seqs,
+                                                       opp.c_identity if opp.c_identity is not None else 0.8,
+                                                       opp.c_coverage_short if opp.c_coverage_short is not None else 0.8,
+                                                       opp.c_coverage_long if opp.c_coverage_long is not None else 0.8, out)
             write_clusters(opp.outfilename, seq1, cluster_of, members)
         else:
             filelist = read_list(opp.file1, out) if opp.list else [(opp.file1, opp.file2)]

@@ -71,7 +71,7 @@ extern "C" void swb_alignment_free(swb_alignment *a)
 }
 
 // The strings' statistics from the core alignment's counts (inflate() above without building anything).
-static void compose_stats(swb_aln_stats *o, int mode, bool retain_all, int64_t la, int64_t lb, const KTStats &S)
+void swb_compose_stats(swb_aln_stats *o, int mode, bool retain_all, int64_t la, int64_t lb, const KTStats &S)
 {
     if (mode == SWB_LOCAL && !retain_all) {                                               // SA.rs:502-504
         o->aln_len = S.ncols; o->a_letters = S.na; o->b_letters = S.nb; o->matches = S.match;
@@ -126,7 +126,7 @@ static int align_batch_impl(swb_engine *e, const char *a_all, const int64_t *off
             S.s1 = la ? 0 : -1; S.e1 = (int32_t)la - 1; S.s2 = lb ? 0 : -1; S.e2 = (int32_t)lb - 1;
             if (e->mode == SWB_LOCAL) { S.ncols = 0; S.na = 0; S.nb = 0; S.s1 = S.s2 = S.e1 = S.e2 = -1; }
             souts[k].score = score; souts[k].end_a = ei; souts[k].end_b = ej;
-            compose_stats(&souts[k], e->mode, retain_all, la, lb, S);
+            swb_compose_stats(&souts[k], e->mode, retain_all, la, lb, S);
             continue;
         }
         inflate(a_all + off_a[k], la, b_all + off_b[k], lb, xa.data(), xb.data(), (int64_t)xa.size(), e->mode, retain_all, ra, rb);
@@ -240,7 +240,7 @@ static int align_batch_impl(swb_engine *e, const char *a_all, const int64_t *off
                 swb_aln_stats *o = &souts[k];
                 o->score = to_f(hr[t].score); o->end_a = hr[t].end_i; o->end_b = hr[t].end_j;
                 if (hst[t].ncols < 0) { o->status = SWB_ERR_EMPTY; continue; }      // the reference panics on this pair (SA.rs:360-371)
-                compose_stats(o, e->mode, retain_all, hp[t].la, hp[t].lb, hst[t]);
+                swb_compose_stats(o, e->mode, retain_all, hp[t].la, hp[t].lb, hst[t]);
             }
             pos = end;
             continue;

@@ -143,5 +143,8 @@ cudaError_t kt_stats_launch(const swb_engine *e, const KWPair *d_pairs, const KW
                             const uint8_t *d_dir, int cols, const uint8_t *d_raw_a, const uint8_t *d_raw_b,
                             KTStats *d_stats, cudaStream_t st);
 
+// The statistics of the strings align(.., retain_all) would return, from the core alignment's counts (align.cu).
+void swb_compose_stats(swb_aln_stats *o, int mode, bool retain_all, int64_t la, int64_t lb, const KTStats &S);
+
 // K0
 cudaError_t k0_run(int which, int sm_count, double *thread_instr_per_s);

@@ -168,7 +168,7 @@ def _as_seq_bytes(s):
 
 def pack_sequences(seqs):
     """list of str/bytes/SeqData -> (uint8 array, int64 offsets[n+1])."""
-    bs = [_as_seq_bytes(s) for s in seqs]
+    bs = [s if type(s) is bytes else _as_seq_bytes(s) for s in seqs]
     off = np.zeros(len(bs) + 1, np.int64)
     if bs:
         off[1:] = np.cumsum([len(b) for b in bs])
@@ -276,16 +276,31 @@ class SequenceAlignment:
                 self.L.swb_alignment_free(ctypes.byref(outs[k]))
 
     def align_stats(self, seqs_a, seqs_b, retain_all=False):
-        """align(a, b, retain_all) of n pairs reduced on the device to the counts the clustering loop reads off the
+        """align(a, b, retain_all) of n pairs (seqs_a may be ONE sequence to be aligned with every b) reduced on the device to the counts the clustering loop reads off the
         strings (OCL-main.rs:205-233) -> numpy record array (score, status, end_a, end_b, aln_len, a_letters,
         b_letters, matches); no strings are built and 48 bytes per pair come back."""
-        a, oa = pack_sequences(seqs_a)
         b, ob = pack_sequences(seqs_b)
+        if isinstance(seqs_a, (bytes, str, SeqData)):         # one sequence against all of seqs_b
+            one = np.frombuffer(_as_seq_bytes(seqs_a), np.uint8)
+            a, oa = np.tile(one, len(ob) - 1), np.arange(len(ob), dtype=np.int64) * len(one)
+        else:
+            a, oa = pack_sequences(seqs_a)
         n = len(oa) - 1
         out = np.zeros(max(n, 1), dtype=_lib.ALN_STATS_DTYPE)
         self._check(self.L.swb_align_stats_batch(self._h, a.ctypes.data, oa.ctypes.data, b.ctypes.data, ob.ctypes.data, n,
                                                  1 if retain_all else 0, out.ctypes.data))
         return out[:n]
+
+    def cluster(self, seqs, identity=0.8, coverage_short=0.8, coverage_long=0.8):
+        """The clustering loop of `sa_opencl -cluster` (OCL-main.rs:149-243) with the sequences resident on the device
+        -> (order, cluster_of, identical, n_alignments), the arrays indexed by sorted position (see swb_cluster)."""
+        s, off = pack_sequences(seqs)
+        n = len(off) - 1
+        order = np.zeros(max(n, 1), np.int64); cl = np.zeros(max(n, 1), np.int64); ident = np.zeros(max(n, 1), np.int64)
+        nal = ctypes.c_int64(0)
+        self._check(self.L.swb_cluster(self._h, s.ctypes.data, off.ctypes.data, n, float(identity), float(coverage_short),
+                                       float(coverage_long), order.ctypes.data, cl.ctypes.data, ident.ctypes.data, ctypes.byref(nal)))
+        return order[:n], cl[:n], ident[:n], nal.value
 
     def score_batch(self, seqs_a, seqs_b):
         a, oa = pack_sequences(seqs_a)

@@ -570,4 +570,28 @@ def test_cluster_with_device_counts_equals_strings():
     assert [s.name for s in s1] == [s.name for s in s2] and c1 == c2 and m1 == m2
     n_clusters = sum(1 for k, c in enumerate(c1) if c == k)
     assert 12 <= n_clusters < len(seqs)
+    # the loop run by the library (swb_cluster, sequences resident on the device), other thresholds as well
+    for thr in ((0.8, 0.8, 0.8), (0.5, 0.3, 0.9), (0.95, 0.9, 0.9)):
+        sp, cp, mp = cli.cluster(seqs, None, *thr, io.StringIO(), stats_many=stats_many)
+        sn, cn, mn = cli.cluster_native(eng, seqs, *thr, io.StringIO())
+        assert [s.name for s in sp] == [s.name for s in sn] and cp == cn and mp == mn, thr
     eng.close()
+
+
+def test_cli_cluster_files(tmp_path):
+    """`sa_opencl -cluster -out F x.fas` end to end: representative FASTA + .clstr member lists (OCL-main.rs:244-265)."""
+    import io
+    from smithwaterman_b200 import cli
+    rng = np.random.default_rng(5)
+    recs = []
+    for f, s in enumerate(_rand_seqs(rng, 5, 120, 200)):
+        for v in range(4):
+            recs.append((">s%d_%d family %d" % (f, v, f), _mutate(rng, s, 0.03 * v, 0.0, 0.0, alphabet=AA.encode()).decode()))
+    recs.append((">copy of s0_0", recs[0][1]))
+    (tmp_path / "in.fas").write_text("".join("%s\n%s\n" % r for r in recs))
+    assert cli.main(["-cluster", "-identity", "0.8", "-out", str(tmp_path / "o.fas"), str(tmp_path / "in.fas")], io.StringIO()) == 0
+    reps = [ln[1:].split()[0] for ln in (tmp_path / "o.fas").read_text().splitlines() if ln.startswith(">")]
+    lists = [ln.split() for ln in (tmp_path / "o.fas.clstr").read_text().splitlines()]
+    assert sorted(x for l in lists for x in l) == sorted(r[0][1:].split()[0] for r in recs)       # every sequence in exactly one list
+    assert len(lists) == 5 and all(len(l) >= 4 for l in lists)
+    assert {l[0] for l in lists} <= set(reps)                                                    # a list starts with its representative
