@@ -39,6 +39,21 @@ def build(force=False, verbose=False):
     return SO_PATH
 
 
+CLI_SRC = os.path.join(os.path.dirname(HEADER), "..", "tools", "swbcli.cpp")
+CLI_PATH = os.path.join(os.path.dirname(SO_PATH), "swbcli")
+
+
+def build_cli(force=False):
+    """g++ tools/swbcli.cpp (the C++ host mirror include/swb200.hpp + the reference's command lines) -> swbcli."""
+    src = os.path.normpath(CLI_SRC)
+    hpp = os.path.join(os.path.dirname(HEADER), "swb200.hpp")
+    if not force and os.path.exists(CLI_PATH) and all(os.path.getmtime(CLI_PATH) >= os.path.getmtime(p) for p in (src, hpp, HEADER, SO_PATH)):
+        return CLI_PATH
+    subprocess.check_call([os.environ.get("CXX", "g++"), "-O2", "-std=c++17", "-Wall", "-I", os.path.dirname(HEADER), src,
+                           "-L", os.path.dirname(SO_PATH), "-lswb200", "-Wl,-rpath,$ORIGIN", "-o", CLI_PATH])
+    return CLI_PATH
+
+
 class Matrix(ctypes.Structure):
     _fields_ = [("n_letters", ctypes.c_int32), ("letters", ctypes.c_char_p), ("scores", ctypes.POINTER(ctypes.c_float))]
 

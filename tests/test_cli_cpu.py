@@ -118,3 +118,33 @@ def test_cluster_batched_equals_serial(thr, tmp_path):
     assert reps[0] == ">%s %s" % (got[0][0].name, got[0][0].desc) and reps[1] == "".join(got[0][0].seq)
     lines = (tmp_path / "o.fas.clstr").read_text().strip().split("\n")
     assert sorted(x for ln in lines for x in ln.split(" ")) == sorted(s.name for s in seqs)
+
+
+def _swbcli():
+    from smithwaterman_b200 import _lib
+    _lib.build()
+    return _lib.build_cli()
+
+
+def test_cpp_host_mirror_fasta_and_formatting(tmp_path):
+    """include/swb200.hpp (the C++ mirror of the reference's Rust API) reads FASTA and prints scores like the Python
+    mirror (SA.rs:830-887 header rules; Rust `{}` of an f32, SA-main.rs:40).  No device needed."""
+    import subprocess
+    from smithwaterman_b200.engine import SeqData, rust_f32_display
+    p = tmp_path / "odd.fas"
+    p.write_text(">a1 first  description here\nACDE FGH\r\nIKL\n>b2\nMNPQ\n  > c3\ttabbed desc \nRST\n>\nVW\nno header > inside name x\nYY\n")
+    out = subprocess.run([_swbcli(), "-dumpfasta", str(p)], capture_output=True, text=True, check=True).stdout.splitlines()
+    want = ["name=%s|desc=%s|seq=%s" % (s.name, s.desc, "".join(s.seq)) for s in SeqData.load_fasta(str(p), False)]
+    assert out == want and len(out) >= 4
+    vals = ["485", "54.5", "-1770.5", "0", "0.1", "1234567.5", "-0.25", "3.4028235e38", "16777216", "0.3"]
+    got = subprocess.run([_swbcli(), "-f32"] + vals, capture_output=True, text=True, check=True).stdout.split()
+    assert got == [rust_f32_display(np.float32(v)) for v in vals]
+
+
+def test_cpp_cli_option_errors():
+    import subprocess
+    exe = _swbcli()
+    assert subprocess.run([exe], capture_output=True).returncode == 255                      # usage (SA-main.rs:12-15)
+    for bad in (["-nope", "a", "b"], ["-cluster", "x.fas"], ["-list", "-cluster", "x", "-out", "o"], ["a", "b", "c"]):
+        r = subprocess.run([exe] + bad, capture_output=True, text=True)
+        assert r.returncode == 1 and "error" in r.stderr, bad

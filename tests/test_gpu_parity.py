@@ -595,3 +595,68 @@ def test_cli_cluster_files(tmp_path):
     assert sorted(x for l in lists for x in l) == sorted(r[0][1:].split()[0] for r in recs)       # every sequence in exactly one list
     assert len(lists) == 5 and all(len(l) >= 4 for l in lists)
     assert {l[0] for l in lists} <= set(reps)                                                    # a list starts with its representative
+
+
+def _swbcli():
+    from smithwaterman_b200 import _lib
+    _lib.build()
+    return _lib.build_cli()
+
+
+@pytest.mark.parametrize("flag,key", [("-local", "local"), ("-glocal", "glocal"), ("-global", "global")])
+def test_cpp_cli_list_mode_vs_emboss(emboss, flag, key, tmp_path):
+    """The compiled command line (tools/swbcli.cpp over include/swb200.hpp, the C++ mirror of the reference's Rust API):
+    `sa_opencl [-mode] -list L` against test/emboss_results, and byte-identical stdout with the Python mirror."""
+    import io
+    import subprocess
+    from smithwaterman_b200 import cli
+    recs = emboss[:30]
+    lines = []
+    for r in recs:
+        f1, f2 = tmp_path / ("seq%s.1.fas" % r["id"]), tmp_path / ("seq%s.2.fas" % r["id"])
+        f1.write_text(">a%s some description\n%s\n" % (r["id"], "\n".join(r["seq1"][k:k + 60] for k in range(0, len(r["seq1"]), 60))))
+        f2.write_text(">b%s\n%s\n" % (r["id"], r["seq2"]))
+        lines.append("%s\t%s" % (f1, f2))
+    (tmp_path / "list.txt").write_text("\n".join(lines) + "\n")
+    got = subprocess.run([_swbcli(), flag, "-list", str(tmp_path / "list.txt")], capture_output=True, text=True, check=True).stdout
+    blocks = got.split("#score:")[1:]
+    assert len(blocks) == len(recs)
+    for r, blk in zip(recs, blocks):
+        ln = blk.split("\n")
+        s1, s2 = ln[3], ln[6]
+        if key == "local":
+            s1, s2 = trim_terminal(s1, s2)
+        assert (s1, s2) == (r[key]["s1"], r[key]["s2"]), r["id"]
+        assert float(ln[0]) == r[key]["score"]
+    out = io.StringIO()
+    assert cli.main([flag, "-list", str(tmp_path / "list.txt")], out) == 0
+    assert out.getvalue() == got
+    # pair mode and -out (the reference writes no newline after #score / #type there, OCL-main.rs:303-307)
+    f1, f2 = lines[0].split("\t")
+    pair = subprocess.run([_swbcli(), flag, f1, f2], capture_output=True, text=True, check=True).stdout
+    assert pair == "#score:" + blocks[0]
+    subprocess.run([_swbcli(), flag, "-list", str(tmp_path / "list.txt"), "-out", str(tmp_path / "cpp.out")], check=True, capture_output=True)
+    assert cli.main([flag, "-list", str(tmp_path / "list.txt"), "-out", str(tmp_path / "py.out")], io.StringIO()) == 0
+    assert (tmp_path / "cpp.out").read_text() == (tmp_path / "py.out").read_text()
+
+
+def test_cpp_cli_cluster_equals_python(tmp_path):
+    import io
+    import subprocess
+    from smithwaterman_b200 import cli
+    rng = np.random.default_rng(11)
+    recs = []
+    for f, s in enumerate(_rand_seqs(rng, 8, 100, 260)):
+        for v in range(5):
+            recs.append((">q%d_%d fam %d  v%d" % (f, v, f, v), _mutate(rng, s, 0.04 * v, 0.01 * v, 0.0, alphabet=AA.encode()).decode()))
+    recs.append((">twin", recs[3][1]))
+    order = rng.permutation(len(recs))
+    (tmp_path / "in.fas").write_text("".join("%s\n%s\n" % recs[k] for k in order))
+    args = ["-cluster", "-identity", "0.7", "-coverage_short", "0.6", "-out"]
+    r = subprocess.run([_swbcli()] + args + [str(tmp_path / "c.fas"), str(tmp_path / "in.fas")], capture_output=True, text=True, check=True)
+    out = io.StringIO()
+    assert cli.main(args + [str(tmp_path / "p.fas"), str(tmp_path / "in.fas")], out) == 0
+    assert (tmp_path / "c.fas").read_text() == (tmp_path / "p.fas").read_text()
+    assert (tmp_path / "c.fas.clstr").read_text() == (tmp_path / "p.fas.clstr").read_text()
+    assert r.stdout == out.getvalue()
+    assert 8 <= len((tmp_path / "c.fas.clstr").read_text().splitlines()) < len(recs)
