@@ -660,3 +660,28 @@ def test_cpp_cli_cluster_equals_python(tmp_path):
     assert (tmp_path / "c.fas.clstr").read_text() == (tmp_path / "p.fas.clstr").read_text()
     assert r.stdout == out.getvalue()
     assert 8 <= len((tmp_path / "c.fas.clstr").read_text().splitlines()) < len(recs)
+
+
+def test_cpp_mirror_runs_the_reference_kats(rust_kats, tmp_path):
+    """tests/cpp/kats.cpp: the reference's known-answer tests written against include/swb200.hpp the way the Rust tests
+    are written against SequenceAlignment (SA.rs:921-1221)."""
+    import os
+    import subprocess
+    from smithwaterman_b200 import _lib
+    _lib.build()
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    exe = str(tmp_path / "kats")
+    subprocess.check_call(["g++", "-O1", "-std=c++17", "-I", os.path.join(root, "include"), os.path.join(root, "tests", "cpp", "kats.cpp"),
+                           "-L", os.path.dirname(_lib.SO_PATH), "-lswb200", "-Wl,-rpath," + os.path.dirname(_lib.SO_PATH), "-o", exe])
+    rows = []
+    for c in rust_kats:
+        if c["pssm"]:
+            continue
+        m = c["matrix"]
+        rows.append("\t".join([c["test"], str(c["mode"]), repr(c["go"]), repr(c["ge"]), "1" if c["retain_all"] else "0", m["kind"],
+                               repr(m.get("match", 0.0)), repr(m.get("mismatch", 0.0)), repr(m.get("scale", 1.0)), c["seq1"], c["seq2"],
+                               swb.rust_f32_display(c["score"]) if "score" in c else "-", c.get("r1", "-"), c.get("r2", "-")]))
+    (tmp_path / "cases.tsv").write_text("\n".join(rows) + "\n")
+    r = subprocess.run([exe, str(tmp_path / "cases.tsv")], capture_output=True, text=True)
+    assert r.returncode == 0, r.stdout + r.stderr
+    assert "kats: %d cases, 0 failures" % len(rows) in r.stdout
