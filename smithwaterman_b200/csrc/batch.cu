@@ -176,11 +176,37 @@ __global__ void SWB_HELPER k1_pack_kernel(const uint8_t *__restrict__ codes_a, c
 // so a chunk's preparation costs the host a streaming pass over the offsets.
 #define K1_MAX_LEN 8192            // longer pairs go to the wavefront kernel
 
+// Which pairs K1 takes, the same rule on the host (routing, buffer bounds) and on the device (sort).  Local mode: both
+// lengths in 1..8192 (an s16 overflow is flagged by the kernel and re-run in int32).  Global mode has no clamp and no
+// flag: the pair must be unable to leave the s16 lanes -- at most min(la,lb) matches of the best score upwards, at
+// most two gap openings plus la+lb extensions, the sentinel offset and one worst substitution downwards.
+struct K1Take {
+    int global_mode;
+    int64_t up_per_match, up_base;     // min(la,lb) * up_per_match + up_base <= 32000
+    int64_t down_per_res, down_base;   // (la+lb) * down_per_res + down_base <= 32000
+};
+__host__ __device__ __forceinline__ bool k1_take(int64_t la, int64_t lb, const K1Take &T)
+{
+    if (la <= 0 || lb <= 0 || la > K1_MAX_LEN || lb > K1_MAX_LEN) return false;
+    if (!T.global_mode) return true;
+    const int64_t mn = la < lb ? la : lb;
+    return mn * T.up_per_match + T.up_base <= 32000 && (la + lb) * T.down_per_res + T.down_base <= 32000;
+}
+static K1Take k1_take_rule(const swb_engine *e)
+{
+    K1Take T;
+    T.global_mode = (e->mode == SWB_GLOBAL) ? 1 : 0;
+    const int64_t ao = -(int64_t)e->o, ae = -(int64_t)e->e, sp = std::max(e->smax, 0), sn = std::max(-e->smin, 0);
+    T.up_per_match = sp; T.up_base = ao + sp + sn + 64;
+    T.down_per_res = ae; T.down_base = 3 * ao + (10 * ao + 10 * ae) + sp + sn + 64;
+    return T;
+}
+
 __device__ __forceinline__ bool sort_take(const int64_t *__restrict__ off_a, const int64_t *__restrict__ off_b, int64_t k,
-                                          int shared_la, int la_cap, int pass_cap, int &la, int &np, int &bucket)
+                                          int shared_la, int la_cap, int pass_cap, const K1Take &T, int &la, int &np, int &bucket)
 {
     const int64_t la64 = shared_la >= 0 ? (int64_t)shared_la : off_a[k + 1] - off_a[k], lb64 = off_b[k + 1] - off_b[k];
-    if (la64 <= 0 || lb64 <= 0 || la64 > K1_MAX_LEN || lb64 > K1_MAX_LEN) return false;
+    if (!k1_take(la64, lb64, T)) return false;
     la = (int)la64; np = ((int)lb64 + K1_STRIP - 1) / K1_STRIP;
     bucket = (pass_cap - np) * (la_cap + 1) + (la_cap - la);
     return true;
@@ -189,12 +215,12 @@ __device__ __forceinline__ bool sort_take(const int64_t *__restrict__ off_a, con
 // SCATTER == false: histogram of the buckets; true: order[cursor[bucket]++] = pair.  One atomic per distinct bucket of a warp.
 template <bool SCATTER>
 __global__ void SWB_HELPER sort_count_kernel(const int64_t *__restrict__ off_a, const int64_t *__restrict__ off_b, int64_t n, int shared_la,
-                                  int la_cap, int pass_cap, int32_t *__restrict__ cnt, int32_t *__restrict__ order)
+                                  int la_cap, int pass_cap, K1Take T, int32_t *__restrict__ cnt, int32_t *__restrict__ order)
 {
     const int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     const int lane = threadIdx.x & 31;
     int la = 0, np = 0, bucket = -1;
-    const bool take = k < n && sort_take(off_a, off_b, k, shared_la, la_cap, pass_cap, la, np, bucket);
+    const bool take = k < n && sort_take(off_a, off_b, k, shared_la, la_cap, pass_cap, T, la, np, bucket);
     const unsigned takers = __ballot_sync(0xffffffffu, take);
     if (!take) return;
     const unsigned peers = __match_any_sync(takers, bucket);
@@ -390,7 +416,8 @@ static int batch_upload_impl(swb_engine *e, const char *a_all, const int64_t *of
     d->base_a = (n && !shared) ? off_a[0] : 0; d->base_b = n ? off_b[0] : 0;
     const int64_t na = shared ? shared_la : (n ? off_a[n] - d->base_a : 0), nb = n ? off_b[n] - d->base_b : 0;
     if (na < 0 || nb < 0 || (na > 0 && !a_all) || (nb > 0 && !b_all)) { e->err = "bad sequence buffer / offsets"; return SWB_ERR_ARG; }
-    const bool use_k1 = (e->mode == SWB_LOCAL && e->o <= e->e);
+    const bool use_k1 = ((e->mode == SWB_LOCAL || e->mode == SWB_GLOBAL) && e->o <= e->e);   // the packed Gotoh cell needs |open| >= |ext|
+    const K1Take take = k1_take_rule(e);
 
     // ---- device buffers + H2D of the raw residues first (stream-ordered, no host synchronisation): the copy engine works
     //      while the host sorts
@@ -419,7 +446,7 @@ static int batch_upload_impl(swb_engine *e, const char *a_all, const int64_t *of
     // ---- routing (one streaming pass over the offsets); the shape sort itself runs on the device
     b->la.resize(n); b->lb.resize(n);
     // a long shared query (database search) goes to K2: lanes split the columns, every work item lasts la + 124 row steps
-    const bool use_k2 = use_k1 && shared && shared_la >= K2_MIN_QUERY && shared_la <= 0x0FFFFFFF;
+    const bool use_k2 = use_k1 && e->mode == SWB_LOCAL && shared && shared_la >= K2_MIN_QUERY && shared_la <= 0x0FFFFFFF;
     std::vector<int32_t> k2_idx;
     int la_cap = 0, pass_cap = 0;
     int64_t n_k1 = 0, sum_blk = 0, sum_np = 0;                 // K1 pairs, their row-block words and passes (buffer bounds)
@@ -431,7 +458,7 @@ static int batch_upload_impl(swb_engine *e, const char *a_all, const int64_t *of
         b->cells += (double)la * (double)lb;
         if (la == 0 || lb == 0) d->degenerate.push_back((int32_t)k);
         else if (use_k2) k2_idx.push_back((int32_t)k);
-        else if (use_k1 && la <= K1_MAX_LEN && lb <= K1_MAX_LEN) {             // == sort_take() on the device
+        else if (use_k1 && k1_take(la, lb, take)) {                               // the device sort applies the same rule
             const int np = (int)((lb + K1_STRIP - 1) / K1_STRIP);
             ++n_k1; sum_blk += (la + 1 + 3) / 4 + 1; sum_np += np;
             la_cap = std::max(la_cap, (int)la); pass_cap = std::max(pass_cap, np);
@@ -466,9 +493,9 @@ static int batch_upload_impl(swb_engine *e, const char *a_all, const int64_t *of
         const int nblk = (int)((n + HELPER_THREADS - 1) / HELPER_THREADS);
         CUDA_TRY(e, join());
         CUDA_TRY(e, zero_async(cnt, n_buckets * sizeof(int32_t), hs));
-        sort_count_kernel<false><<<nblk, HELPER_THREADS, 0, hs>>>(d->off_a, d->off_b, n, sla, la_cap, pass_cap, cnt, nullptr);
+        sort_count_kernel<false><<<nblk, HELPER_THREADS, 0, hs>>>(d->off_a, d->off_b, n, sla, la_cap, pass_cap, take, cnt, nullptr);
         scan_kernel<int32_t><<<1, HELPER_THREADS, 0, hs>>>(cnt, cur, n_buckets);
-        sort_count_kernel<true><<<nblk, HELPER_THREADS, 0, hs>>>(d->off_a, d->off_b, n, sla, la_cap, pass_cap, cur, d->order);
+        sort_count_kernel<true><<<nblk, HELPER_THREADS, 0, hs>>>(d->off_a, d->off_b, n, sla, la_cap, pass_cap, take, cur, d->order);
         sort_groups_kernel<<<(ng + HELPER_THREADS / 32 - 1) / (HELPER_THREADS / 32), HELPER_THREADS, 0, hs>>>(d->off_a, d->off_b, sla, d->order, d->n_k1, ng, b->d_groups, asz, bsz);
         scan_kernel<int64_t><<<1, HELPER_THREADS, 0, hs>>>(asz, aoff, ng);
         scan_kernel<int64_t><<<1, HELPER_THREADS, 0, hs>>>(bsz, boff, ng);
@@ -608,7 +635,10 @@ static int batch_launch(swb_engine *e, swb_batch *b, int64_t *launches)
     cudaStream_t st = kstream(e, b);
     CUDA_TRY(e, cudaStreamWaitEvent(st, d->ev_ready, 0));     // upload may have run on the copy stream
     d->launched = true; d->done_recorded = false;
-    if (d->n_k1) { CUDA_TRY(e, k1_launch(e, b, e->sm_count, bnd_slot(e, b), st)); ++*launches; }
+    if (d->n_k1) {
+        CUDA_TRY(e, e->mode == SWB_GLOBAL ? k1_global_launch(e, b, e->sm_count, bnd_slot(e, b), st) : k1_launch(e, b, e->sm_count, bnd_slot(e, b), st));
+        ++*launches;
+    }
     if (d->n_k2) {
         CUDA_TRY(e, k2_launch(e, d->codes_a, (int)d->shared_la, d->codes_b, d->off_b, d->base_b, d->items, d->sweeps, d->n_items,
                               bnd_slot(e, b), b->d_counter, b->d_res, e->sm_count, st));

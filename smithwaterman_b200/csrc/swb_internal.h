@@ -92,6 +92,7 @@ struct swb_batch {
 // ---- kernel launchers (defined in the .cu files) ----------------------------------------------
 // K1: local, score + first-maximum cell, packed s16x2, one thread per pair.
 cudaError_t k1_launch(const swb_engine *e, const swb_batch *b, int n_blocks, void *d_bnd, cudaStream_t st);
+cudaError_t k1_global_launch(const swb_engine *e, const swb_batch *b, int n_blocks, void *d_bnd, cudaStream_t st);   // k1_global.cu
 size_t k1_bnd_bytes(int n_blocks, int la_max);
 int k1_blocks_per_sm(const swb_engine *e);
 // K2: shared long query, lanes split the columns (database search).
