@@ -84,9 +84,12 @@ def lib():
     global _lib
     if _lib is not None:
         return _lib
-    if needs_build():
-        build()
-    L = ctypes.CDLL(SO_PATH)
+    so = os.environ.get("SWB_LIB")          # tuning aid: A/B a differently compiled build of the same sources
+    if not so:
+        if needs_build():
+            build()
+        so = SO_PATH
+    L = ctypes.CDLL(so)
     c = ctypes
     vp, i64, i32, f32 = c.c_void_p, c.c_int64, c.c_int32, c.c_float
     sig = {

@@ -66,6 +66,24 @@ __global__ void __launch_bounds__(1024) k0_kernel(unsigned *out, unsigned seed)
                 v[c] = __viaddmax_s16x2(v[c], k1, k2);
                 w[c] = w[c] * k1 + k2;
             }
+            else if (WHICH == 12) { v[c] = __viaddmax_s16x2(v[c], 0xFFFFFFFFu, w[c]); }   // immediate addend
+            else if (WHICH == 13) { v[c] = __vadd2(v[c], 0xFFECFFECu); }                  // immediate addend
+            else if (WHICH == 14) { v[c] = __viaddmax_s16x2(v[c], seed, w[c]); }          // addend in a uniform register
+            else if (WHICH == 15) { v[c] = __viaddmax_s16x2(v[c], w[c], 0x00010001u); }   // immediate max operand
+            else if (WHICH == 16) {     // K1's cell with immediate penalties (5 DPX), table words faked by the chains
+                unsigned Fk = __viaddmax_s16x2(w[c], 0xFFFFFFFFu, v[c]);
+                unsigned G = __viaddmax_s16x2_relu(v[c], k2, Fk);
+                unsigned E = __viaddmax_s16x2(Fk, 0xFFFFFFFFu, G);
+                unsigned Go = __vadd2(G, 0xFFECFFECu);
+                v[c] = __viaddmax_s16x2(E, 0xFFECFFECu, Go); w[c] = Fk;
+            }
+            else if (WHICH == 17) {     // the same cell with the penalties in registers
+                unsigned Fk = __viaddmax_s16x2(w[c], k1, v[c]);
+                unsigned G = __viaddmax_s16x2_relu(v[c], k2, Fk);
+                unsigned E = __viaddmax_s16x2(Fk, k1, G);
+                unsigned Go = __vadd2(G, k2);
+                v[c] = __viaddmax_s16x2(E, k2, Go); w[c] = Fk;
+            }
         }
     }
     unsigned acc = 0;
@@ -115,6 +133,12 @@ cudaError_t k0_run(int which, int sm_count, double *rate)
     case 9: return k0_time<9>(sm_count, 2, rate);
     case 10: return k0_time<10>(sm_count, 2, rate);
     case 11: return k0_time<11>(sm_count, 2, rate);
+    case 12: return k0_time<12>(sm_count, 1, rate);
+    case 13: return k0_time<13>(sm_count, 1, rate);
+    case 14: return k0_time<14>(sm_count, 1, rate);
+    case 15: return k0_time<15>(sm_count, 1, rate);
+    case 16: return k0_time<16>(sm_count, 5, rate);
+    case 17: return k0_time<17>(sm_count, 5, rate);
     default: return cudaErrorInvalidValue;
     }
 }

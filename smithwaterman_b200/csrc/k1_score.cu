@@ -25,12 +25,20 @@
 // End cell = first strict maximum of H in (row, column) order == the reference's first strict
 // maximum of the MATCH state (SA.rs:286-294): a maximal H cell reached through a gap state always
 // has an equal-valued cell before it in that order.  Per row step only a packed row maximum is
-// kept (VIMNMX3, half an instruction per cell); the column is recovered by a register scan in
-// the (rare) steps where the running best improves.
+// kept (VIMNMX3, half an instruction per cell, seeded with the current threshold so that one compare
+// tells whether anything improved).  In the (rare) steps where the running best of a lane improves,
+// only the row and the 16-column half are decided; the step's 16 packed Ho words are parked in a
+// per-thread shared-memory slot (4 STS.128) and the column is read off that slot once per pair.
+// (K1_NOTRACK=1 builds a timing-only variant without the end cell: the per-row test, its branch and
+// the rare path together cost 10 % of the kernel, see DESIGN.md.)
 #include <cstdlib>
 
 #include "swb_internal.h"
 #include "k1_common.cuh"
+
+#ifndef K1_NOTRACK
+#define K1_NOTRACK 0
+#endif
 
 // One packed cell-vector.  The only loop-carried dependency along k is the single VIADDMNMX of E:
 //   G  = max(Hdiag + s, F, 0)                 (independent of the row chain)
@@ -59,7 +67,7 @@ k1_local_kernel(const uint8_t *__restrict__ a_pk, const uint8_t *__restrict__ b_
                 int limit_ho, uint4 *__restrict__ bnd, int bnd_blocks, int *counter, const int32_t *__restrict__ order,
                 K1Result *__restrict__ res)
 {
-    extern __shared__ unsigned T_sh[];               // [nl*nl][32 lanes]: (s - open) & 0xFFFF
+    extern __shared__ __align__(16) unsigned T_sh[];               // [nl*nl][32 lanes]: (s - open) & 0xFFFF
     for (int idx = threadIdx.x; idx < nl * nl * 32; idx += blockDim.x)
         T_sh[idx] = (unsigned)(mat[idx >> 5] - open) & 0xFFFFu;
     __syncthreads();
@@ -76,6 +84,8 @@ k1_local_kernel(const uint8_t *__restrict__ a_pk, const uint8_t *__restrict__ b_
     const unsigned rowstride = (unsigned)nl * 128u;
     const unsigned open2 = pack2(open, open), ext2 = pack2(ext, ext);
     const unsigned long long pol = keep_policy();
+    // per-thread snapshot of the 16 packed Ho words of the row step that holds the running best: [4][thread] uint4
+    uint4 *snap = reinterpret_cast<uint4 *>(T_sh + nl * nl * 32) + threadIdx.x;
 
     for (;;) {
         int g = 0;
@@ -144,41 +154,55 @@ k1_local_kernel(const uint8_t *__restrict__ a_pk, const uint8_t *__restrict__ b_
                     lo15_Ho = Ho[15]; lo15_E = E;
                     HoD = HoD_next;
                     // packed row maximum of Ho (low lane: row i, high lane: row i-1)
-                    unsigned rm = __vimax3_s16x2(Ho[0], Ho[1], Ho[2]);
-                    rm = __vimax3_s16x2(rm, Ho[3], Ho[4]);
-                    rm = __vimax3_s16x2(rm, Ho[5], Ho[6]);
-                    rm = __vimax3_s16x2(rm, Ho[7], Ho[8]);
-                    rm = __vimax3_s16x2(rm, Ho[9], Ho[10]);
-                    rm = __vimax3_s16x2(rm, Ho[11], Ho[12]);
-                    rm = __vimax3_s16x2(rm, Ho[13], Ho[14]);
-                    rm = __vmaxs2(rm, Ho[15]);
+                    // (thr2 rides in the chain: 8 max3 for 17 operands, and "rm != thr2" is the improvement test)
+                    unsigned rm = __vimax3_s16x2(thr2, Ho[0], Ho[1]);
+                    rm = __vimax3_s16x2(rm, Ho[2], Ho[3]);
+                    rm = __vimax3_s16x2(rm, Ho[4], Ho[5]);
+                    rm = __vimax3_s16x2(rm, Ho[6], Ho[7]);
+                    rm = __vimax3_s16x2(rm, Ho[8], Ho[9]);
+                    rm = __vimax3_s16x2(rm, Ho[10], Ho[11]);
+                    rm = __vimax3_s16x2(rm, Ho[12], Ho[13]);
+                    rm = __vimax3_s16x2(rm, Ho[14], Ho[15]);
                     // (the predicate outputs of __vibmax_s16x2 gave wrong answers here with nvcc 12.9; compare the max instead)
-                    if (__vmaxs2(thr2, rm) != thr2) {
+#if K1_NOTRACK == 1
+                    thr2 = rm;      // timing experiment only: no end cell
+#else
+                    if (rm != thr2) {
+                        // Rare path (the running best of some lane improves).  Only the row and the half are decided
+                        // here; the 16 packed Ho words of the step are parked in shared memory (4 STS.128 of the lanes
+                        // that improved) and the column is read off them once, after the last pass.
                         const int rlo = lo16(rm), rhi = hi16(rm);
-                        // low lane: row i
-                        if (i <= la && (rlo > bestHo || (rlo == bestHo && rlo > open && i < bi))) {
-                            int kk = 0;
-#pragma unroll
-                            for (int k = K1_HALF - 1; k >= 0; --k)
-                                if (lo16(Ho[k]) == rlo) kk = k;
-                            bestHo = rlo; bi = i; bj = jbase + kk + 1;
-                            if (rlo >= limit_ho) ovf = 1;
+                        const bool ulo = i <= la && (rlo > bestHo || (rlo == bestHo && rlo > open && i < bi));
+                        if (ulo) { bestHo = rlo; bi = i; bj = jbase; }
+                        const bool uhi = i >= 2 && i - 1 <= la && (rhi > bestHo || (rhi == bestHo && rhi > open && i - 1 < bi));
+                        if (uhi) { bestHo = rhi; bi = i - 1; bj = jbase + K1_HALF; }
+                        if (ulo || uhi) {
+                            snap[0] = make_uint4(Ho[0], Ho[1], Ho[2], Ho[3]);
+                            snap[K1_THREADS * 2] = make_uint4(Ho[4], Ho[5], Ho[6], Ho[7]);
+                            snap[K1_THREADS * 4] = make_uint4(Ho[8], Ho[9], Ho[10], Ho[11]);
+                            snap[K1_THREADS * 6] = make_uint4(Ho[12], Ho[13], Ho[14], Ho[15]);
+                            if (bestHo >= limit_ho) ovf = 1;
+                            thr2 = pack2(bestHo - (first ? 0 : 1), bestHo - (first ? 0 : 1));
                         }
-                        // high lane: row i-1
-                        if (i >= 2 && i - 1 <= la && (rhi > bestHo || (rhi == bestHo && rhi > open && i - 1 < bi))) {
-                            int kk = 0;
-#pragma unroll
-                            for (int k = K1_HALF - 1; k >= 0; --k)
-                                if (hi16(Ho[k]) == rhi) kk = k;
-                            bestHo = rhi; bi = i - 1; bj = jbase + K1_HALF + kk + 1;
-                            if (rhi >= limit_ho) ovf = 1;
-                        }
-                        thr2 = pack2(bestHo - (first ? 0 : 1), bestHo - (first ? 0 : 1));
                     }
+#endif
                 }
                 c1 = wout[1]; c2 = wout[2]; c3 = wout[3];
             }
             if (!last) st_keep(mybnd + (size_t)(nblk - 1) * bstride, make_uint4(c1, c2, c3, open2), pol);   // rows 4(nblk-1)+1..+3
+#if K1_NOTRACK
+            bestHo = max(bestHo, max(lo16(thr2), hi16(thr2)));
+#endif
+        }
+        if (bestHo > open) {                        // column of the best cell: first word of its half that holds bestHo
+            const uint4 s0 = snap[0], s1 = snap[K1_THREADS * 2], s2 = snap[K1_THREADS * 4], s3 = snap[K1_THREADS * 6];
+            const unsigned w[K1_HALF] = {s0.x, s0.y, s0.z, s0.w, s1.x, s1.y, s1.z, s1.w, s2.x, s2.y, s2.z, s2.w, s3.x, s3.y, s3.z, s3.w};
+            const bool hi = (bj & K1_HALF) != 0;    // jbase is a multiple of 32
+            int kk = 0;
+#pragma unroll
+            for (int k = K1_HALF - 1; k >= 0; --k)
+                if ((hi ? hi16(w[k]) : lo16(w[k])) == bestHo) kk = k;
+            bj += kk + 1;
         }
         if (valid) {
             K1Result r;
@@ -201,7 +225,7 @@ size_t k1_bnd_bytes(int n_blocks, int la_max)
 cudaError_t k1_launch(const swb_engine *e, const swb_batch *b, int n_blocks, void *d_bnd, cudaStream_t st)
 {
     const int nl = e->n + 1;
-    const size_t smem = (size_t)nl * nl * 32 * sizeof(unsigned);
+    const size_t smem = (size_t)nl * nl * 32 * sizeof(unsigned) + (size_t)K1_THREADS * 2 * 4 * sizeof(uint4);
     cudaError_t err = cudaFuncSetAttribute(k1_local_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (err != cudaSuccess) return err;
     err = cudaMemsetAsync(b->d_counter, 0, sizeof(int32_t), st);
@@ -235,7 +259,7 @@ k2_search_kernel(const unsigned *__restrict__ a_words, int la, const uint8_t *__
                  const int32_t *__restrict__ item_sweeps, int n_items, const int32_t *__restrict__ mat, int nl, int open,
                  int ext, int limit_ho, uint4 *__restrict__ gbnd, int gb_blocks, int *counter, K1Result *__restrict__ res)
 {
-    extern __shared__ unsigned T_sh[];               // [nl*nl][32 lanes]: (s - open) & 0xFFFF
+    extern __shared__ __align__(16) unsigned T_sh[];               // [nl*nl][32 lanes]: (s - open) & 0xFFFF
     __shared__ int cand_sh[K1_THREADS * 2 / 32][32][4];
     for (int idx = threadIdx.x; idx < nl * nl * 32; idx += blockDim.x)
         T_sh[idx] = (unsigned)(mat[idx >> 5] - open) & 0xFFFFu;
@@ -248,6 +272,7 @@ k2_search_kernel(const unsigned *__restrict__ a_words, int la, const uint8_t *__
     const unsigned rowstride = (unsigned)nl * 128u;
     const unsigned open2 = pack2(open, open), ext2 = pack2(ext, ext);
     const unsigned pad = (unsigned)(nl - 1), pad4 = pad * 0x01010101u;
+    uint4 *snap = reinterpret_cast<uint4 *>(T_sh + nl * nl * 32) + threadIdx.x;    // [4][thread] uint4, see K1
     const int nblk = (la + 1 + 3) >> 2;              // row blocks of a pass (one step past la finishes the high half)
     const int nwords = (la + 3) >> 2;                // query words that hold real rows
 
@@ -333,31 +358,26 @@ k2_search_kernel(const unsigned *__restrict__ a_words, int la, const uint8_t *__
                     }
                     lo15_Ho = Ho[15]; lo15_E = E;
                     HoD = HoD_next;
-                    unsigned rm = __vimax3_s16x2(Ho[0], Ho[1], Ho[2]);
-                    rm = __vimax3_s16x2(rm, Ho[3], Ho[4]);
-                    rm = __vimax3_s16x2(rm, Ho[5], Ho[6]);
-                    rm = __vimax3_s16x2(rm, Ho[7], Ho[8]);
-                    rm = __vimax3_s16x2(rm, Ho[9], Ho[10]);
-                    rm = __vimax3_s16x2(rm, Ho[11], Ho[12]);
-                    rm = __vimax3_s16x2(rm, Ho[13], Ho[14]);
-                    rm = __vmaxs2(rm, Ho[15]);
-                    if (__vmaxs2(thr2, rm) != thr2) {
+                    unsigned rm = __vimax3_s16x2(thr2, Ho[0], Ho[1]);
+                    rm = __vimax3_s16x2(rm, Ho[2], Ho[3]);
+                    rm = __vimax3_s16x2(rm, Ho[4], Ho[5]);
+                    rm = __vimax3_s16x2(rm, Ho[6], Ho[7]);
+                    rm = __vimax3_s16x2(rm, Ho[8], Ho[9]);
+                    rm = __vimax3_s16x2(rm, Ho[10], Ho[11]);
+                    rm = __vimax3_s16x2(rm, Ho[12], Ho[13]);
+                    rm = __vimax3_s16x2(rm, Ho[14], Ho[15]);
+                    if (rm != thr2) {                           // rare path as in K1: row + half here, column from the parked words
                         const int rlo = lo16(rm), rhi = hi16(rm);
-                        if (i >= 1 && i <= la && (rlo > bestHo || (rlo == bestHo && rlo > open && i < bi))) {
-                            int kk = 0;
-#pragma unroll
-                            for (int k = K1_HALF - 1; k >= 0; --k)
-                                if (lo16(Ho[k]) == rlo) kk = k;
-                            bestHo = rlo; bi = i; bj = jbase + kk + 1;
-                            if (rlo >= limit_ho) ovf = 1;
-                        }
-                        if (i >= 2 && i - 1 <= la && (rhi > bestHo || (rhi == bestHo && rhi > open && i - 1 < bi))) {
-                            int kk = 0;
-#pragma unroll
-                            for (int k = K1_HALF - 1; k >= 0; --k)
-                                if (hi16(Ho[k]) == rhi) kk = k;
-                            bestHo = rhi; bi = i - 1; bj = jbase + K1_HALF + kk + 1;
-                            if (rhi >= limit_ho) ovf = 1;
+                        const bool ulo = i >= 1 && i <= la && (rlo > bestHo || (rlo == bestHo && rlo > open && i < bi));
+                        if (ulo) { bestHo = rlo; bi = i; bj = jbase; }
+                        const bool uhi = i >= 2 && i - 1 <= la && (rhi > bestHo || (rhi == bestHo && rhi > open && i - 1 < bi));
+                        if (uhi) { bestHo = rhi; bi = i - 1; bj = jbase + K1_HALF; }
+                        if (ulo || uhi) {
+                            snap[0] = make_uint4(Ho[0], Ho[1], Ho[2], Ho[3]);
+                            snap[K1_THREADS * 2] = make_uint4(Ho[4], Ho[5], Ho[6], Ho[7]);
+                            snap[K1_THREADS * 4] = make_uint4(Ho[8], Ho[9], Ho[10], Ho[11]);
+                            snap[K1_THREADS * 6] = make_uint4(Ho[12], Ho[13], Ho[14], Ho[15]);
+                            if (bestHo >= limit_ho) ovf = 1;
                         }
                         tb = max(tb, bestHo);
                         thr2 = pack2(tb - 1, tb - 1);
@@ -376,6 +396,16 @@ k2_search_kernel(const unsigned *__restrict__ a_words, int la, const uint8_t *__
             __syncwarp();
         }
 
+        if (bestHo > open) {                        // column of this lane's best cell (see K1)
+            const uint4 s0 = snap[0], s1 = snap[K1_THREADS * 2], s2 = snap[K1_THREADS * 4], s3 = snap[K1_THREADS * 6];
+            const unsigned w[K1_HALF] = {s0.x, s0.y, s0.z, s0.w, s1.x, s1.y, s1.z, s1.w, s2.x, s2.y, s2.z, s2.w, s3.x, s3.y, s3.z, s3.w};
+            const bool hi = (bj & K1_HALF) != 0;
+            int kk = 0;
+#pragma unroll
+            for (int k = K1_HALF - 1; k >= 0; --k)
+                if ((hi ? hi16(w[k]) : lo16(w[k])) == bestHo) kk = k;
+            bj += kk + 1;
+        }
         // per-lane candidates -> the segment's head lane: score desc, row asc, column asc (SA.rs:286-294 scan order)
         cand_sh[wib][lane][0] = bestHo; cand_sh[wib][lane][1] = bi; cand_sh[wib][lane][2] = bj; cand_sh[wib][lane][3] = ovf;
         __syncwarp();
@@ -403,7 +433,7 @@ cudaError_t k2_launch(const swb_engine *e, const uint8_t *d_query, int la, const
                       int *d_counter, K1Result *d_res, int n_blocks, cudaStream_t st)
 {
     const int nl = e->n + 1;
-    const size_t smem = (size_t)nl * nl * 32 * sizeof(unsigned);
+    const size_t smem = (size_t)nl * nl * 32 * sizeof(unsigned) + (size_t)K1_THREADS * 2 * 4 * sizeof(uint4);
     cudaError_t err = cudaFuncSetAttribute(k2_search_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (err != cudaSuccess) return err;
     err = cudaMemsetAsync(d_counter, 0, sizeof(int32_t), st);

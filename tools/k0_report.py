@@ -3,7 +3,8 @@ import json
 import sys, os
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import smithwaterman_b200 as swb
-names = ["VIADDMNMX.S16x2", "VIMNMX3.S16x2", "VIADD.16x2", "gotoh-cell-mix(5)", "VIADDMNMX.S32", "IMAD", "cell-mix+3IMAD(8)", "HMNMX2 (fp16x2 max)", "HFMA2", "VIADDMNMX+HMNMX2 (2)", "VIADDMNMX+HFMA2 (2)", "VIADDMNMX+IMAD (2)"]
+names = ["VIADDMNMX.S16x2", "VIMNMX3.S16x2", "VIADD.16x2", "gotoh-cell-mix(5)", "VIADDMNMX.S32", "IMAD", "cell-mix+3IMAD(8)", "HMNMX2 (fp16x2 max)", "HFMA2", "VIADDMNMX+HMNMX2 (2)", "VIADDMNMX+HFMA2 (2)", "VIADDMNMX+IMAD (2)",
+         "VIADDMNMX imm addend", "VIADD.16x2 imm", "VIADDMNMX uniform addend", "VIADDMNMX imm max", "K1 cell imm penalties (5)", "K1 cell reg penalties (5)"]
 out = {}
 for k, n in enumerate(names):
     v = swb.dpx_peak(k)
