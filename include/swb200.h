@@ -89,6 +89,7 @@ typedef struct swb_stats {
     int64_t i32_reruns;      /* pairs re-run in int32 lanes after s16 overflow */
     int32_t scale;           /* integer rescaling factor in use (10/0.5 -> 2) */
     int32_t exact_scale;     /* 1 = every input was exactly representable on the integer grid */
+    int64_t ckpt_pairs;      /* pairs traced back through checkpointed recompute (direction bytes over the budget) */
 } swb_stats;
 
 /* Built-in matrices (SA.rs:697-733 BLOSUM62, 24 letters; SA.rs:681-695 match/mismatch, A-Z).

@@ -73,7 +73,7 @@ ALN_STATS_DTYPE = [("score", "<f4"), ("status", "<i4"), ("end_a", "<i8"), ("end_
 class Stats(ctypes.Structure):
     _fields_ = [("cells", ctypes.c_double), ("kernel_ms", ctypes.c_double), ("h2d_bytes", ctypes.c_double),
                 ("d2h_bytes", ctypes.c_double), ("launches", ctypes.c_int64), ("i32_reruns", ctypes.c_int64),
-                ("scale", ctypes.c_int32), ("exact_scale", ctypes.c_int32)]
+                ("scale", ctypes.c_int32), ("exact_scale", ctypes.c_int32), ("ckpt_pairs", ctypes.c_int64)]
 
 
 _lib = None

@@ -83,6 +83,118 @@ void swb_compose_stats(swb_aln_stats *o, int mode, bool retain_all, int64_t la, 
     o->matches = S.match;
 }
 
+// Direction-byte budget: a chunk of pairs keeps at most this many direction bytes resident, and a single pair that
+// needs more takes the checkpointed path below.  SWB_CKPT_BYTES overrides it (the tests force tiny budgets).
+static int64_t dir_budget()
+{
+    if (const char *f = getenv("SWB_CKPT_BYTES")) { const long long v = atoll(f); if (v >= 4096) return v; }
+    return DIR_BUDGET_BYTES;
+}
+
+// Checkpointed traceback of ONE pair whose direction bytes exceed the budget (BASELINE configs[3]: "wavefront +
+// checkpointed recompute"; the reference keeps the whole SWCell matrix, SA.rs:60-86, and cannot run such pairs at all).
+//   1. forward sweep, score only (KW, no direction bytes): finds the start cell of the walk (SA.rs:282-308) and saves
+//      the three states of every R-th row (16 B per column per checkpoint).
+//   2. from the band that holds the start cell upwards: re-run KW with direction bytes on rows (bR, cx] x columns [1, cy]
+//      only -- the walk never moves right or down, so everything beyond the cursor is skipped -- starting from the
+//      checkpoint row bR, then let KT walk until it reaches row bR, and continue in the band above.
+// Memory: R * lb direction bytes + (la / R) * lb * 16 checkpoint bytes instead of la * lb.
+static int align_ckpt_pair(swb_engine *e, const uint8_t *d_a, const uint8_t *d_b, int64_t a_off, int64_t b_off, int32_t la,
+                           int32_t lb, int64_t budget, KWResult *hres, std::vector<int64_t> &xa, std::vector<int64_t> &xb)
+{
+    cudaStream_t st = e->stream;
+    const int64_t row_bytes = ((int64_t)lb + 255) / 256 * 256;                    // direction bytes per row, widest strips
+    int32_t R = (int32_t)std::max<int64_t>(32, std::min<int64_t>(la, budget / row_bytes - 31));
+    const int32_t n_ck = (la - 1) / R;                                            // checkpoint rows R, 2R, .. (< la)
+    const int64_t stride = (int64_t)lb + 2;
+    DevBuf d_ck, d_pair, d_res, d_cur, d_xa, d_xb;
+    CUDA_TRY(e, d_ck.alloc((size_t)std::max<int64_t>(1, (int64_t)n_ck * stride) * sizeof(int4), st));
+    CUDA_TRY(e, d_pair.alloc(sizeof(KWPair), st)); CUDA_TRY(e, d_res.alloc(2 * sizeof(KWResult), st));
+    CUDA_TRY(e, d_cur.alloc(sizeof(KTCursor), st));
+    CUDA_TRY(e, d_xa.alloc(((size_t)la + lb + 1) * sizeof(int32_t), st)); CUDA_TRY(e, d_xb.alloc(((size_t)la + lb + 1) * sizeof(int32_t), st));
+    if (!e->h_tb || e->tb_bytes < 256) {
+        if (e->h_tb) cudaFreeHost(e->h_tb);
+        e->h_tb = nullptr; e->tb_bytes = 0;
+        CUDA_TRY(e, cudaMallocHost(&e->h_tb, 4096)); e->tb_bytes = 4096;
+    }
+    KWPair *hp = (KWPair *)e->h_tb;                                               // pinned staging: pair, result, cursor
+    KWResult *hr = (KWResult *)((char *)e->h_tb + 64);
+    KTCursor *hc = (KTCursor *)((char *)e->h_tb + 128);
+
+    auto run_kw = [&](int32_t row0, int32_t rows, int32_t cols_used, bool dirs, const KWBand &band, KWPlan &plan) -> int {
+        KWPair P; P.a_off = a_off + row0; P.b_off = b_off; P.la = rows; P.lb = cols_used; P.dir_off = dirs ? 0 : -1;
+        P.bnd_off = 0; P.scr_off = 0; P.pssm_off = -1;
+        // short, wide bands: the 32-row lag between the warps of a team dominates, fewer and wider strips win (measured)
+        kw_plan(e, &P, 1, dirs, &plan, (dirs && rows < 16384) ? 8 : 0);
+        if (dirs && (size_t)plan.dir_bytes + 16 > e->dir_bytes) {
+            CUDA_TRY(e, cudaStreamSynchronize(st));
+            if (e->d_dir) cudaFree(e->d_dir);
+            e->d_dir = nullptr; e->dir_bytes = 0;
+            CUDA_TRY(e, cudaMalloc(&e->d_dir, (size_t)plan.dir_bytes + 16));
+            e->dir_bytes = (size_t)plan.dir_bytes + 16;
+        }
+        DevBuf d_bnd, d_scr;
+        CUDA_TRY(e, d_bnd.alloc(plan.bnd_elems * sizeof(int4), st)); CUDA_TRY(e, d_scr.alloc(plan.scratch_ints * sizeof(int), st));
+        CUDA_TRY(e, cudaStreamSynchronize(st));                                   // the staging slot is reused per launch
+        *hp = P;
+        CUDA_TRY(e, cudaMemcpyAsync(d_pair.p, hp, sizeof(KWPair), cudaMemcpyHostToDevice, st));
+        CUDA_TRY(e, kw_launch_band(e, d_a, d_b, d_pair.as<KWPair>(), plan, band, dirs ? (uint8_t *)e->d_dir : nullptr,
+                                   d_bnd.as<int4>(), d_scr.as<int>(), d_res.as<KWResult>() + (dirs ? 1 : 0), st));
+        e->stats.launches += 1;
+        return SWB_OK;
+    };
+
+    CUDA_TRY(e, cudaEventRecord(e->ev0, st));
+    {   // 1. forward sweep with checkpoints
+        KWBand band; band.row0 = 0; band.la_full = la; band.lb_full = lb; band.ckpt_out = d_ck.as<int4>(); band.every = R; band.stride = stride;
+        KWPlan plan;
+        int rc = run_kw(0, la, lb, false, band, plan);
+        if (rc != SWB_OK) return rc;
+        CUDA_TRY(e, cudaMemcpyAsync(hr, d_res.p, sizeof(KWResult), cudaMemcpyDeviceToHost, st));
+        CUDA_TRY(e, cudaStreamSynchronize(st));
+        *hres = *hr;
+    }
+    xa.clear(); xb.clear();
+    if (hres->end_i < 0) {                                                        // local score 0: no alignment (SA.rs:346-348)
+        CUDA_TRY(e, cudaEventRecord(e->ev1, st)); CUDA_TRY(e, cudaStreamSynchronize(st));
+        float ms = 0; cudaEventElapsedTime(&ms, e->ev0, e->ev1); e->stats.kernel_ms += ms;
+        return SWB_OK;
+    }
+    KTCursor C; C.cx = hres->end_i; C.cy = hres->end_j; C.st = hres->state; C.n = 0; C.status = 1;
+    while (C.status == 1) {                                                       // 2. bands, bottom-up
+        const int32_t b = (C.cx >= 1 && C.cy >= 1) ? (C.cx - 1) / R : 0;
+        const int32_t row0 = b * R, rows = C.cx - row0;
+        KWPlan plan;
+        if (C.cx >= 1 && C.cy >= 1) {
+            KWBand band; band.row0 = row0; band.la_full = la; band.lb_full = lb; band.every = R; band.stride = stride;
+            band.ckpt_in = (b > 0) ? d_ck.as<int4>() + (int64_t)(b - 1) * stride : nullptr;
+            int rc = run_kw(row0, rows, C.cy, true, band, plan);
+            if (rc != SWB_OK) return rc;
+        } else CUDA_TRY(e, cudaStreamSynchronize(st));                            // the rest runs along the matrix boundary: no bytes needed
+        *hc = C;
+        CUDA_TRY(e, cudaMemcpyAsync(d_cur.p, hc, sizeof(KTCursor), cudaMemcpyHostToDevice, st));
+        CUDA_TRY(e, kt_band_launch(e, (const uint8_t *)e->d_dir, plan.cols, rows, row0, d_cur.as<KTCursor>(), d_xa.as<int32_t>(), d_xb.as<int32_t>(), st));
+        CUDA_TRY(e, cudaMemcpyAsync(hc, d_cur.p, sizeof(KTCursor), cudaMemcpyDeviceToHost, st));
+        CUDA_TRY(e, cudaStreamSynchronize(st));
+        e->stats.launches += 1;
+        if (hc->status == 1 && hc->cx == C.cx && hc->cy == C.cy && hc->n == C.n) { e->err = "checkpointed traceback made no progress"; return SWB_ERR_CUDA; }
+        C = *hc;
+    }
+    CUDA_TRY(e, cudaEventRecord(e->ev1, st));
+    if (C.status < 0) { e->err = "traceback left the matrix (the reference panics here, SA.rs:360-371)"; return SWB_ERR_EMPTY; }
+    std::vector<int32_t> ha((size_t)C.n), hb((size_t)C.n);                       // (a one-off pageable copy: this path is for a few huge pairs)
+    if (C.n > 0) {
+        CUDA_TRY(e, cudaMemcpyAsync(ha.data(), d_xa.p, (size_t)C.n * sizeof(int32_t), cudaMemcpyDeviceToHost, st));
+        CUDA_TRY(e, cudaMemcpyAsync(hb.data(), d_xb.p, (size_t)C.n * sizeof(int32_t), cudaMemcpyDeviceToHost, st));
+    }
+    CUDA_TRY(e, cudaStreamSynchronize(st));
+    float ms = 0; cudaEventElapsedTime(&ms, e->ev0, e->ev1); e->stats.kernel_ms += ms;
+    e->stats.d2h_bytes += 8.0 * C.n;
+    xa.resize(C.n); xb.resize(C.n);
+    for (int64_t c = 0; c < C.n; ++c) { xa[c] = ha[C.n - 1 - c]; xb[c] = hb[C.n - 1 - c]; }   // reverse (SA.rs:384-385)
+    return SWB_OK;
+}
+
 // outs: full alignments (lists + strings); souts: the counting form (swb_align_stats_batch).  Exactly one is non-null.
 static int align_batch_impl(swb_engine *e, const char *a_all, const int64_t *off_a, const char *b_all,
                             const int64_t *off_b, int64_t n, unsigned flags, swb_alignment *outs, const float *pssm,
@@ -161,6 +273,22 @@ static int align_batch_impl(swb_engine *e, const char *a_all, const int64_t *off
         e->stats.h2d_bytes += (double)na + (double)nb;
     }
 
+    const int64_t budget = dir_budget();
+    if (outs && !pssm) {                              // pairs whose direction bytes do not fit: checkpointed traceback, one at a time
+        std::vector<int64_t> rest;
+        for (int64_t k : work) {
+            const int32_t la = (int32_t)(off_a[k + 1] - off_a[k]), lb = (int32_t)(off_b[k + 1] - off_b[k]);
+            if (kw_dir_bytes(la, lb, 8) <= budget) { rest.push_back(k); continue; }
+            KWResult R; std::vector<int64_t> xa, xb; std::string ra, rb;
+            int rc = align_ckpt_pair(e, d_a.as<uint8_t>(), d_b.as<uint8_t>(), off_a[k], off_b[k], la, lb, budget, &R, xa, xb);
+            if (rc != SWB_OK) return rc;
+            e->stats.ckpt_pairs += 1;
+            inflate(a_all + off_a[k], la, b_all + off_b[k], lb, xa.data(), xb.data(), (int64_t)xa.size(), e->mode, retain_all, ra, rb);
+            rc = fill_out(&outs[k], to_f(R.score), R.end_i, R.end_j, xa, xb, ra, rb);
+            if (rc != SWB_OK) { e->err = "out of memory"; return rc; }
+        }
+        work.swap(rest);
+    }
     size_t pos = 0;
     while (pos < work.size()) {
         // chunk of pairs whose direction bytes fit the budget
@@ -171,7 +299,7 @@ static int align_batch_impl(swb_engine *e, const char *a_all, const int64_t *off
             const int64_t k = work[end];
             const int32_t la = (int32_t)(off_a[k + 1] - off_a[k]), lb = (int32_t)(off_b[k + 1] - off_b[k]);
             const int64_t db = kw_dir_bytes(la, lb, 8);              // upper bound over both strip widths
-            if (!hp.empty() && dir_total + db > DIR_BUDGET_BYTES) break;
+            if (!hp.empty() && dir_total + db > budget) break;
             KWPair P; P.a_off = off_a[k]; P.b_off = off_b[k]; P.la = la; P.lb = lb; P.dir_off = dir_total; P.bnd_off = 0; P.scr_off = 0; P.pssm_off = pssm ? 0 : -1;
             hp.push_back(P); out_off.push_back(out_total);
             dir_total += db; out_total += (int64_t)la + lb + 1;

@@ -77,12 +77,14 @@ template <> struct KWCodes<8> { typedef unsigned long long T; };
 template <> struct KWCodes<4> { typedef unsigned T; };
 template <> struct KWCodes<2> { typedef unsigned short T; };
 
-template <int MODE, bool DIRS, int C>
+// BAND: the (single) pair is a row band of a larger matrix (KWBand, swb_internal.h): absolute rows = band.row0 + i, the
+// top row comes from a checkpoint, checkpoint rows are written on the way (checkpointed traceback, align.cu).
+template <int MODE, bool DIRS, int C, bool BAND>
 __global__ void __launch_bounds__(KW_WARPS * 32)
 kw_kernel(const uint8_t *__restrict__ a_all, const uint8_t *__restrict__ b_all, const KWPair *__restrict__ pairs,
           int n_pairs, int team_warps, int n_teams, const int32_t *__restrict__ mat, int nl, int o, int e, int unit,
           uint8_t *__restrict__ dir, int4 *__restrict__ bnd, int *__restrict__ scratch, KWResult *__restrict__ res,
-          const int32_t *__restrict__ pssm_all)
+          const int32_t *__restrict__ pssm_all, const KWBand band)
 {
     constexpr int SW = 32 * C;
     typedef typename KWCodes<C>::T codes_t;
@@ -105,6 +107,8 @@ kw_kernel(const uint8_t *__restrict__ a_all, const uint8_t *__restrict__ b_all, 
         const KWPair P = pairs[pidx];
         const uint8_t *a = a_all + P.a_off, *b = b_all + P.b_off;
         const int la = P.la, lb = P.lb;
+        const int row0 = BAND ? band.row0 : 0;                 // absolute row = row0 + i
+        const int la_abs = BAND ? band.la_full : la, lb_abs = BAND ? band.lb_full : lb;
         // PositionSpecificMatrix (SA.rs:583-623): score of (row i, column j) = scores[(i-1) + (j-1)*la]
         const int32_t *pssm = (pssm_all != nullptr && P.pssm_off >= 0) ? pssm_all + P.pssm_off : nullptr;
         const int n_strips = (lb + SW - 1) / SW;
@@ -130,16 +134,21 @@ kw_kernel(const uint8_t *__restrict__ a_all, const uint8_t *__restrict__ b_all, 
                 const int j = j0 + c + 1;
                 const int ls = j * se + (so - se);             // SA.rs:100-104: X = ls, M = Y = ls + sentinel, prev = GAPINX
                 Mu[c] = ls + sent; Xu[c] = ls; Yu[c] = ls + sent;
+                if (BAND && band.ckpt_in != nullptr && j <= lb) { const int4 v = band.ckpt_in[j]; Mu[c] = v.x; Xu[c] = v.y; Yu[c] = v.z; }
                 Hu[c] = __vimax3_s32(Mu[c], Xu[c], Yu[c]); Au[c] = kw_am(Mu[c], Xu[c], Yu[c]);
                 boff[c] = (j <= lb) ? (pssm ? 0 : (int)b[j - 1]) : (nl - 1);
             }
             int hd0; unsigned ad0;                             // diagonal of column 0 at the next row: cell (row-1, j0)
             if (j0 == 0) { hd0 = 0; ad0 = 0u; }                // (0,0): M = 0, X = Y = -1 (SA.rs:88-93)
             else { const int ls = j0 * se + (so - se); hd0 = __vimax3_s32(ls + sent, ls, ls + sent); ad0 = kw_am(ls + sent, ls, ls + sent); }
+            if (BAND && row0 > 0) {                            // the diagonal of the band's first row is cell (row0, j0)
+                if (j0 == 0) { const int ls = row0 * se + (so - se); hd0 = __vimax3_s32(ls + sent, ls + sent, ls); ad0 = kw_am(ls + sent, ls + sent, ls); }   // SA.rs:109-113
+                else if (j0 <= lb) { const int4 v = band.ckpt_in[j0]; hd0 = __vimax3_s32(v.x, v.y, v.z); ad0 = kw_am(v.x, v.y, v.z); }
+            }
             int lastM = 0, lastX = 0, lastY = 0;               // this lane's last column, row of the previous step
             uint8_t *dstrip = DIRS ? dir + P.dir_off + (int64_t)sidx * (la + 31) * SW + lane * C : nullptr;
             int sb = 0, si = -1, sj = -1;                      // local: this strip's first strict maximum in this lane
-            const int own = lb - 1 - j0;                       // register index of column lb when it is in this lane
+            const int own = lb_abs - 1 - j0;                   // register index of column lb when it is in this lane
 
             const int n_steps = la + 31;
             for (int t = 0; t < n_steps; ++t) {
@@ -165,13 +174,13 @@ kw_kernel(const uint8_t *__restrict__ a_all, const uint8_t *__restrict__ b_all, 
                 int tY = __shfl_up_sync(0xffffffffu, lastY, 1);
                 const bool active = (i >= 1 && i <= la);
                 if (lane == 0 && active) {
-                    if (sidx == 0) { const int ls = i * se + (so - se); tM = ls + sent; tX = ls + sent; tY = ls; }   // SA.rs:109-113
+                    if (sidx == 0) { const int ls = (row0 + i) * se + (so - se); tM = ls + sent; tX = ls + sent; tY = ls; }   // SA.rs:109-113
                     else { const int4 v = bnd_sh[wib][t & 31]; tM = v.x; tX = v.y; tY = v.z; }
                 }
                 if (active) {
                     const int *mrow = mat_sh + (int)a_sh[wib][(i - 1) & 63] * nl;
-                    const int po = (MODE == SWB_GLOCAL && i == la) ? so : o;     // SA.rs:166-167 (global: so == o)
-                    const int pe = (MODE == SWB_GLOCAL && i == la) ? se : e;
+                    const int po = (MODE == SWB_GLOCAL && row0 + i == la_abs) ? so : o;     // SA.rs:166-167 (global: so == o)
+                    const int pe = (MODE == SWB_GLOCAL && row0 + i == la_abs) ? se : e;
                     int hd = hd0; unsigned ad = ad0;
                     hd0 = __vimax3_s32(tM, tX, tY); ad0 = kw_am(tM, tX, tY);     // next row's diagonal for column 0
                     codes_t codes = 0;
@@ -211,6 +220,12 @@ kw_kernel(const uint8_t *__restrict__ a_all, const uint8_t *__restrict__ b_all, 
                         have_fin = true;
                     }
                     lastM = Mu[C - 1]; lastX = Xu[C - 1]; lastY = Yu[C - 1];
+                    if (BAND && band.ckpt_out != nullptr && (row0 + i) % band.every == 0 && row0 + i < la_abs) {
+                        int4 *crow = band.ckpt_out + (int64_t)((row0 + i) / band.every - 1) * band.stride;
+#pragma unroll
+                        for (int c = 0; c < C; ++c)
+                            if (j0 + c + 1 <= lb) crow[j0 + c + 1] = make_int4(Mu[c], Xu[c], Yu[c], 0);
+                    }
                     if (lane == 31 && sidx + 1 < n_strips) {
                         bnd_out[i] = make_int4(lastM, lastX, lastY, 0);
                         if (team_warps > 1 && ((i & 31) == 0 || i == la)) {       // publish rows 1..i of this strip's last column
@@ -290,30 +305,43 @@ static int kw_blocks_per_sm(const swb_engine *e, int cols)
     if (cached[which][nl]) return cached[which][nl];
     const size_t smem = (size_t)nl * nl * sizeof(int);
     int best = 1 << 30, v = 0;
-#define KW_OCC(M, D, C) if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&v, kw_kernel<M, D, C>, KW_WARPS * 32, smem) == cudaSuccess) best = std::min(best, v); else best = 0;
+#define KW_OCC(M, D, C) if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&v, kw_kernel<M, D, C, false>, KW_WARPS * 32, smem) == cudaSuccess) best = std::min(best, v); else best = 0;
     if (which) { KW_FOR_MODES(KW_OCC, 2) } else { KW_FOR_MODES(KW_OCC, 8) }
 #undef KW_OCC
     cached[which][nl] = std::max(1, std::min(best, 8));
     return cached[which][nl];
 }
 
-void kw_plan(const swb_engine *e, KWPair *pairs, int n_pairs, bool with_dirs, KWPlan *plan)
+void kw_plan(const swb_engine *e, KWPair *pairs, int n_pairs, bool with_dirs, KWPlan *plan, int force_cols)
 {
-    // narrow strips (2 columns per lane) when even one warp per 256-column strip would leave most of the GPU idle
+    // Strip width.  Score only: 8 columns per lane -- with whole-round teams (cost model below) a step of 8 cells per lane
+    // costs the same 0.44 us as a step of 2 (the step is bound by its shuffle / staging latency), so the wide strip wins:
+    // 100 kb pair 49 ms vs 71 ms.  With direction bytes a step of 8 cells is ~340 instructions of one warp and no longer
+    // latency-bound (0.71 us vs 0.51 us per step): a few long pairs then run better on 2-column strips and 4x the warps.
     int64_t strips8 = 0;
     for (int k = 0; k < n_pairs; ++k) strips8 += (pairs[k].lb + 255) / 256;
-    int cols = (n_pairs > 0 && strips8 * 3 < e->sm_count * kw_blocks_per_sm(e, 8) * KW_WARPS) ? 2 : 8;
+    int cols = (with_dirs && n_pairs > 0 && strips8 * 3 < e->sm_count * kw_blocks_per_sm(e, 8) * KW_WARPS) ? 2 : 8;
+    if (force_cols == 2 || force_cols == 8) cols = force_cols;
     if (const char *f = getenv("SWB_KW_COLS")) { if (atoi(f) == 2) cols = 2; else if (atoi(f) == 8) cols = 8; }   // tests force both widths
     const int capacity = e->sm_count * kw_blocks_per_sm(e, cols) * KW_WARPS;   // warps that are guaranteed to be co-resident
     const int sw = 32 * cols;
     int T = 1;
     if (n_pairs > 0 && n_pairs < capacity / 4) {
-        int useful = 1;
-        for (int k = 0; k < n_pairs; ++k) {
-            const int strips = (pairs[k].lb + sw - 1) / sw;
-            useful = std::max(useful, std::min(strips, std::max(1, pairs[k].la / 128)));
+        // A team of T warps sweeps a pair in ceil(strips / T) rounds; warp w trails warp w-1 by 32 rows, so the sweep lasts
+        // about rounds * la + 32 * T steps.  Take the T (a whole number of rounds) that minimises it for the largest pair.
+        int big = 0;
+        for (int k = 1; k < n_pairs; ++k)
+            if ((int64_t)pairs[k].la * pairs[k].lb > (int64_t)pairs[big].la * pairs[big].lb) big = k;
+        const int strips = (pairs[big].lb + sw - 1) / sw, cap = std::max(1, std::min(capacity / n_pairs, strips));
+        int64_t best_cost = -1;
+        for (int rounds = 1; rounds <= strips; ++rounds) {
+            const int t = (strips + rounds - 1) / rounds;
+            if (t > cap) continue;
+            const int64_t cost = (int64_t)rounds * pairs[big].la + 32ll * t;
+            if (best_cost < 0 || cost < best_cost) { best_cost = cost; T = t; }
+            if (t == 1) break;
         }
-        T = std::max(1, std::min(capacity / n_pairs, useful));
+        if (const char *f = getenv("SWB_KW_TEAM")) { const int v = atoi(f); if (v >= 1) T = std::min(v, cap); }   // tuning aid
     }
     plan->cols = cols;
     plan->team_warps = T;
@@ -343,14 +371,46 @@ static cudaError_t kw_launch_mode(const swb_engine *e, const uint8_t *d_a, const
     cudaError_t err = cudaMemsetAsync(d_scratch, 0, (size_t)pl.scratch_ints * sizeof(int), st);
     if (err != cudaSuccess) return err;
     if (d_dir)
-        kw_kernel<MODE, true, C><<<pl.blocks, KW_WARPS * 32, smem, st>>>(d_a, d_b, d_pairs, n_pairs, pl.team_warps, pl.n_teams,
-                                                                         e->d_mat, nl, e->o, e->e, e->scale, d_dir, d_bnd,
-                                                                         d_scratch, d_res, d_pssm);
+        kw_kernel<MODE, true, C, false><<<pl.blocks, KW_WARPS * 32, smem, st>>>(d_a, d_b, d_pairs, n_pairs, pl.team_warps, pl.n_teams,
+                                                                                e->d_mat, nl, e->o, e->e, e->scale, d_dir, d_bnd,
+                                                                                d_scratch, d_res, d_pssm, KWBand());
     else
-        kw_kernel<MODE, false, C><<<pl.blocks, KW_WARPS * 32, smem, st>>>(d_a, d_b, d_pairs, n_pairs, pl.team_warps, pl.n_teams,
-                                                                          e->d_mat, nl, e->o, e->e, e->scale, d_dir, d_bnd,
-                                                                          d_scratch, d_res, d_pssm);
+        kw_kernel<MODE, false, C, false><<<pl.blocks, KW_WARPS * 32, smem, st>>>(d_a, d_b, d_pairs, n_pairs, pl.team_warps, pl.n_teams,
+                                                                                 e->d_mat, nl, e->o, e->e, e->scale, d_dir, d_bnd,
+                                                                                 d_scratch, d_res, d_pssm, KWBand());
     return cudaGetLastError();
+}
+
+template <int MODE, int C>
+static cudaError_t kw_launch_band_mode(const swb_engine *e, const uint8_t *d_a, const uint8_t *d_b, const KWPair *d_pair,
+                                       const KWPlan &pl, const KWBand &band, uint8_t *d_dir, int4 *d_bnd, int *d_scratch,
+                                       KWResult *d_res, cudaStream_t st)
+{
+    const int nl = e->n + 1;
+    const size_t smem = (size_t)nl * nl * sizeof(int);
+    cudaError_t err = cudaMemsetAsync(d_scratch, 0, (size_t)pl.scratch_ints * sizeof(int), st);
+    if (err != cudaSuccess) return err;
+    if (d_dir)
+        kw_kernel<MODE, true, C, true><<<pl.blocks, KW_WARPS * 32, smem, st>>>(d_a, d_b, d_pair, 1, pl.team_warps, pl.n_teams, e->d_mat, nl,
+                                                                               e->o, e->e, e->scale, d_dir, d_bnd, d_scratch, d_res, nullptr, band);
+    else
+        kw_kernel<MODE, false, C, true><<<pl.blocks, KW_WARPS * 32, smem, st>>>(d_a, d_b, d_pair, 1, pl.team_warps, pl.n_teams, e->d_mat, nl,
+                                                                                e->o, e->e, e->scale, d_dir, d_bnd, d_scratch, d_res, nullptr, band);
+    return cudaGetLastError();
+}
+
+cudaError_t kw_launch_band(const swb_engine *e, const uint8_t *d_a, const uint8_t *d_b, const KWPair *d_pair,
+                           const KWPlan &plan, const KWBand &band, uint8_t *d_dir, int4 *d_bnd, int *d_scratch,
+                           KWResult *d_res, cudaStream_t st)
+{
+#define KW_GO(M) (plan.cols == 2 ? kw_launch_band_mode<M, 2>(e, d_a, d_b, d_pair, plan, band, d_dir, d_bnd, d_scratch, d_res, st) \
+                                 : kw_launch_band_mode<M, 8>(e, d_a, d_b, d_pair, plan, band, d_dir, d_bnd, d_scratch, d_res, st))
+    switch (e->mode) {
+    case SWB_GLOBAL: return KW_GO(SWB_GLOBAL);
+    case SWB_GLOCAL: return KW_GO(SWB_GLOCAL);
+    default: return KW_GO(SWB_LOCAL);
+    }
+#undef KW_GO
 }
 
 cudaError_t kw_launch(const swb_engine *e, const uint8_t *d_a, const uint8_t *d_b, const KWPair *d_pairs, int n_pairs,
@@ -471,6 +531,68 @@ cudaError_t kt_stats_launch(const swb_engine *e, const KWPair *d_pairs, const KW
     const int sent = 10 * e->o + 10 * e->e;
 #define KT_GO(M) do { if (cols == 2) kt_kernel<M, 2, true><<<blocks, threads, 0, st>>>(d_pairs, d_res, n_pairs, d_dir, nullptr, nullptr, nullptr, nullptr, sent, d_raw_a, d_raw_b, d_stats); \
                       else kt_kernel<M, 8, true><<<blocks, threads, 0, st>>>(d_pairs, d_res, n_pairs, d_dir, nullptr, nullptr, nullptr, nullptr, sent, d_raw_a, d_raw_b, d_stats); } while (0)
+    switch (e->mode) {
+    case SWB_GLOBAL: KT_GO(SWB_GLOBAL); break;
+    case SWB_GLOCAL: KT_GO(SWB_GLOCAL); break;
+    default: KT_GO(SWB_LOCAL); break;
+    }
+#undef KT_GO
+    return cudaGetLastError();
+}
+
+
+// KT on a row band (checkpointed traceback): the walk of kt_kernel, resumed at a cursor and suspended at the band's
+// top row.  dir holds the direction bytes of rows (row0, row0 + la_band] only.
+template <int MODE, int COLS>
+__global__ void kt_band_kernel(const uint8_t *__restrict__ dir, int la_band, int row0, KTCursor *__restrict__ cur,
+                               int32_t *__restrict__ xa, int32_t *__restrict__ xb, int sent)
+{
+    if (blockIdx.x != 0 || threadIdx.x != 0) return;
+    KTCursor K = *cur;
+    int cx = K.cx, cy = K.cy, st = K.st, n = K.n, status = 0;
+    for (;;) {
+        if (row0 > 0 && cx == row0) { status = 1; break; }         // the predecessor codes of this row belong to the band above
+        unsigned prev;
+        if (cx >= 1 && cy >= 1) {
+            if (cx - row0 > KT_AHEAD && cy > KT_AHEAD)
+                asm volatile("prefetch.global.L1 [%0];" ::"l"(dir + kt_addr<COLS>(0, la_band, cx - row0 - KT_AHEAD, cy - KT_AHEAD)));
+            prev = ((unsigned)dir[kt_addr<COLS>(0, la_band, cx - row0, cy)] >> (2 * st)) & 3u;
+        }
+        else if (cx == 0 && cy == 0) prev = 0;
+        else if (cx == 0) {                                        // row 0: prev = GAPINX for all states (SA.rs:105-107)
+            prev = 1;
+            if (MODE == SWB_LOCAL && (st == 1 || sent == 0)) prev = 3;
+        } else {                                                   // column 0: prev = GAPINY (SA.rs:114-116)
+            prev = 2;
+            if (MODE == SWB_LOCAL && (st == 2 || sent == 0)) prev = 3;
+        }
+        if (MODE == SWB_LOCAL && prev == 3) break;
+        if (st == 0) {
+            if (cx == 0 || cy == 0) { status = -2; break; }
+            xa[n] = cx - 1; xb[n] = cy - 1;
+            ++n; --cx; --cy;
+        } else if (st == 1) {
+            if (cy == 0) { status = -2; break; }
+            xa[n] = -1; xb[n] = cy - 1;
+            ++n; --cy;
+        } else {
+            if (cx == 0) { status = -2; break; }
+            xa[n] = cx - 1; xb[n] = -1;
+            ++n; --cx;
+        }
+        if (cx == 0 && cy == 0) break;
+        st = (int)prev;
+    }
+    K.cx = cx; K.cy = cy; K.st = st; K.n = n; K.status = status;
+    *cur = K;
+}
+
+cudaError_t kt_band_launch(const swb_engine *e, const uint8_t *d_dir, int cols, int32_t la_band, int32_t row0,
+                           KTCursor *d_cur, int32_t *d_idx_a, int32_t *d_idx_b, cudaStream_t st)
+{
+    const int sent = 10 * e->o + 10 * e->e;
+#define KT_GO(M) do { if (cols == 2) kt_band_kernel<M, 2><<<1, 32, 0, st>>>(d_dir, la_band, row0, d_cur, d_idx_a, d_idx_b, sent); \
+                      else kt_band_kernel<M, 8><<<1, 32, 0, st>>>(d_dir, la_band, row0, d_cur, d_idx_a, d_idx_b, sent); } while (0)
     switch (e->mode) {
     case SWB_GLOBAL: KT_GO(SWB_GLOBAL); break;
     case SWB_GLOCAL: KT_GO(SWB_GLOCAL); break;

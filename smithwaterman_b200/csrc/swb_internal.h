@@ -118,7 +118,7 @@ struct KWPlan {
     int64_t scratch_ints = 0;       // progress counters + candidates of all pairs
     int64_t dir_bytes = 0;          // direction bytes of all pairs (with_dirs)
 };
-void kw_plan(const swb_engine *e, KWPair *pairs, int n_pairs, bool with_dirs, KWPlan *plan);   // also assigns dir_off
+void kw_plan(const swb_engine *e, KWPair *pairs, int n_pairs, bool with_dirs, KWPlan *plan, int force_cols = 0);   // also assigns dir_off
 struct KWResult {
     int32_t score;                  // scaled
     int32_t end_i, end_j;           // start cell of the traceback (1-based), -1 = empty
@@ -127,6 +127,25 @@ struct KWResult {
 cudaError_t kw_launch(const swb_engine *e, const uint8_t *d_a, const uint8_t *d_b, const KWPair *d_pairs,
                       int n_pairs, const KWPlan &plan, uint8_t *d_dir, int4 *d_bnd, int *d_scratch, KWResult *d_res,
                       cudaStream_t st, const int32_t *d_pssm = nullptr);
+// Checkpointed traceback (pairs whose direction bytes do not fit): the same kernel run on ONE pair as a ROW BAND.
+// The pair handed to the kernel is the sub-matrix rows (row0, row0+la] x columns [1, lb] of a la_full x lb_full matrix;
+// its top row (row0) comes from a checkpoint row instead of the boundary, and/or it writes checkpoint rows itself.
+struct KWBand {
+    int32_t row0 = 0;               // rows above the band (a_off of the pair already points at row row0+1)
+    int32_t la_full = 0, lb_full = 0;
+    const int4 *ckpt_in = nullptr;  // (M, X, Y) of row row0 at [j], j = 1..lb; nullptr = the matrix boundary (row0 == 0)
+    int4 *ckpt_out = nullptr;       // rows every, 2*every, ... (< la_full): row k*every at [(k-1)*stride + j]
+    int32_t every = 0;
+    int64_t stride = 0;
+};
+cudaError_t kw_launch_band(const swb_engine *e, const uint8_t *d_a, const uint8_t *d_b, const KWPair *d_pair,
+                           const KWPlan &plan, const KWBand &band, uint8_t *d_dir, int4 *d_bnd, int *d_scratch,
+                           KWResult *d_res, cudaStream_t st);
+// KT on a band: resumes the walk at the cursor, stops at the band's top row (status 1), at the alignment's start
+// (status 0) or at one of the reference's panic cases (status < 0); appends to the reversed column lists at [n].
+struct KTCursor { int32_t cx, cy, st, n, status; };
+cudaError_t kt_band_launch(const swb_engine *e, const uint8_t *d_dir, int cols, int32_t la_band, int32_t row0,
+                           KTCursor *d_cur, int32_t *d_idx_a, int32_t *d_idx_b, cudaStream_t st);
 int64_t kw_dir_bytes(int32_t la, int32_t lb, int cols);   // bytes of the skewed direction store of one pair
 // KT: pointer walk over the direction bytes; one thread per pair.  Writes reversed column lists.
 cudaError_t kt_launch(const swb_engine *e, const KWPair *d_pairs, const KWResult *d_res, int n_pairs,

@@ -717,3 +717,60 @@ def test_global_score_batch_packed_kernel(go, ge):
     o2, _, _ = _oracle_scores(m, [q] * 800, sb[:800], go, ge, swb.ALIGN_GLOBAL)
     assert np.array_equal(np.rint(s2.astype(np.float64) * 2).astype(np.int64), o2)
     eng.close()
+
+
+@pytest.mark.parametrize("cols", ["2", "8"])
+@pytest.mark.parametrize("mode", [swb.ALIGN_LOCAL, swb.ALIGN_GLOCAL, swb.ALIGN_GLOBAL])
+def test_checkpointed_traceback_equals_direct(mode, cols, monkeypatch):
+    """Checkpointed recompute (configs[3]): with a direction-byte budget far below the pairs' needs the traceback runs
+    as forward sweep + row bands; index lists, strings, score and end cell must equal the oracle and the direct path.
+    Pairs include related DNA (long diagonal path through every band), unrelated sequences (local: short path; global:
+    path along the edges), very unequal lengths and |open| < |extend|."""
+    monkeypatch.setenv("SWB_KW_COLS", cols)
+    rng = np.random.default_rng(20250 + int(cols))
+    m = swb.SubstitutionMatrix.get_mat_matrix(2.0, -3.0)
+    for go, ge in ((5.0, 2.0), (2.0, 3.0)):
+        sa, sb = [], []
+        for la in (900, 2500, 1700):
+            a = _rand_seqs(rng, 1, la, la, "ACGT")[0]
+            sa.append(a); sb.append(_mutate(rng, a, 0.08, 0.03, 0.03))
+        sa.append(_rand_seqs(rng, 1, 1500, 1500, "ACGT")[0]); sb.append(_rand_seqs(rng, 1, 1300, 1300, "ACGT")[0])   # unrelated
+        a = _rand_seqs(rng, 1, 3000, 3000, "ACGT")[0]
+        sa.append(a); sb.append(a[1200:1500])                                                                        # tall
+        sa.append(a[2000:2200]); sb.append(a)                                                                        # wide
+        oeng = O.Engine(_omatrix(m), go, ge, mode)
+        monkeypatch.delenv("SWB_CKPT_BYTES", raising=False)
+        eng = swb.SequenceAlignment(m, go, ge, mode)
+        direct = eng.align_list(sa, sb, True)
+        assert eng.stats()["ckpt_pairs"] == 0
+        for budget in ("65536", "300000"):
+            monkeypatch.setenv("SWB_CKPT_BYTES", budget)
+            res = eng.align_list(sa, sb, True)
+            assert eng.stats()["ckpt_pairs"] >= 5
+            for a_, b_, out, ref in zip(sa, sb, res, direct):
+                xa, xb, sc, ei, ej = oeng.raw(oeng.matrix.seq_to_index(a_.decode()), oeng.matrix.seq_to_index(b_.decode()))
+                assert out["score"] == sc == ref["score"]
+                assert (out["end_a"], out["end_b"]) == (ref["end_a"], ref["end_b"])
+                assert np.array_equal(out["idx_a"], xa) and np.array_equal(out["idx_b"], xb)
+                assert out["aln_a"] == ref["aln_a"] and out["aln_b"] == ref["aln_b"]
+        eng.close()
+
+
+def test_checkpointed_traceback_30kb(monkeypatch):
+    """A 30 kb x 30 kb DNA pair (+2/-3, 5/2) under a 64 MB direction-byte budget (the direct store needs 0.9 GB):
+    same score, end cell and strings as the direct path; the strings re-score to the reported score."""
+    rng = np.random.default_rng(20251)
+    a = _rand_seqs(rng, 1, 30000, 30000, "ACGT")[0]
+    b = _mutate(rng, a, 0.10, 0.02, 0.02)
+    m = swb.SubstitutionMatrix.get_mat_matrix(2.0, -3.0)
+    for mode in (swb.ALIGN_LOCAL, swb.ALIGN_GLOBAL):
+        eng = swb.SequenceAlignment(m, 5.0, 2.0, mode)
+        monkeypatch.delenv("SWB_CKPT_BYTES", raising=False)
+        ref = eng.align_raw(a, b, mode != swb.ALIGN_LOCAL)
+        monkeypatch.setenv("SWB_CKPT_BYTES", str(64 << 20))
+        out = eng.align_raw(a, b, mode != swb.ALIGN_LOCAL)
+        assert eng.stats()["ckpt_pairs"] == 1
+        assert out["score"] == ref["score"] and out["aln_a"] == ref["aln_a"] and out["aln_b"] == ref["aln_b"]
+        assert (out["end_a"], out["end_b"]) == (ref["end_a"], ref["end_b"])
+        assert _rescore(out["aln_a"], out["aln_b"], 2.0, -3.0, 5.0, 2.0) == out["score"]
+        eng.close()
