@@ -274,7 +274,7 @@ static int align_batch_impl(swb_engine *e, const char *a_all, const int64_t *off
     }
 
     const int64_t budget = dir_budget();
-    if (outs && !pssm) {                              // pairs whose direction bytes do not fit: checkpointed traceback, one at a time
+    if (!pssm) {                                      // pairs whose direction bytes do not fit: checkpointed traceback, one at a time
         std::vector<int64_t> rest;
         for (int64_t k : work) {
             const int32_t la = (int32_t)(off_a[k + 1] - off_a[k]), lb = (int32_t)(off_b[k + 1] - off_b[k]);
@@ -283,6 +283,17 @@ static int align_batch_impl(swb_engine *e, const char *a_all, const int64_t *off
             int rc = align_ckpt_pair(e, d_a.as<uint8_t>(), d_b.as<uint8_t>(), off_a[k], off_b[k], la, lb, budget, &R, xa, xb);
             if (rc != SWB_OK) return rc;
             e->stats.ckpt_pairs += 1;
+            if (souts) {                              // counting form: the same counts KT takes on the device, from the lists
+                KTStats S; S.ncols = (int32_t)xa.size(); S.na = 0; S.nb = 0; S.match = 0; S.s1 = S.e1 = S.s2 = S.e2 = -1;
+                for (size_t c = 0; c < xa.size(); ++c) {
+                    if (xa[c] >= 0) { if (S.s1 < 0) S.s1 = (int32_t)xa[c]; S.e1 = (int32_t)xa[c]; ++S.na; }
+                    if (xb[c] >= 0) { if (S.s2 < 0) S.s2 = (int32_t)xb[c]; S.e2 = (int32_t)xb[c]; ++S.nb; }
+                    if (xa[c] >= 0 && xb[c] >= 0 && a_all[off_a[k] + xa[c]] == b_all[off_b[k] + xb[c]]) ++S.match;
+                }
+                souts[k].score = to_f(R.score); souts[k].end_a = R.end_i; souts[k].end_b = R.end_j;
+                swb_compose_stats(&souts[k], e->mode, retain_all, la, lb, S);
+                continue;
+            }
             inflate(a_all + off_a[k], la, b_all + off_b[k], lb, xa.data(), xb.data(), (int64_t)xa.size(), e->mode, retain_all, ra, rb);
             rc = fill_out(&outs[k], to_f(R.score), R.end_i, R.end_j, xa, xb, ra, rb);
             if (rc != SWB_OK) { e->err = "out of memory"; return rc; }

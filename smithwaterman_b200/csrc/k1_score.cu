@@ -84,8 +84,8 @@ k1_local_kernel(const uint8_t *__restrict__ a_pk, const uint8_t *__restrict__ b_
     const unsigned rowstride = (unsigned)nl * 128u;
     const unsigned open2 = pack2(open, open), ext2 = pack2(ext, ext);
     const unsigned long long pol = keep_policy();
-    // per-thread snapshot of the 16 packed Ho words of the row step that holds the running best: [4][thread] uint4
-    uint4 *snap = reinterpret_cast<uint4 *>(T_sh + nl * nl * 32) + threadIdx.x;
+    // per-thread snapshot of the 16 packed Ho words of the row step that holds the running best: [16][thread]
+    unsigned *snap = T_sh + nl * nl * 32 + threadIdx.x;
 
     for (;;) {
         int g = 0;
@@ -169,18 +169,16 @@ k1_local_kernel(const uint8_t *__restrict__ a_pk, const uint8_t *__restrict__ b_
 #else
                     if (rm != thr2) {
                         // Rare path (the running best of some lane improves).  Only the row and the half are decided
-                        // here; the 16 packed Ho words of the step are parked in shared memory (4 STS.128 of the lanes
-                        // that improved) and the column is read off them once, after the last pass.
+                        // here; the 16 packed Ho words of the step are parked in shared memory (16 STS of the lanes
+                        // that improved; scalar stores: vector stores made the compiler shuffle Ho into aligned quads in the hot path) and the column is read off them once, after the last pass.
                         const int rlo = lo16(rm), rhi = hi16(rm);
                         const bool ulo = i <= la && (rlo > bestHo || (rlo == bestHo && rlo > open && i < bi));
                         if (ulo) { bestHo = rlo; bi = i; bj = jbase; }
                         const bool uhi = i >= 2 && i - 1 <= la && (rhi > bestHo || (rhi == bestHo && rhi > open && i - 1 < bi));
                         if (uhi) { bestHo = rhi; bi = i - 1; bj = jbase + K1_HALF; }
                         if (ulo || uhi) {
-                            snap[0] = make_uint4(Ho[0], Ho[1], Ho[2], Ho[3]);
-                            snap[K1_THREADS * 2] = make_uint4(Ho[4], Ho[5], Ho[6], Ho[7]);
-                            snap[K1_THREADS * 4] = make_uint4(Ho[8], Ho[9], Ho[10], Ho[11]);
-                            snap[K1_THREADS * 6] = make_uint4(Ho[12], Ho[13], Ho[14], Ho[15]);
+#pragma unroll
+                            for (int k = 0; k < K1_HALF; ++k) snap[k * K1_THREADS * 2] = Ho[k];
                             if (bestHo >= limit_ho) ovf = 1;
                             thr2 = pack2(bestHo - (first ? 0 : 1), bestHo - (first ? 0 : 1));
                         }
@@ -195,13 +193,11 @@ k1_local_kernel(const uint8_t *__restrict__ a_pk, const uint8_t *__restrict__ b_
 #endif
         }
         if (bestHo > open) {                        // column of the best cell: first word of its half that holds bestHo
-            const uint4 s0 = snap[0], s1 = snap[K1_THREADS * 2], s2 = snap[K1_THREADS * 4], s3 = snap[K1_THREADS * 6];
-            const unsigned w[K1_HALF] = {s0.x, s0.y, s0.z, s0.w, s1.x, s1.y, s1.z, s1.w, s2.x, s2.y, s2.z, s2.w, s3.x, s3.y, s3.z, s3.w};
             const bool hi = (bj & K1_HALF) != 0;    // jbase is a multiple of 32
             int kk = 0;
 #pragma unroll
             for (int k = K1_HALF - 1; k >= 0; --k)
-                if ((hi ? hi16(w[k]) : lo16(w[k])) == bestHo) kk = k;
+                { const unsigned w = snap[k * K1_THREADS * 2]; if ((hi ? hi16(w) : lo16(w)) == bestHo) kk = k; }
             bj += kk + 1;
         }
         if (valid) {
@@ -272,7 +268,7 @@ k2_search_kernel(const unsigned *__restrict__ a_words, int la, const uint8_t *__
     const unsigned rowstride = (unsigned)nl * 128u;
     const unsigned open2 = pack2(open, open), ext2 = pack2(ext, ext);
     const unsigned pad = (unsigned)(nl - 1), pad4 = pad * 0x01010101u;
-    uint4 *snap = reinterpret_cast<uint4 *>(T_sh + nl * nl * 32) + threadIdx.x;    // [4][thread] uint4, see K1
+    uint4 *snap = reinterpret_cast<uint4 *>(T_sh + nl * nl * 32) + threadIdx.x;    // [4][thread] uint4 (K2 keeps the vector form: measured faster here)
     const int nblk = (la + 1 + 3) >> 2;              // row blocks of a pass (one step past la finishes the high half)
     const int nwords = (la + 3) >> 2;                // query words that hold real rows
 

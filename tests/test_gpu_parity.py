@@ -774,3 +774,22 @@ def test_checkpointed_traceback_30kb(monkeypatch):
         assert (out["end_a"], out["end_b"]) == (ref["end_a"], ref["end_b"])
         assert _rescore(out["aln_a"], out["aln_b"], 2.0, -3.0, 5.0, 2.0) == out["score"]
         eng.close()
+
+
+@pytest.mark.parametrize("mode", [swb.ALIGN_LOCAL, swb.ALIGN_GLOBAL])
+def test_checkpointed_counting_form(mode, monkeypatch):
+    """swb_align_stats_batch on pairs over the direction-byte budget: the counts equal those of the direct path."""
+    rng = np.random.default_rng(20252)
+    m = swb.SubstitutionMatrix.get_blosum62_matrix()
+    sa = _rand_seqs(rng, 6, 600, 1500)
+    sb = [bytes(_mutate(rng, a, 0.2, 0.03, 0.03, AA.encode())) for a in sa[:4]] + _rand_seqs(rng, 2, 700, 900)
+    eng = swb.SequenceAlignment(m, 10.0, 0.5, mode)
+    monkeypatch.delenv("SWB_CKPT_BYTES", raising=False)
+    for retain_all in (False, True):
+        ref = eng.align_stats(sa, sb, retain_all)
+        monkeypatch.setenv("SWB_CKPT_BYTES", "100000")
+        out = eng.align_stats(sa, sb, retain_all)
+        assert eng.stats()["ckpt_pairs"] == 6
+        monkeypatch.delenv("SWB_CKPT_BYTES", raising=False)
+        assert out.tobytes() == ref.tobytes()
+    eng.close()
