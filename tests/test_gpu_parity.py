@@ -354,11 +354,13 @@ def test_config4_dna_pair_dense_oracle(mode, cols, monkeypatch):
     eng.close()
 
 
-def test_config4_dna_pair_100kb_properties():
+def test_config4_dna_pair_100kb_properties(monkeypatch):
     """BASELINE configs[3] at full size (100 kb x ~100 kb, 10^10 cells, 10 GB of direction bytes).  The dense oracle
     cannot hold this; checked instead: (i) the score equals the linear-memory integer oracle's on a 30 kb prefix pair,
     (ii) at full size the emitted strings re-score to the reported score, spell the inputs, and the global score is
-    not above the local one, (iii) score-only and traceback paths agree."""
+    not above the local one, (iii) score-only and traceback paths agree, (iv) the checkpointed recompute (2 GB of
+    direction bytes instead of 10 GB) returns the same strings, score and end cell as the direct store."""
+    monkeypatch.delenv("SWB_CKPT_BYTES", raising=False)
     rng = np.random.default_rng(20244)
     a = _rand_seqs(rng, 1, 100000, 100000, "ACGT")[0]
     b = _mutate(rng, a, 0.08, 0.02, 0.02)
@@ -375,6 +377,12 @@ def test_config4_dna_pair_100kb_properties():
         sc, ea, eb = eng.score_batch([a], [b])
         assert float(sc[0]) == out["score"] and (int(ea[0]), int(eb[0])) == (out["end_a"], out["end_b"])
         scores[mode] = out["score"]
+        monkeypatch.setenv("SWB_CKPT_BYTES", str(2 << 30))
+        ck = eng.align_raw(a, b, False)
+        monkeypatch.delenv("SWB_CKPT_BYTES", raising=False)
+        assert eng.stats()["ckpt_pairs"] == 1
+        assert (ck["score"], ck["end_a"], ck["end_b"], ck["aln_a"], ck["aln_b"]) == \
+               (out["score"], out["end_a"], out["end_b"], out["aln_a"], out["aln_b"])
         pa, pb = a[:30000], b[:30000]
         sc, ea, eb = eng.score_batch([pa], [pb])
         ia, oa = O.pack([om.seq_to_index(pa.decode())]); ib, ob = O.pack([om.seq_to_index(pb.decode())])
