@@ -801,3 +801,28 @@ def test_checkpointed_counting_form(mode, monkeypatch):
         monkeypatch.delenv("SWB_CKPT_BYTES", raising=False)
         assert out.tobytes() == ref.tobytes()
     eng.close()
+
+
+def test_srspair_reports_from_the_engine(emboss):
+    """8f-n3: the engine's alignments printed by the srspair writer equal the bodies of the reference's EMBOSS golden
+    files byte for byte: all 100 water (local) reports, and every needle report whose terminal overhang EMBOSS places
+    like the reference does (the rest differ only there, test/check_results.pl:486-508)."""
+    import gzip, json, os
+    from conftest import GOLDEN
+    from smithwaterman_b200 import report
+    with gzip.open(os.path.join(GOLDEN, "emboss_reports.json.gz")) as f:
+        bodies = {(r["kind"], r["id"]): r["body"] for r in json.loads(f.read().decode())}
+    m = swb.SubstitutionMatrix.get_blosum62_matrix()
+    same = {}
+    for mode, key in ((swb.ALIGN_LOCAL, "local"), (swb.ALIGN_GLOBAL, "global"), (swb.ALIGN_GLOCAL, "glocal")):
+        eng = swb.SequenceAlignment(m, 10.0, 0.5, mode)
+        res = eng.align_list([p["seq1"].encode() for p in emboss], [p["seq2"].encode() for p in emboss], mode != swb.ALIGN_LOCAL)
+        same[key] = 0
+        for p, r in zip(emboss, res):
+            sa, sb = report.starts_of(r["idx_a"], r["idx_b"]) if mode == swb.ALIGN_LOCAL else (1, 1)
+            body = report.srspair_body(r["aln_a"], r["aln_b"], r["score"], m, 10.0, 0.5, sa, sb)
+            if mode == swb.ALIGN_LOCAL or (r["aln_a"], r["aln_b"]) == (p[key]["s1"], p[key]["s2"]):
+                assert body == bodies[(key, p["id"])], "%s %d" % (key, p["id"])
+                same[key] += 1
+        eng.close()
+    assert same["local"] == 100 and same["global"] > 0
