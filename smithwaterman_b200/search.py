@@ -12,6 +12,7 @@ per-rank top-K records (K x 24 bytes).  Ties are broken by (score desc, database
 independent of the number of ranks.
 """
 import ctypes
+import os
 
 import numpy as np
 
@@ -53,9 +54,81 @@ class Database:
         return Database(out, off, None)
 
 
-def shard_indices(lengths, world_size):
+    # ---- packed on-disk form -------------------------------------------------------------------
+    # One file, little endian, every section 4096-byte aligned so that it can be memory-mapped and handed to the
+    # C ABI (which takes letters + int64 offsets) without a parse step:
+    #   header (4096 B): magic "SWB200DB", u32 version, u32 flags, i64 n, i64 n_residues, i64 names_bytes,
+    #                    i64 offset of {offsets, residues, order, names}
+    #   offsets  int64[n+1]   residues  u8[n_residues] (letters as in the FASTA)   order  int64[n] (stable, longest first:
+    #   what shard_indices deals round-robin, stored so that a rank does not sort 6*10^5 lengths per query)
+    #   names    UTF-8, one per line
+    MAGIC = b"SWB200DB"
+    VERSION = 1
+
+    def save(self, path):
+        def pad(k):
+            return (k + 4095) // 4096 * 4096
+        names = ("\n".join(self.names) + "\n").encode() if self.names else b""
+        order = np.argsort(-self.lengths(), kind="stable").astype(np.int64)
+        o_off = 4096
+        o_res = o_off + pad(self.offsets.nbytes)
+        o_ord = o_res + pad(self.residues.nbytes)
+        o_nam = o_ord + pad(order.nbytes)
+        head = np.zeros(4096, np.uint8)
+        head[:8] = np.frombuffer(self.MAGIC, np.uint8)
+        head[8:16].view(np.uint32)[:] = (self.VERSION, 1 if self.names else 0)
+        head[16:72].view(np.int64)[:] = (self.n, len(self.residues), len(names), o_off, o_res, o_ord, o_nam)
+        with open(path, "wb") as f:
+            f.write(head.tobytes())
+            for off, blob in ((o_off, self.offsets.tobytes()), (o_res, self.residues.tobytes()), (o_ord, order.tobytes()), (o_nam, names)):
+                f.seek(off)
+                f.write(blob)
+            f.truncate(o_nam + pad(len(names)))
+
+    @staticmethod
+    def load(path, mmap=True):
+        """Memory-mapped (default) or in-memory Database from a file written by save()."""
+        head = np.fromfile(path, np.uint8, 4096)
+        if len(head) < 4096 or head[:8].tobytes() != Database.MAGIC:
+            raise ValueError("%s: not a swb200 database file" % path)
+        ver, flags = (int(v) for v in head[8:16].view(np.uint32))
+        if ver != Database.VERSION:
+            raise ValueError("%s: unsupported database version %d" % (path, ver))
+        n, nres, nnames, o_off, o_res, o_ord, o_nam = (int(v) for v in head[16:72].view(np.int64))
+        size = os.path.getsize(path)
+        if n < 0 or nres < 0 or o_off + 8 * (n + 1) > size or o_res + nres > size or o_ord + 8 * n > size or o_nam + nnames > size:
+            raise ValueError("%s: truncated database file" % path)
+        rd = (lambda dt, off, cnt: np.memmap(path, dt, "r", off, (cnt,))) if mmap else \
+             (lambda dt, off, cnt: np.fromfile(path, dt, cnt, offset=off))
+        offsets = np.asarray(rd(np.int64, o_off, n + 1))
+        if offsets[0] != 0 or offsets[-1] != nres or np.any(offsets[1:] < offsets[:-1]):
+            raise ValueError("%s: corrupt offsets" % path)
+        names = None
+        if flags & 1:
+            with open(path, "rb") as f:
+                f.seek(o_nam)
+                names = f.read(nnames).decode().split("\n")[:n]
+        db = Database.__new__(Database)
+        db.residues = rd(np.uint8, o_res, nres) if nres else np.zeros(0, np.uint8)
+        db.offsets = np.ascontiguousarray(offsets)
+        db.names = names
+        db.n = n
+        db.order = np.asarray(rd(np.int64, o_ord, n)) if n else np.zeros(0, np.int64)
+        return db
+
+    @staticmethod
+    def from_fasta(path):
+        """FASTA ingest with the reference's header rules (SeqData.load_fasta, SA.rs:830-887)."""
+        from .engine import SeqData
+        recs = SeqData.load_fasta(path)
+        return Database.from_sequences([r.to_bytes() if hasattr(r, "to_bytes") else "".join(r.seq).encode() for r in recs],
+                                       [r.name for r in recs])
+
+
+def shard_indices(lengths, world_size, order=None):
     """Round-robin deal over the length-sorted order (stable, longest first): list of index arrays, one per rank."""
-    order = np.argsort(-np.asarray(lengths, np.int64), kind="stable")
+    if order is None:
+        order = np.argsort(-np.asarray(lengths, np.int64), kind="stable")
     return [np.sort(order[r::world_size]) for r in range(world_size)]
 
 
@@ -129,7 +202,7 @@ def search(engine, query, db, topk=100, traceback=True, retain_all=False, rank=0
     """
     if world_size > 1:
         if shard is None:
-            idx = shard_indices(db.lengths(), world_size)[rank]
+            idx = shard_indices(db.lengths(), world_size, getattr(db, "order", None))[rank]
             shard = (idx, db.subset(idx))
         idx, sub = shard
     else:

@@ -75,3 +75,40 @@ def test_world2_gloo_matches_single_process():
     scores = [r[1] for r in ref]
     assert any(scores[i] == scores[i + 1] and ref[i][0] < ref[i + 1][0] for i in range(len(ref) - 1))
     assert scores == sorted(scores, reverse=True)
+
+
+def test_packed_database_file_round_trip(tmp_path):
+    """8f-n3: the packed on-disk database (Database.save / load): memory-mapped load returns the same residues, offsets,
+    names and shard deal as the in-memory object; FASTA ingest follows the reference's header rules; bad files raise."""
+    import pytest
+    rng = np.random.default_rng(7)
+    aa = np.frombuffer(b"ARNDCQEGHILKMFPSTWYV", np.uint8)
+    seqs = [bytes(aa[rng.integers(0, 20, int(k))]) for k in rng.integers(1, 400, 300)] + [b""]
+    names = ["sp|%05d|x y" % k for k in range(len(seqs))]
+    db = S.Database.from_sequences(seqs, names)
+    path = str(tmp_path / "db.swdb")
+    db.save(path)
+    for mm in (True, False):
+        d2 = S.Database.load(path, mmap=mm)
+        assert d2.n == db.n and np.array_equal(d2.offsets, db.offsets) and np.array_equal(np.asarray(d2.residues), db.residues)
+        assert d2.names == names and d2.sequence(17) == seqs[17] and d2.sequence(db.n - 1) == b""
+        for w in (1, 2, 8):
+            a = S.shard_indices(db.lengths(), w); b = S.shard_indices(d2.lengths(), w, d2.order)
+            assert all(np.array_equal(x, y) for x, y in zip(a, b))
+        sub = d2.subset(S.shard_indices(d2.lengths(), 4, d2.order)[1])
+        ref = db.subset(S.shard_indices(db.lengths(), 4)[1])
+        assert np.array_equal(sub.residues, ref.residues) and np.array_equal(sub.offsets, ref.offsets)
+    # FASTA ingest
+    fa = tmp_path / "x.fas"
+    fa.write_text(">a first\nACD\nEF\n>b\nGHI\n")
+    d3 = S.Database.from_fasta(str(fa))
+    assert d3.n == 2 and d3.sequence(0) == b"ACDEF" and d3.sequence(1) == b"GHI" and d3.names == ["a", "b"]
+    # bad files
+    bad = tmp_path / "bad.swdb"
+    bad.write_bytes(b"NOTADB" + bytes(5000))
+    with pytest.raises(ValueError):
+        S.Database.load(str(bad))
+    raw = bytearray(open(path, "rb").read())
+    open(str(bad), "wb").write(raw[:6000])
+    with pytest.raises(ValueError):
+        S.Database.load(str(bad))

@@ -43,6 +43,7 @@ def main():
     ap.add_argument("--query", type=int, default=5000)
     ap.add_argument("--topk", type=int, default=100)
     ap.add_argument("--steps", type=int, default=3)
+    ap.add_argument("--db", default=None, help="packed database file (Database.save); written first by rank 0 if it does not exist")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0")); local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -55,10 +56,16 @@ def main():
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     q, res, off = make_db(args.query, int(args.residues))
     db = S.Database(res, off)
-    idx = S.shard_indices(db.lengths(), world)[rank]
+    if args.db:                                                # the database as a resident service would hold it: memory-mapped file
+        if rank == 0 and not os.path.exists(args.db):
+            db.save(args.db)
+        if world > 1:
+            dist.barrier()
+        db = S.Database.load(args.db)
+    idx = S.shard_indices(db.lengths(), world, getattr(db, "order", None))[rank]
     shard = (idx, db.subset(idx)) if world > 1 else (np.arange(db.n, dtype=np.int64), db)
     # the shard lives in pinned host memory, as a resident database would
-    shard[1].residues = torch.from_numpy(shard[1].residues).pin_memory().numpy()
+    shard[1].residues = torch.from_numpy(np.array(shard[1].residues)).pin_memory().numpy()
     eng = swb.SequenceAlignment(swb.SubstitutionMatrix.get_blosum62_matrix(), 10.0, 0.5, swb.ALIGN_LOCAL, device=local_rank)
     dev = torch.device("cuda", local_rank)
 
