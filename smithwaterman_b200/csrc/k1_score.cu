@@ -28,7 +28,7 @@
 // kept (VIMNMX3, half an instruction per cell, seeded with the current threshold so that one compare
 // tells whether anything improved).  In the (rare) steps where the running best of a lane improves,
 // only the row and the 16-column half are decided; the step's 16 packed Ho words are parked in a
-// per-thread shared-memory slot (4 STS.128) and the column is read off that slot once per pair.
+// per-thread shared-memory slot (16 STS; K2: 4 STS.128) and the column is read off that slot once per pair.
 // (K1_NOTRACK=1 builds a timing-only variant without the end cell: the per-row test, its branch and
 // the rare path together cost 10 % of the kernel, see DESIGN.md.)
 #include <cstdlib>
@@ -96,7 +96,7 @@ k1_local_kernel(const uint8_t *__restrict__ a_pk, const uint8_t *__restrict__ b_
         const int p = G_.first_pair + lane;
         const bool valid = lane < G_.n_pairs;
         const int la = valid ? la_arr[p] : 0;
-        int bestHo = open, bi = -1, bj = -1, ovf = 0;
+        int bestHo = open, bi = -1, bj = -1;
         const unsigned *ap = reinterpret_cast<const unsigned *>(a_pk + G_.a_off) + lane;  // rows 4B+1..4B+4 at ap[B*32]
         const uint4 *bp = reinterpret_cast<const uint4 *>(b_pk + G_.b_off) + lane * 2;    // pass q at bp[q*64]
         const int nblk = (G_.la_max + 1 + 3) >> 2;      // row steps run in blocks of 4
@@ -179,7 +179,6 @@ k1_local_kernel(const uint8_t *__restrict__ a_pk, const uint8_t *__restrict__ b_
                         if (ulo || uhi) {
 #pragma unroll
                             for (int k = 0; k < K1_HALF; ++k) snap[k * K1_THREADS * 2] = Ho[k];
-                            if (bestHo >= limit_ho) ovf = 1;
                             thr2 = pack2(bestHo - (first ? 0 : 1), bestHo - (first ? 0 : 1));
                         }
                     }
@@ -205,7 +204,7 @@ k1_local_kernel(const uint8_t *__restrict__ a_pk, const uint8_t *__restrict__ b_
             r.score = bestHo - open;
             r.end_i = (bestHo > open) ? bi : -1;
             r.end_j = (bestHo > open) ? bj : -1;
-            r.flags = ovf;
+            r.flags = (bestHo >= limit_ho) ? 1 : 0;      // the running best is monotone: one overflow test per pair
             res[order[p]] = r;                      // scatter to the caller's order: the host pass over the results is linear
         }
     }
@@ -292,7 +291,7 @@ k2_search_kernel(const unsigned *__restrict__ a_words, int la, const uint8_t *__
 #pragma unroll
         for (int d = 16; d >= 1; d >>= 1) pmax = max(pmax, __shfl_xor_sync(0xffffffffu, pmax, d));
         const int n_gb = nblk + pmax;                                 // global row blocks: every lane finishes its rows
-        int bestHo = open, bi = -1, bj = -1, ovf = 0;
+        int bestHo = open, bi = -1, bj = -1;
         int tb = open;                                                // best of the SUBJECT known to this lane: the exact path is
                                                                       // entered only by rows that reach it (ties included)
 
@@ -373,7 +372,6 @@ k2_search_kernel(const unsigned *__restrict__ a_words, int la, const uint8_t *__
                             snap[K1_THREADS * 2] = make_uint4(Ho[4], Ho[5], Ho[6], Ho[7]);
                             snap[K1_THREADS * 4] = make_uint4(Ho[8], Ho[9], Ho[10], Ho[11]);
                             snap[K1_THREADS * 6] = make_uint4(Ho[12], Ho[13], Ho[14], Ho[15]);
-                            if (bestHo >= limit_ho) ovf = 1;
                         }
                         tb = max(tb, bestHo);
                         thr2 = pack2(tb - 1, tb - 1);
@@ -403,9 +401,10 @@ k2_search_kernel(const unsigned *__restrict__ a_words, int la, const uint8_t *__
             bj += kk + 1;
         }
         // per-lane candidates -> the segment's head lane: score desc, row asc, column asc (SA.rs:286-294 scan order)
-        cand_sh[wib][lane][0] = bestHo; cand_sh[wib][lane][1] = bi; cand_sh[wib][lane][2] = bj; cand_sh[wib][lane][3] = ovf;
+        cand_sh[wib][lane][0] = bestHo; cand_sh[wib][lane][1] = bi; cand_sh[wib][lane][2] = bj; cand_sh[wib][lane][3] = (bestHo >= limit_ho) ? 1 : 0;
         __syncwarp();
         if (head && pair >= 0) {
+            int ovf = (bestHo >= limit_ho) ? 1 : 0;
             for (int l2 = lane + 1; l2 < seg_end; ++l2) {
                 const int ob_ = cand_sh[wib][l2][0], oi = cand_sh[wib][l2][1], oj = cand_sh[wib][l2][2];
                 ovf |= cand_sh[wib][l2][3];
