@@ -11,6 +11,7 @@
 //
 // Where the reference panics, these throw swb200::Error (code = SWB_ERR_*).  Header only; link with libswb200.so.
 #pragma once
+#include <algorithm>
 #include <cmath>
 #include <cstdint>
 #include <cstdio>
@@ -305,5 +306,56 @@ private:
     SubstitutionMatrix m_;
     swb_engine *h_ = nullptr;
 };
+
+// EMBOSS `srspair` report body (format of test/emboss_results/*.dat, res0.dat:17-45): the text from the
+// first `#====` rule to the closing `#----` rules.  Markup: `|` identical, `:` substitution score > 0, `.` other residue
+// pairs, blank for gap columns; a block that holds residues shows the numbers of its first and last residue, a block of
+// gaps only repeats the count so far.  start_a / start_b = 1-based number of the first residue of each row.
+// (Same rules as smithwaterman_b200/report.py, which is pinned to all 300 golden reports.)
+inline std::string srspair_body(const std::string &aln_a, const std::string &aln_b, float score, const SubstitutionMatrix &m,
+                                float gap_open, float gap_extend, int64_t start_a = 1, int64_t start_b = 1,
+                                const std::string &name_a = "s1", const std::string &name_b = "s2",
+                                const std::string &matrix_name = "EBLOSUM62")
+{
+    if (aln_a.size() != aln_b.size()) throw Error(SWB_ERR_ARG, "aligned strings differ in length");
+    const size_t n = aln_a.size(), nl = m.letters.size();
+    auto index_of = [&](char c) { size_t k = m.letters.find(c); if (k == std::string::npos) k = m.letters.find('X'); return k; };
+    std::string mk(n, ' ');
+    int64_t ident = 0, simil = 0, gaps = 0;
+    for (size_t k = 0; k < n; ++k) {
+        const char x = aln_a[k], y = aln_b[k];
+        if (x == '-' || y == '-') { ++gaps; continue; }
+        if (x == y) { mk[k] = '|'; ++ident; ++simil; continue; }
+        const size_t i = index_of(x), j = index_of(y);
+        const float sc = (i != std::string::npos && j != std::string::npos) ? m.scores[i * nl + j] : 0.0f;
+        if (sc > 0) { mk[k] = ':'; ++simil; } else mk[k] = '.';
+    }
+    char buf[256];
+    std::string out = "#=======================================\n#\n# Aligned_sequences: 2\n";
+    out += "# 1: " + name_a + "\n# 2: " + name_b + "\n# Matrix: " + matrix_name + "\n";
+    snprintf(buf, sizeof buf, "# Gap_penalty: %.1f\n# Extend_penalty: %.1f\n#\n# Length: %zu\n", std::fabs(gap_open), std::fabs(gap_extend), n);
+    out += buf;
+    const double d = n ? 100.0 / (double)n : 0.0;
+    snprintf(buf, sizeof buf, "# Identity:   %5lld/%zu (%4.1f%%)\n# Similarity: %5lld/%zu (%4.1f%%)\n# Gaps:       %5lld/%zu (%4.1f%%)\n",
+             (long long)ident, n, ident * d, (long long)simil, n, simil * d, (long long)gaps, n, gaps * d);
+    out += buf;
+    snprintf(buf, sizeof buf, "# Score: %.1f\n# \n#\n#=======================================\n\n", score);
+    out += buf;
+    int64_t done_a = start_a - 1, done_b = start_b - 1;
+    for (size_t lo = 0; lo < n; lo += 50) {
+        const std::string ra = aln_a.substr(lo, 50), rb = aln_b.substr(lo, 50), rm = mk.substr(lo, 50);
+        const int64_t na = (int64_t)ra.size() - std::count(ra.begin(), ra.end(), '-');
+        const int64_t nb = (int64_t)rb.size() - std::count(rb.begin(), rb.end(), '-');
+        snprintf(buf, sizeof buf, "%-13.13s %6lld %s %6lld\n", name_a.c_str(), (long long)(na ? done_a + 1 : done_a), ra.c_str(), (long long)(done_a + na));
+        out += buf;
+        snprintf(buf, sizeof buf, "%-13s %6s %s\n", "", "", rm.c_str());
+        out += buf;
+        snprintf(buf, sizeof buf, "%-13.13s %6lld %s %6lld\n\n", name_b.c_str(), (long long)(nb ? done_b + 1 : done_b), rb.c_str(), (long long)(done_b + nb));
+        out += buf;
+        done_a += na; done_b += nb;
+    }
+    out += "\n#---------------------------------------\n#---------------------------------------\n";
+    return out;
+}
 
 }  // namespace swb200

@@ -826,3 +826,34 @@ def test_srspair_reports_from_the_engine(emboss):
                 same[key] += 1
         eng.close()
     assert same["local"] == 100 and same["global"] > 0
+
+
+def test_cpp_cli_emboss_reports(emboss, tmp_path):
+    """`swbcli -emboss -local <list> <outdir>`: the compiled host mirror writes res<k>.dat files whose text equals the
+    bodies of the reference's golden water reports (ids 0..39); the needle variants equal the Python writer's output."""
+    import gzip, json, os, subprocess
+    from conftest import GOLDEN
+    from smithwaterman_b200 import report
+    with gzip.open(os.path.join(GOLDEN, "emboss_reports.json.gz")) as f:
+        bodies = {(r["kind"], r["id"]): r["body"] for r in json.loads(f.read().decode())}
+    recs = emboss[:40]
+    lines = []
+    for r in recs:
+        f1, f2 = tmp_path / ("seq%s.1.fas" % r["id"]), tmp_path / ("seq%s.2.fas" % r["id"])
+        f1.write_text(">s1\n%s\n" % r["seq1"]); f2.write_text(">s2\n%s\n" % r["seq2"])
+        lines.append("%s\t%s" % (f1, f2))
+    (tmp_path / "list.txt").write_text("\n".join(lines) + "\n")
+    m = swb.SubstitutionMatrix.get_blosum62_matrix()
+    for flag, key, pre, mode in (("-local", "local", "res", swb.ALIGN_LOCAL), ("-global", "global", "needle_res", swb.ALIGN_GLOBAL)):
+        out = tmp_path / key
+        out.mkdir()
+        subprocess.run([_swbcli(), "-emboss", flag, str(tmp_path / "list.txt"), str(out)], check=True, capture_output=True)
+        eng = swb.SequenceAlignment(m, 10.0, 0.5, mode)
+        res = eng.align_list([r["seq1"].encode() for r in recs], [r["seq2"].encode() for r in recs], mode != swb.ALIGN_LOCAL)
+        eng.close()
+        for k, (r, a) in enumerate(zip(recs, res)):
+            txt = (out / ("%s%d.dat" % (pre, k))).read_text()
+            if key == "local":
+                assert txt == bodies[("local", r["id"])], r["id"]
+            sa, sb = report.starts_of(a["idx_a"], a["idx_b"]) if key == "local" else (1, 1)
+            assert txt == report.srspair_body(a["aln_a"], a["aln_b"], a["score"], m, 10.0, 0.5, sa, sb)

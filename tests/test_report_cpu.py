@@ -52,3 +52,31 @@ def test_program_header_and_errors():
     assert "# Gaps:           1/5 (20.0%)" in txt and "# Identity:       4/5 (80.0%)" in txt
     with pytest.raises(ValueError):
         report.srspair_body("AC", "A", 1.0, m, 10.0, 0.5)
+
+
+def test_cpp_mirror_srspair_equals_all_golden_reports(emboss, reports, tmp_path):
+    """include/swb200.hpp::srspair_body (the compiled host mirror) prints the same 300 bodies."""
+    import subprocess
+    from smithwaterman_b200 import _lib
+    _lib.build()
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    exe = str(tmp_path / "srspair")
+    subprocess.check_call(["g++", "-O1", "-std=c++17", "-I", os.path.join(root, "include"), os.path.join(root, "tests", "cpp", "srspair.cpp"),
+                           "-L", os.path.dirname(_lib.SO_PATH), "-lswb200", "-Wl,-rpath," + os.path.dirname(_lib.SO_PATH), "-o", exe])
+    by_id = {p["id"]: p for p in emboss}
+    rows = []
+    for r in reports:
+        g = by_id[r["id"]][r["kind"]]
+        sa, sb = (r["first1"], r["first2"]) if r["kind"] == "local" else (1, 1)
+        rows.append("\t".join([r["kind"], str(r["id"]), str(sa), str(sb), repr(g["score"]), g["s1"], g["s2"]]))
+    (tmp_path / "cases.tsv").write_text("\n".join(rows) + "\n")
+    out = subprocess.run([exe, str(tmp_path / "cases.tsv")], capture_output=True, text=True)
+    assert out.returncode == 0, out.stderr
+    got = {}
+    for chunk in out.stdout.split("@@ ")[1:]:
+        head, body = chunk.split("\n", 1)
+        kind, k = head.split()
+        got[(kind, int(k))] = body
+    assert len(got) == 300
+    for r in reports:
+        assert got[(r["kind"], r["id"])] == r["body"], "%s %d" % (r["kind"], r["id"])

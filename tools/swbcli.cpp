@@ -105,6 +105,36 @@ int main(int argc, char **argv)
             for (size_t k = 1; k < args.size(); ++k) std::cout << f32_display(strtof(args[k].c_str(), nullptr)) << "\n";
             return 0;
         }
+        // EMBOSS srspair reports:  swbcli -emboss -local|-glocal|-global <file_list> <outdir>
+        // writes res<k>.dat / needle_glocal_res<k>.dat / needle_res<k>.dat, diffable against test/emboss_results.
+        if (args[0] == "-emboss") {
+            if (args.size() != 4) throw Error(SWB_ERR_ARG, "usage: swbcli -emboss -local|-glocal|-global <file_list> <outdir>");
+            const int type = args[1] == "-local" ? ALIGN_LOCAL : args[1] == "-glocal" ? ALIGN_GLOCAL : args[1] == "-global" ? ALIGN_GLOBAL : -1;
+            if (type < 0) throw Error(SWB_ERR_ARG, "unknown alignment type " + args[1]);
+            const char *pre = type == ALIGN_LOCAL ? "res" : type == ALIGN_GLOCAL ? "needle_glocal_res" : "needle_res";
+            const SubstitutionMatrix bl = SubstitutionMatrix::get_blosum62_matrix();
+            SequenceAlignment sw(bl, 10.0f, 0.5f, type);
+            std::vector<std::vector<SeqData>> keep;
+            for (const auto &fp : read_list(args[2])) { keep.push_back(SeqData::load_fasta(fp.first, false)); keep.push_back(SeqData::load_fasta(fp.second, false)); }
+            std::vector<const SeqData *> sa, sb;
+            for (size_t k = 0; k + 1 < keep.size(); k += 2) {
+                if (keep[k].empty() || keep[k + 1].empty()) throw Error(SWB_ERR_ARG, "empty FASTA file in the list");
+                sa.push_back(&keep[k][0]); sb.push_back(&keep[k + 1][0]);
+            }
+            std::vector<Alignment> res = sw.align_list(sa, sb, type != ALIGN_LOCAL);
+            for (size_t k = 0; k < res.size(); ++k) {
+                int64_t s1 = 1, s2 = 1;
+                if (type == ALIGN_LOCAL) {
+                    for (int64_t v : res[k].idx_a) if (v >= 0) { s1 = v + 1; break; }
+                    for (int64_t v : res[k].idx_b) if (v >= 0) { s2 = v + 1; break; }
+                }
+                std::ofstream fo(args[3] + "/" + pre + std::to_string(k) + ".dat");
+                if (!fo) throw Error(SWB_ERR_ARG, "can not write into " + args[3]);
+                fo << srspair_body(res[k].aln_a, res[k].aln_b, res[k].score, bl, 10.0f, 0.5f, s1, s2);
+            }
+            std::cout << "wrote " << res.size() << " reports to " << args[3] << "\n";
+            return 0;
+        }
         Options opp(args);
         SequenceAlignment sw(SubstitutionMatrix::get_blosum62_matrix(), 10.0f, 0.5f, opp.alignment_type);
         if (opp.clustering) {
