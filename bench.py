@@ -147,6 +147,16 @@ def other_configs(swb, dev):
         t0 = time.perf_counter(); r = eng.align_list(sa, sb, True); dt = time.perf_counter() - t0
         cells = float(sum(len(x) * len(y) for x, y in zip(sa, sb)))
         out[tag] = {"gcups": cells / dt / 1e9, "seconds": dt, "device_ms": eng.stats()["kernel_ms"], "score0": r[0]["score"]}
+        if n == 1:                                             # the same pair through checkpointed recompute (256 MB of direction bytes)
+            os.environ["SWB_CKPT_BYTES"] = str(256 << 20)
+            try:
+                t0 = time.perf_counter(); c = eng.align_list(sa, sb, True); dt = time.perf_counter() - t0
+                st = eng.stats()
+            finally:
+                os.environ.pop("SWB_CKPT_BYTES", None)
+            out[tag.replace("full traceback", "checkpointed traceback, 256 MB budget")] = {
+                "gcups": cells / dt / 1e9, "seconds": dt, "device_ms": st["kernel_ms"], "ckpt_pairs": st["ckpt_pairs"],
+                "identical_to_direct": bool(c[0]["aln_a"] == r[0]["aln_a"] and c[0]["aln_b"] == r[0]["aln_b"] and c[0]["score"] == r[0]["score"])}
         eng.close()
     return out
 

@@ -3,6 +3,7 @@
 import os, sys, time
 import numpy as np
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
 import smithwaterman_b200 as swb
 from ckpt_probe import mutate, NT
 rng = np.random.default_rng(20260)
