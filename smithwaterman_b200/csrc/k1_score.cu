@@ -36,6 +36,12 @@
 #include "swb_internal.h"
 #include "k1_common.cuh"
 
+// K1_BLK_UNROLL=2 unrolls two 4-row blocks (8 rows) per loop trip: compiles to 119 registers without spills and about
+// half the back-edge register moves per row; not measured yet (tools/ab_k1.sh with -DK1_BLK_UNROLL=2).
+#ifndef K1_BLK_UNROLL
+#define K1_BLK_UNROLL 1
+#endif
+constexpr int kBlkUnroll = K1_BLK_UNROLL;
 #ifndef K1_NOTRACK
 #define K1_NOTRACK 0
 #endif
@@ -127,7 +133,7 @@ k1_local_kernel(const uint8_t *__restrict__ a_pk, const uint8_t *__restrict__ b_
             unsigned word_next = ap[0];
             unsigned c1 = open2, c2 = open2, c3 = open2; // boundary words of rows i0-3..i0-1 waiting for their 4th
 
-#pragma unroll 1
+#pragma unroll kBlkUnroll
             for (int blk = 0; blk < nblk; ++blk) {
                 const int i0 = blk * 4;                           // rows i0+1 .. i0+4 (low lane)
                 const unsigned word = word_next;
