@@ -40,11 +40,13 @@ def _oracle_score_fn(engine, query, db):
     return (sc / 2.0).astype(np.float32), ei, ej
 
 
-def _worker(rank, world, port, out):
+def _worker(rank, world, port, out, db_path=None):
     os.environ["MASTER_ADDR"] = "127.0.0.1"
     os.environ["MASTER_PORT"] = str(port)
     dist.init_process_group("gloo", rank=rank, world_size=world)
     query, db = _make_db()
+    if db_path:                               # every rank maps the same packed database file (Database.save / load)
+        db = S.Database.load(db_path)
     hits = S.search(None, query, db, topk=25, traceback=False, rank=rank, world_size=world, score_fn=_oracle_score_fn)
     out[rank] = [(h["idx"], h["score"], h["end_q"], h["end_t"]) for h in hits]
     dist.destroy_process_group()
@@ -75,6 +77,22 @@ def test_world2_gloo_matches_single_process():
     scores = [r[1] for r in ref]
     assert any(scores[i] == scores[i + 1] and ref[i][0] < ref[i + 1][0] for i in range(len(ref) - 1))
     assert scores == sorted(scores, reverse=True)
+
+
+def test_world2_gloo_from_packed_database_file(tmp_path):
+    """The same world-2 run with both ranks reading the memory-mapped database file and its stored shard order."""
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        port = s.getsockname()[1]
+    query, db = _make_db()
+    path = str(tmp_path / "db.swdb")
+    db.save(path)
+    mgr = mp.Manager()
+    out = mgr.dict()
+    mp.spawn(_worker, args=(2, port, out, path), nprocs=2, join=True)
+    single = S.search(None, query, db, topk=25, traceback=False, score_fn=_oracle_score_fn)
+    ref = [(h["idx"], h["score"], h["end_q"], h["end_t"]) for h in single]
+    assert out[0] == ref and out[1] == ref
 
 
 def test_packed_database_file_round_trip(tmp_path):
