@@ -332,7 +332,10 @@ void kw_plan(const swb_engine *e, KWPair *pairs, int n_pairs, bool with_dirs, KW
         int big = 0;
         for (int k = 1; k < n_pairs; ++k)
             if ((int64_t)pairs[k].la * pairs[k].lb > (int64_t)pairs[big].la * pairs[big].lb) big = k;
-        const int strips = (pairs[big].lb + sw - 1) / sw, cap = std::max(1, std::min(capacity / n_pairs, strips));
+        const int strips = (pairs[big].lb + sw - 1) / sw;
+        int cap = std::max(1, std::min(capacity / n_pairs, strips));
+        // the boundary ring holds T + 1 columns of 16 B per row: keep it under 32 GB for very long pairs (la > 0.8 M rows)
+        cap = (int)std::max<int64_t>(1, std::min<int64_t>(cap, (32ll << 30) / (16ll * (pairs[big].la + 2)) - 1));
         int64_t best_cost = -1;
         for (int rounds = 1; rounds <= strips; ++rounds) {
             const int t = (strips + rounds - 1) / rounds;
