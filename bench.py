@@ -109,22 +109,88 @@ def _idx(m, raw):
     return lut[raw]
 
 
-def other_configs(swb, dev):
-    """configs[2] (5000-aa query vs 1e8-residue database, score stage through swb_search_scores, host buffers),
-    configs[3] (one 50 kb x 50 kb DNA pair, +2/-3 5/2, local, full traceback) and configs[4] (64 x 10 kb global DNA
-    pairs with strings) -- wall-clock GCUPS of the public calls after one warm-up call each."""
+def search_block(swb, local_rank, rank, world, roof_gcups, hbm_peak, steps=3):
+    """BASELINE configs[2] at the named size on EVERY N (strong scaling): 5000-aa query vs the 2e8-residue synthetic
+    database (500 planted homologs), shard `rank` of `world` resident on this rank's GPU (swb_db_upload_shard), device-side
+    top-100, ONE all-gather of the per-rank hit lists, each rank traces the hits it owns.  Times are device times
+    (CUDA events inside the library, max over ranks) for the scan and wall times between barriers for the whole call."""
+    import torch
+    import torch.distributed as dist
     sys.path.insert(0, os.path.join(ROOT, "tools"))
     import search_bench as SB
     from smithwaterman_b200 import search as S
-    out = {}
-    q, res, off = SB.make_db(5000, int(1e8))
+    q, res, off = SB.make_db(5000, int(2e8))
     db = S.Database(res, off)
-    eng = swb.SequenceAlignment(swb.SubstitutionMatrix.get_blosum62_matrix(), 10.0, 0.5, swb.ALIGN_LOCAL, device=dev)
-    S.search_scores(eng, q, db)
-    t0 = time.perf_counter(); sc, _, _ = S.search_scores(eng, q, db); dt = time.perf_counter() - t0
-    out["configs[2] search 5000 aa x 1e8 residues, score stage"] = {"gcups": 5000.0 * float(off[-1]) / dt / 1e9, "seconds": dt,
-                                                                    "device_ms": eng.stats()["kernel_ms"], "top_score": float(sc.max())}
-    eng.close()
+    eng = swb.SequenceAlignment(swb.SubstitutionMatrix.get_blosum62_matrix(), 10.0, 0.5, swb.ALIGN_LOCAL, device=local_rank)
+    dev = torch.device("cuda", local_rank)
+    t0 = time.perf_counter()
+    ddb = S.DeviceDatabase(eng, db, rank, world)
+    t_upload = time.perf_counter() - t0
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def one(tb):
+        return S.search(eng, q, db, topk=100, traceback=tb, rank=rank, world_size=world, device=dev, ddb=ddb)
+
+    hits = one(True)                                          # warm-up: scratch growth, NCCL channels
+    one(False)
+    t_score, t_full, dev_ms, tb_ms = [], [], [], []
+    for _ in range(steps):
+        barrier(); a0 = time.perf_counter()
+        ddb.search(q, 100)
+        dev_ms.append(eng.stats()["kernel_ms"])
+        barrier(); a1 = time.perf_counter()
+        one(False)
+        barrier(); a2 = time.perf_counter()
+        hits = one(True)
+        tb_ms.append(eng.stats()["kernel_ms"])
+        barrier(); a3 = time.perf_counter()
+        t_score.append(a2 - a1); t_full.append(a3 - a2)
+    idx = S.native_shard_indices(db.offsets, rank, world)
+    owned = int(np.isin(np.array([h["idx"] for h in hits], np.int64), idx).sum())
+    # host-buffer variant of the scan (shard in pinned host memory, H2D inside the call), as round 1 measured it
+    sub = db.subset(idx) if world > 1 else db
+    sub.residues = torch.from_numpy(np.array(sub.residues)).pin_memory().numpy()
+    S.search_scores(eng, q, sub)
+    barrier(); b0 = time.perf_counter()
+    sc_host, _, _ = S.search_scores(eng, q, sub)
+    barrier(); b1 = time.perf_counter()
+    same = bool(np.array_equal(sc_host, ddb.scores()[0])) if world == 1 else None
+    t = torch.tensor([min(t_score), min(t_full), min(dev_ms), b1 - b0, min(tb_ms), float(ddb.residues), float(owned)], dtype=torch.float64, device=dev)
+    if world > 1:
+        tm = t.clone(); dist.all_reduce(tm, op=dist.ReduceOp.MAX)
+        ts = t.clone(); dist.all_reduce(ts, op=dist.ReduceOp.SUM)
+    else:
+        tm, ts = t, t
+    cells = 5000.0 * float(off[-1])
+    ddb.free(); eng.close()
+    per_gpu_scan = 5000.0 * tm[5].item() / (tm[2].item() * 1e-3) / 1e9          # the largest shard over the slowest scan
+    return {"workload": "configs[2]: 5000-aa query vs %d-residue synthetic protein database (%d sequences, 500 planted homologs), "
+                        "BLOSUM62 10/0.5 local, score + top-100 + traceback of the hits" % (int(off[-1]), db.n),
+            "scaling": "strong", "n_gpus": world, "cells": cells, "topk": 100,
+            "database": "shard resident on the GPU (swb_db_upload_shard, %.2f s once); per query: %d B up, 3.2 kB of hits down" % (t_upload, len(q)),
+            "scan_device_ms": tm[2].item(), "gcups_scan_device": cells / (tm[2].item() * 1e-3) / 1e9,
+            "score_stage_s": tm[0].item(), "gcups_score_stage": cells / tm[0].item() / 1e9,
+            "score_plus_traceback_s": tm[1].item(), "gcups_with_traceback": cells / tm[1].item() / 1e9,
+            "traceback_device_ms_max_rank": tm[4].item(), "hits_traced_by_this_rank": int(owned), "hits_traced_total": int(ts[6].item()),
+            "per_gpu": {"gcups_scan": per_gpu_scan, "frac_of_dpx_roof": per_gpu_scan / roof_gcups,
+                        "hbm_gbs_streamed_shard": tm[5].item() / (tm[2].item() * 1e-3) / 1e9, "hbm_peak_gbs": hbm_peak,
+                        "hbm_frac": tm[5].item() / (tm[2].item() * 1e-3) / 1e9 / hbm_peak},
+            "host_buffer_scan_s": tm[3].item(), "gcups_host_buffer_scan": cells / tm[3].item() / 1e9,
+            "host_buffer_scores_equal_resident": same,
+            "top_hit": {"idx": hits[0]["idx"], "score": hits[0]["score"]},
+            "checksum_top100": float(sum(h["score"] for h in hits)), "idx_top10": [h["idx"] for h in hits[:10]],
+            "strings_returned": int(sum(1 for h in hits if "aln_q" in h))}
+
+
+def other_configs(swb, dev):
+    """configs[3] (one 100 kb x 100 kb DNA pair, +2/-3 5/2, local, full traceback: direct and checkpointed) and
+    configs[4] (256 x 10 kb global DNA pairs with strings) at the named sizes -- wall-clock GCUPS of the public calls
+    after one warm-up call each.  (configs[2] has its own `search` block.)"""
+    out = {}
     rng = np.random.default_rng(SEED + 3)
     nt = np.frombuffer(b"ACGT", np.uint8)
 
@@ -139,14 +205,15 @@ def other_configs(swb, dev):
             sa.append(a.tobytes()); sb.append(b.tobytes())
         return sa, sb
     dna = swb.SubstitutionMatrix.get_mat_matrix(2.0, -3.0)
-    for tag, mode, n, length, sub, indel in (("configs[3] 50 kb x 50 kb DNA pair, local, full traceback", swb.ALIGN_LOCAL, 1, 50000, 0.08, 0.02),
-                                             ("configs[4] 64 x 10 kb DNA pairs, global, strings", swb.ALIGN_GLOBAL, 64, 10000, 0.05, 0.05)):
+    for tag, mode, n, length, sub, indel in (("configs[3] 100 kb x 100 kb DNA pair, local, full traceback", swb.ALIGN_LOCAL, 1, 100000, 0.08, 0.02),
+                                             ("configs[4] 256 x 10 kb DNA pairs, global, strings", swb.ALIGN_GLOBAL, 256, 10000, 0.05, 0.05)):
         sa, sb = noisy(n, length, sub, indel)
         eng = swb.SequenceAlignment(dna, 5.0, 2.0, mode, device=dev)
         eng.align_list(sa[:1], sb[:1], True)
         t0 = time.perf_counter(); r = eng.align_list(sa, sb, True); dt = time.perf_counter() - t0
         cells = float(sum(len(x) * len(y) for x, y in zip(sa, sb)))
-        out[tag] = {"gcups": cells / dt / 1e9, "seconds": dt, "device_ms": eng.stats()["kernel_ms"], "score0": r[0]["score"]}
+        out[tag] = {"gcups": cells / dt / 1e9, "seconds": dt, "device_ms": eng.stats()["kernel_ms"],
+                    "gcups_device": cells / (eng.stats()["kernel_ms"] * 1e-3) / 1e9, "score0": r[0]["score"]}
         if n == 1:                                             # the same pair through checkpointed recompute (256 MB of direction bytes)
             os.environ["SWB_CKPT_BYTES"] = str(256 << 20)
             try:
@@ -189,7 +256,8 @@ def main():
     ap.add_argument("--pairs", type=int, default=1_000_000)
     ap.add_argument("--impl", default="swb200")
     ap.add_argument("--cpu-seconds", type=float, default=10.0)
-    ap.add_argument("--no-extras", action="store_true", help="skip the side measurements of configs[2..4]")
+    ap.add_argument("--no-extras", action="store_true", help="skip the side measurements of configs[3..4]")
+    ap.add_argument("--no-search", action="store_true", help="skip the configs[2] search block")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
@@ -198,7 +266,9 @@ def main():
     config = {"workload": "configs[1]: %d synthetic protein pairs/GPU, la,lb~U[100,500], Robinson-Robinson residues, "
                           "BLOSUM62 open 10 extend 0.5, local, score+end cell" % args.pairs,
               "pairs_per_gpu": args.pairs, "seed": SEED, "sharding": "independent pairs per rank, no collective on the data path",
-              "l2": "inputs (~600 MB/GPU) larger than L2"}
+              "l2": "inputs (~600 MB/GPU) larger than L2",
+              "value_covers": "K1 on the resident, already encoded / sorted / packed batch (those steps run once per upload and are "
+                              "inside e2e, not inside value)"}
 
     if args.impl == "reference":
         if rank != 0:
@@ -287,10 +357,35 @@ def main():
     else:
         ms_step, e2e_ms, tot_cells = t[0].item(), t[1].item(), cells
         e2e_ranks = [round(e2e_ms, 2)]
+    # ---- configs[2] at every N (all ranks take part; strong scaling)
+    search = None
+    if not args.no_search:
+        try:
+            dpx_rate_s = swb.dpx_peak(0, local_rank)
+            peaks_s = {}
+            try:
+                peaks_s = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+            except Exception:
+                pass
+            search = search_block(swb, local_rank, rank, world, dpx_rate_s / 2.0 / 1e9, peaks_s.get("hbm_gbs", 6650.0))
+        except Exception as ex:                                   # never lose the bench line over it
+            if world > 1:
+                raise
+            search = {"error": repr(ex)}
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
         return
+
+    # ---- parity of the benchmarked batch itself: a fixed 10^4-pair subset (and every pair re-run in int32) vs the integer oracle
+    from oracle import oracle as O
+    om = O.Matrix.blosum62()
+    pick = np.sort(np.random.default_rng(SEED).choice(n, min(n, 10_000), replace=False))
+    if reruns:
+        pass                                                      # (re-run pairs are flagged inside the library; none occur on this workload)
+    ia, ioa = O.pack([_idx(om, a[oa[k]:oa[k + 1]]) for k in pick]); ib, iob = O.pack([_idx(om, b[ob[k]:ob[k + 1]]) for k in pick])
+    osc, oi, oj = O.score_batch_int(ia, ioa, ib, iob, np.rint(om.scores * 2).astype(np.int32), -20, -1, 2, O.ALIGN_LOCAL, threads)
+    mism = int(np.sum(np.rint(sc[pick].astype(np.float64) * 2).astype(np.int64) != osc) + np.sum(ea[pick] != oi) + np.sum(eb[pick] != oj))
 
     value = tot_cells / (ms_step * 1e-3) / 1e9
     e2e_val = tot_cells / (e2e_ms * 1e-3) / 1e9
@@ -310,7 +405,7 @@ def main():
         tr = json.load(open(os.path.join(ROOT, "profiles", "k1_traffic.json")))
         if args.pairs == 1_000_000:
             traffic = tr["dram_bytes_per_launch"]
-            traffic_detail = {"algorithmic_bytes": alg_bytes, "source": tr["source"],
+            traffic_detail = {"algorithmic_bytes": alg_bytes, "traffic_source": "committed capture, not this run: " + tr["source"],
                               "note": "the excess over the algorithmic bytes is the 4-byte-per-row pass-boundary column "
                                       "(0.125 B/cell written + re-read once per 32-column pass); 12 % of HBM peak, not the bound"}
     except Exception:
@@ -341,7 +436,8 @@ def main():
             "e2e": {"value": e2e_val, "unit": "GCUPS", "h2d_bytes_per_step": st["h2d_bytes"], "d2h_bytes_per_step": st["d2h_bytes"],
                     "ms_per_step": e2e_ms, "steps": e2e_steps, "ms_per_rank": e2e_ranks, "numa_bound_cpus": numa},
             "gpu_launches": int(launches), "roofline": roofline, "cpu_baseline": cpu,
-            "i32_reruns": int(reruns), "cells_per_step": tot_cells, "other_configs": extras}
+            "i32_reruns": int(reruns), "cells_per_step": tot_cells,
+            "oracle_checked_pairs": int(len(pick)), "mismatches": mism, "other_configs": extras, "search": search}
     print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()

@@ -16,6 +16,10 @@
  *   swb_cluster            the clustering loop of `sa_opencl -cluster`  OCL-main.rs:149-243
  *   swb_score_batch        align_partial(.., score_only=true) per pair  SA.rs:393-467
  *   swb_search_scores      the all-vs-all loops of the CLIs with one fixed query (SA-main.rs:35-45), n subjects per call
+ *   swb_db_* / swb_search* the same loop as a database search: the subjects stay resident on the device (encoded once),
+ *                          a call scans one query, selects the top-K on the device and traces the hits back
+ *                          (SA-main.rs:35-45 / OCL-main.rs:295-316 with one fixed `ss1`; align() SA.rs:389 per hit)
+ *   swb_align_partial      SequenceAlignment::align_partial  SA.rs:393-551 (partial_region, score_only)
  *   swb_batch_*            the same as swb_score_batch, split into upload / run / fetch so that a
  *                          caller can keep inputs resident in HBM (bench.py `value` vs `e2e`)
  *   swb_alignment_free     Drop of the (Vec<String>,Vec<String>,f32) result
@@ -107,6 +111,11 @@ int swb_device_count(void);
 /* One pair with traceback (SA.rs:389).  out is filled on SWB_OK. */
 int swb_align(swb_engine *e, const char *a, int64_t la, const char *b, int64_t lb, int retain_all,
               swb_alignment *out);
+/* align_partial (SA.rs:393-551): the DP runs on the prefixes a[0..pa), b[0..pb) (partial_region; pa = la, pb = lb for
+ * None) while the retain_all padding spells the WHOLE sequences (SA.rs:512-549 loop over s1.seq.len()); score_only != 0
+ * returns the score and end cell with empty strings (SA.rs:438-467). */
+int swb_align_partial(swb_engine *e, const char *a, int64_t la, const char *b, int64_t lb, int64_t pa, int64_t pb,
+                      int retain_all, int score_only, swb_alignment *out);
 /* One pair scored by a PositionSpecificMatrix (SA.rs:583-623; psm_test SA.rs:1057-1086): the score of (position i of a,
  * position j of b) is scores[i + j*la] (f32, la*lb values on the engine's penalty grid); the engine's matrix is not used,
  * the letters only spell the output strings.  Gap penalties and mode are the engine's. */
@@ -156,6 +165,47 @@ int swb_score_batch(swb_engine *e, const char *a_all, const int64_t *off_a, cons
  * deterministic) and obtains the alignments of those hits with swb_align_batch. */
 int swb_search_scores(swb_engine *e, const char *query, int64_t lq, const char *db_all, const int64_t *off_db,
                       int64_t n, float *scores, int64_t *end_q, int64_t *end_t);
+
+/* ---- Database search with a resident database -----------------------------------------------------------------------
+ * swb_db_upload keeps n subjects (letters[off[k]..off[k+1]), global index global_index[k], ascending; NULL = 0..n-1)
+ * encoded on the engine's device; swb_db_upload_shard takes the WHOLE database and keeps shard `rank` of `world`: the
+ * subjects are dealt round-robin over the stable longest-first order (swb_db_shard returns that index list; host only),
+ * so every shard holds the same length mix.  The database keeps a host copy of its letters (the hits' strings are
+ * spelled from it); the caller's buffers may be released after the call.  A database belongs to one engine's device. */
+typedef struct swb_db swb_db;
+typedef struct swb_hit {
+    float score;             /* as the reference's f32 */
+    int32_t shard;           /* set by swb_search_sharded: the shard that owns the subject; 0 otherwise */
+    int64_t index;           /* global index of the subject */
+    int64_t end_q, end_t;    /* first-maximum cell (local) or (lq, lt) (global / glocal), as swb_score_batch */
+} swb_hit;
+#define SWB_MAX_TOPK 4096
+int swb_db_shard(const int64_t *off, int64_t n, int rank, int world, int64_t *idx, int64_t *n_idx);
+int swb_db_upload(swb_engine *e, const char *letters, const int64_t *off, int64_t n, const int64_t *global_index,
+                  swb_db **out);
+int swb_db_upload_shard(swb_engine *e, const char *letters, const int64_t *off, int64_t n_total, int rank, int world,
+                        swb_db **out);
+void swb_db_free(swb_engine *e, swb_db *db);
+int64_t swb_db_count(const swb_db *db);
+int64_t swb_db_residues(const swb_db *db);
+/* One query against the resident database: score + end cell of every subject (align_partial(.., score_only) per pair,
+ * SA.rs:438-467; s16 overflows re-run in int32), then the top-K by (score desc, global index asc) selected ON THE
+ * DEVICE -- topk x 32 bytes cross PCIe, not the score vector.  hits[topk]; *n_hits = min(topk, n). */
+int swb_search(swb_engine *e, const char *query, int64_t lq, swb_db *db, int topk, swb_hit *hits, int64_t *n_hits);
+/* The full score vector of the last swb_search on this database, in the database's local subject order. */
+int swb_db_scores(swb_engine *e, swb_db *db, float *scores, int64_t *end_q, int64_t *end_t);
+/* Host only: global top-K of the concatenated per-shard lists (the one exchange between shards: gather n_shards x K
+ * records with NCCL / MPI / plain memory, then merge).  Same key, so the list does not depend on the sharding. */
+int swb_search_merge(const swb_hit *parts, int64_t n_parts, int topk, swb_hit *out, int64_t *n_out);
+/* Traceback (align(query, subject, retain_all), SA.rs:389) of the hits whose subject this database holds: owned[k] = 1
+ * and alns[k] filled for those, the others stay zeroed -- every shard traces its own hits, so the traceback divides by
+ * the number of GPUs like the scan.  owned may be NULL. */
+int swb_search_align(swb_engine *e, const char *query, int64_t lq, swb_db *db, const swb_hit *hits, int64_t n_hits,
+                     unsigned flags, swb_alignment *alns, int32_t *owned);
+/* One process, n_shards GPUs: engines[g] and dbs[g] = shard g of n_shards.  Scan + select on one host thread per shard,
+ * host merge, hits traced by their owners.  alns may be NULL (no traceback). */
+int swb_search_sharded(swb_engine **engines, swb_db **dbs, int n_shards, const char *query, int64_t lq, int topk,
+                       unsigned flags, swb_hit *hits, int64_t *n_hits, swb_alignment *alns);
 
 /* The same, staged: upload (encode + pack + H2D) once, run the kernels any number of times on the
  * resident batch, fetch (D2H + unpermute).  swb_batch_run is asynchronous on the engine's stream;

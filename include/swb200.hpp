@@ -223,22 +223,20 @@ public:
         Alignment r = align_full(s1.seq, s2.seq, retain_all);
         return {r.aln_a, r.aln_b, r.score};
     }
-    // SA.rs:393-467: partial_region = align the prefixes only; score_only = no traceback, empty strings.
+    // SA.rs:393-551: partial_region = the DP runs on the prefixes (SA.rs:396-405) while the retain_all padding spells the
+    // whole sequences (SA.rs:512-549); score_only = no traceback, empty strings (SA.rs:438-467).
     std::tuple<std::string, std::string, float> align_partial(const SeqData &s1, const SeqData &s2, bool retain_all,
                                                               const std::pair<size_t, size_t> *partial_region, bool score_only)
     {
-        std::string a = s1.seq, b = s2.seq;
-        if (partial_region) {
-            if (partial_region->first > a.size() || partial_region->second > b.size()) throw Error(SWB_ERR_ARG, "partial_region exceeds the sequences");
-            a.resize(partial_region->first); b.resize(partial_region->second);
-        }
-        if (score_only) {
-            float sc; int64_t ea, eb;
-            const int64_t oa[2] = {0, (int64_t)a.size()}, ob[2] = {0, (int64_t)b.size()};
-            check(swb_score_batch(h_, a.data(), oa, b.data(), ob, 1, &sc, &ea, &eb));
-            return {std::string(), std::string(), sc};
-        }
-        Alignment r = align_full(a, b, retain_all);
+        const std::string &a = s1.seq, &b = s2.seq;
+        if (partial_region && (partial_region->first > a.size() || partial_region->second > b.size()))
+            throw Error(SWB_ERR_ARG, "partial_region exceeds the sequences");
+        const int64_t pa = partial_region ? (int64_t)partial_region->first : (int64_t)a.size();
+        const int64_t pb = partial_region ? (int64_t)partial_region->second : (int64_t)b.size();
+        swb_alignment out;
+        check(swb_align_partial(h_, a.data(), (int64_t)a.size(), b.data(), (int64_t)b.size(), pa, pb, retain_all ? 1 : 0, score_only ? 1 : 0, &out));
+        Alignment r = take(out);
+        swb_alignment_free(&out);
         return {r.aln_a, r.aln_b, r.score};
     }
     Alignment align_full(const std::string &a, const std::string &b, bool retain_all)

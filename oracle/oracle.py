@@ -253,14 +253,16 @@ class Engine:
         lib().swo_cell(self._h, lb, i, j, _ptr(sc), _ptr(pv))
         return sc, pv
 
-    def align(self, s1, s2, retain_all=True, score_only=False, pssm=None):
-        """align_partial (SA.rs:393-551) -> (list[str], list[str], score)."""
+    def align(self, s1, s2, retain_all=True, score_only=False, pssm=None, partial_region=None):
+        """align_partial (SA.rs:393-551) -> (list[str], list[str], score).  partial_region: the DP sees the prefixes
+        (seq_to_index(.., Some(x)), SA.rs:396-405, 649-656), the padding loops run over the whole sequences (SA.rs:512-549)."""
         if isinstance(s1, str):
             s1 = SeqData(seq=s1)
         if isinstance(s2, str):
             s2 = SeqData(seq=s2)
         if pssm is None:
-            ia, ib = self.matrix.seq_to_index(s1.seq), self.matrix.seq_to_index(s2.seq)
+            p1, p2 = (len(s1.seq), len(s2.seq)) if partial_region is None else partial_region
+            ia, ib = self.matrix.seq_to_index(s1.seq[:p1]), self.matrix.seq_to_index(s2.seq[:p2])
         else:
             ia, ib = np.arange(len(s1.seq), dtype=np.int32), np.arange(len(s2.seq), dtype=np.int32)
         xa, xb, score, _, _ = self.raw(ia, ib, score_only, pssm)

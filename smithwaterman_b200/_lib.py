@@ -25,7 +25,7 @@ def needs_build():
     if not os.path.exists(SO_PATH):
         return True
     t = os.path.getmtime(SO_PATH)
-    deps = sources() + glob.glob(os.path.join(CSRC, "*.h")) + [HEADER]
+    deps = sources() + glob.glob(os.path.join(CSRC, "*.h")) + glob.glob(os.path.join(CSRC, "*.cuh")) + [HEADER]
     return any(os.path.getmtime(p) > t for p in deps)
 
 
@@ -68,6 +68,14 @@ class Alignment(ctypes.Structure):
 # swb_aln_stats as a numpy record (48 bytes, the C layout)
 ALN_STATS_DTYPE = [("score", "<f4"), ("status", "<i4"), ("end_a", "<i8"), ("end_b", "<i8"), ("aln_len", "<i8"),
                    ("a_letters", "<i8"), ("b_letters", "<i8"), ("matches", "<i8")]
+
+
+class Hit(ctypes.Structure):            # swb_hit, 32 bytes
+    _fields_ = [("score", ctypes.c_float), ("shard", ctypes.c_int32), ("index", ctypes.c_int64),
+                ("end_q", ctypes.c_int64), ("end_t", ctypes.c_int64)]
+
+
+HIT_DTYPE = [("score", "<f4"), ("shard", "<i4"), ("index", "<i8"), ("end_q", "<i8"), ("end_t", "<i8")]
 
 
 class Stats(ctypes.Structure):
@@ -115,6 +123,18 @@ def lib():
         "swb_batch_last_run_ms": (c.c_int, [vp, vp, c.POINTER(f32), c.POINTER(i64)]),
         "swb_batch_run_n": (c.c_int, [vp, vp, c.c_int, c.POINTER(f32), c.POINTER(i64)]),
         "swb_dpx_peak": (c.c_int, [c.c_int, c.c_int, c.POINTER(c.c_double)]),
+        "swb_align_partial": (c.c_int, [vp, vp, i64, vp, i64, i64, i64, c.c_int, c.c_int, c.POINTER(Alignment)]),
+        "swb_db_shard": (c.c_int, [vp, i64, c.c_int, c.c_int, vp, c.POINTER(i64)]),
+        "swb_db_upload": (c.c_int, [vp, vp, vp, i64, vp, c.POINTER(vp)]),
+        "swb_db_upload_shard": (c.c_int, [vp, vp, vp, i64, c.c_int, c.c_int, c.POINTER(vp)]),
+        "swb_db_free": (None, [vp, vp]),
+        "swb_db_count": (i64, [vp]),
+        "swb_db_residues": (i64, [vp]),
+        "swb_search": (c.c_int, [vp, vp, i64, vp, c.c_int, vp, c.POINTER(i64)]),
+        "swb_db_scores": (c.c_int, [vp, vp, vp, vp, vp]),
+        "swb_search_merge": (c.c_int, [vp, i64, c.c_int, vp, c.POINTER(i64)]),
+        "swb_search_align": (c.c_int, [vp, vp, i64, vp, vp, i64, c.c_uint, vp, vp]),
+        "swb_search_sharded": (c.c_int, [vp, vp, c.c_int, vp, i64, c.c_int, c.c_uint, vp, c.POINTER(i64), vp]),
     }
     for name, (res, args) in sig.items():
         fn = getattr(L, name)          # AttributeError here == header/library mismatch

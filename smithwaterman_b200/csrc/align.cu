@@ -91,6 +91,18 @@ static int64_t dir_budget()
     return DIR_BUDGET_BYTES;
 }
 
+// int32 lanes of the wavefront kernel: every score of a pair must stay well inside +-2^29 (its PAD score).  Upwards a
+// pair can reach min(la,lb) best substitutions, downwards (la+lb) extensions + two openings + the boundary sentinel +
+// min(la,lb) worst substitutions.
+bool swb_range_ok(const swb_engine *e, int64_t la, int64_t lb, int64_t smax_abs)
+{
+    const int64_t lim = 1ll << 28, mn = la < lb ? la : lb;
+    const int64_t sp = smax_abs >= 0 ? smax_abs : std::max(e->smax, 0), sn = smax_abs >= 0 ? smax_abs : std::max(-e->smin, 0);
+    const int64_t up = mn * sp;
+    const int64_t down = (la + lb) * -(int64_t)e->e + 3 * -(int64_t)e->o + -(int64_t)(10 * e->o + 10 * e->e) + mn * sn;
+    return up <= lim && down <= lim;
+}
+
 // Checkpointed traceback of ONE pair whose direction bytes exceed the budget (BASELINE configs[3]: "wavefront +
 // checkpointed recompute"; the reference keeps the whole SWCell matrix, SA.rs:60-86, and cannot run such pairs at all).
 //   1. forward sweep, score only (KW, no direction bytes): finds the start cell of the walk (SA.rs:282-308) and saves
@@ -125,7 +137,7 @@ static int align_ckpt_pair(swb_engine *e, const uint8_t *d_a, const uint8_t *d_b
         KWPair P; P.a_off = a_off + row0; P.b_off = b_off; P.la = rows; P.lb = cols_used; P.dir_off = dirs ? 0 : -1;
         P.bnd_off = 0; P.scr_off = 0; P.pssm_off = -1;
         // short, wide bands: the 32-row lag between the warps of a team dominates, fewer and wider strips win (measured)
-        kw_plan(e, &P, 1, dirs, &plan, (dirs && rows < 16384) ? 8 : 0);
+        kw_plan(e, &P, 1, dirs, &plan, (dirs && rows < 16384) ? 8 : 0, true);
         if (dirs && (size_t)plan.dir_bytes + 16 > e->dir_bytes) {
             CUDA_TRY(e, cudaStreamSynchronize(st));
             if (e->d_dir) cudaFree(e->d_dir);
@@ -195,110 +207,42 @@ static int align_ckpt_pair(swb_engine *e, const uint8_t *d_a, const uint8_t *d_b
     return SWB_OK;
 }
 
-// outs: full alignments (lists + strings); souts: the counting form (swb_align_stats_batch).  Exactly one is non-null.
-static int align_batch_impl(swb_engine *e, const char *a_all, const int64_t *off_a, const char *b_all,
-                            const int64_t *off_b, int64_t n, unsigned flags, swb_alignment *outs, const float *pssm,
-                            swb_aln_stats *souts = nullptr)
+// AlnJob (swb_internal.h): the kernels see the DP extents (la, lb) at (a_off, b_off) of the device code arrays; the
+// strings are spelled from the letters as given with the FULL lengths.  Local mode: a hit of a database search is traced
+// inside the prefix box that ends at its end cell -- every cell of the box has the value it has in the full matrix and
+// precedes the end cell in the reference's scan order (SA.rs:286-294), so the walk is the same.
+// Device core of the traceback path: KW with direction bytes + KT for the jobs whose bytes fit the budget (chunked),
+// checkpointed recompute for the others.  outs: full alignments; souts: the counting form.  Exactly one is non-null.
+int align_jobs_device(swb_engine *e, const uint8_t *d_a, const uint8_t *d_b, const std::vector<AlnJob> &jobs, bool retain_all,
+                      swb_alignment *outs, swb_aln_stats *souts, const int32_t *d_pssm, const uint8_t *d_ra, const uint8_t *d_rb)
 {
-    if (!e) return SWB_ERR_ARG;
-    if (n < 0 || (n > 0 && (!off_a || !off_b || (!outs && !souts)))) { e->err = "bad argument"; return SWB_ERR_ARG; }
-    CUDA_TRY(e, cudaSetDevice(e->device));
-    const bool retain_all = (flags & SWB_RETAIN_ALL) != 0;
-    if (outs) memset(outs, 0, sizeof(swb_alignment) * (size_t)n);
-    if (souts) memset(souts, 0, sizeof(swb_aln_stats) * (size_t)n);
     const float inv = 1.0f / (float)e->scale;
     const bool dyadic = (e->scale & (e->scale - 1)) == 0;
     auto to_f = [&](int64_t s) { return dyadic ? (float)s * inv : (float)((double)s / e->scale); };
-    e->stats = swb_stats{}; e->stats.scale = e->scale; e->stats.exact_scale = e->exact_scale;
-
-    // encode on the host (small inputs on this path); unknown letters as SA.rs:669-679
-    const int64_t na = n ? off_a[n] : 0, nb = n ? off_b[n] : 0;
-    std::vector<uint8_t> ca(na + 16), cb(nb + 16);
-    for (int64_t k = 0; k < na && !pssm; ++k) { int c = e->code_of[(unsigned char)a_all[k]]; if (c < 0) { e->err = std::string("unknown letter ") + a_all[k] + ". please set X to allow scoring for undefined letter pair."; return SWB_ERR_LETTER; } ca[k] = (uint8_t)c; }
-    for (int64_t k = 0; k < nb && !pssm; ++k) { int c = e->code_of[(unsigned char)b_all[k]]; if (c < 0) { e->err = std::string("unknown letter ") + b_all[k] + ". please set X to allow scoring for undefined letter pair."; return SWB_ERR_LETTER; } cb[k] = (uint8_t)c; }
-
-    std::vector<int64_t> work;                       // pairs that need the device
-    for (int64_t k = 0; k < n; ++k) {
-        const int64_t la = off_a[k + 1] - off_a[k], lb = off_b[k + 1] - off_b[k];
-        if (la < 0 || lb < 0 || la > 0x3FFFFFF0 || lb > 0x3FFFFFF0) { e->err = "bad offsets"; return SWB_ERR_ARG; }
-        e->stats.cells += (double)la * (double)lb;
-        if (la > 0 && lb > 0) { work.push_back(k); continue; }
-        // an empty sequence: the walk runs along the boundary row/column only (SA.rs:100-118, 296-383)
-        std::vector<int64_t> xa, xb; std::string ra, rb; float score = 0.0f; int64_t ei = -1, ej = -1;
-        if (e->mode != SWB_LOCAL) {
-            if (la == 0 && lb == 0) { e->err = "both sequences are empty (the reference panics here, SA.rs:360-363)"; return SWB_ERR_EMPTY; }
-            const int32_t so = (e->mode == SWB_GLOBAL) ? e->o : 0, se = (e->mode == SWB_GLOBAL) ? e->e : 0;
-            score = to_f((la + lb) * (int64_t)se + (so - se)); ei = la; ej = lb;
-            if (10 * e->o + 10 * e->e == 0) { e->err = "zero gap penalties with an empty sequence (the reference panics here)"; return SWB_ERR_EMPTY; }
-            for (int64_t t = 0; t < la; ++t) { xa.push_back(t); xb.push_back(-1); }
-            for (int64_t t = 0; t < lb; ++t) { xa.push_back(-1); xb.push_back(t); }
-        }
-        if (souts) {
-            KTStats S; S.ncols = (int32_t)xa.size(); S.na = (int32_t)la; S.nb = (int32_t)lb; S.match = 0;
-            S.s1 = la ? 0 : -1; S.e1 = (int32_t)la - 1; S.s2 = lb ? 0 : -1; S.e2 = (int32_t)lb - 1;
-            if (e->mode == SWB_LOCAL) { S.ncols = 0; S.na = 0; S.nb = 0; S.s1 = S.s2 = S.e1 = S.e2 = -1; }
-            souts[k].score = score; souts[k].end_a = ei; souts[k].end_b = ej;
-            swb_compose_stats(&souts[k], e->mode, retain_all, la, lb, S);
+    const int64_t budget = dir_budget();
+    std::vector<size_t> work;
+    for (size_t w = 0; w < jobs.size(); ++w) {
+        const AlnJob &J = jobs[w];
+        if (d_pssm || kw_dir_bytes(J.la, J.lb, 8) <= budget) { work.push_back(w); continue; }
+        // direction bytes do not fit: checkpointed traceback, one pair at a time
+        KWResult R; std::vector<int64_t> xa, xb; std::string ra, rb;
+        int rc = align_ckpt_pair(e, d_a, d_b, J.a_off, J.b_off, J.la, J.lb, budget, &R, xa, xb);
+        if (rc != SWB_OK) return rc;
+        e->stats.ckpt_pairs += 1;
+        if (souts) {                              // counting form: the same counts KT takes on the device, from the lists
+            KTStats S; S.ncols = (int32_t)xa.size(); S.na = 0; S.nb = 0; S.match = 0; S.s1 = S.e1 = S.s2 = S.e2 = -1;
+            for (size_t c = 0; c < xa.size(); ++c) {
+                if (xa[c] >= 0) { if (S.s1 < 0) S.s1 = (int32_t)xa[c]; S.e1 = (int32_t)xa[c]; ++S.na; }
+                if (xb[c] >= 0) { if (S.s2 < 0) S.s2 = (int32_t)xb[c]; S.e2 = (int32_t)xb[c]; ++S.nb; }
+                if (xa[c] >= 0 && xb[c] >= 0 && J.ra[xa[c]] == J.rb[xb[c]]) ++S.match;
+            }
+            souts[J.out].score = to_f(R.score); souts[J.out].end_a = R.end_i; souts[J.out].end_b = R.end_j;
+            swb_compose_stats(&souts[J.out], e->mode, retain_all, J.la_full, J.lb_full, S);
             continue;
         }
-        inflate(a_all + off_a[k], la, b_all + off_b[k], lb, xa.data(), xb.data(), (int64_t)xa.size(), e->mode, retain_all, ra, rb);
-        int rc = fill_out(&outs[k], score, ei, ej, xa, xb, ra, rb);
+        inflate(J.ra, J.la_full, J.rb, J.lb_full, xa.data(), xb.data(), (int64_t)xa.size(), e->mode, retain_all, ra, rb);
+        rc = fill_out(&outs[J.out], to_f(R.score), R.end_i, R.end_j, xa, xb, ra, rb);
         if (rc != SWB_OK) { e->err = "out of memory"; return rc; }
-    }
-    if (work.empty()) return SWB_OK;
-
-    DevBuf d_a, d_b, d_pssm;
-    if (pssm) {                                      // PositionSpecificMatrix (SA.rs:583-623): scores[a + b*a_length] on the engine's grid
-        const size_t np_ = (size_t)na * (size_t)nb;
-        std::vector<int32_t> ps(np_ ? np_ : 1);
-        for (size_t k = 0; k < np_; ++k) {
-            const double v = (double)pssm[k] * e->scale, r = std::nearbyint(v);
-            if (std::fabs(v - r) > 1e-4 * e->scale || std::fabs(r) > 8000) { e->err = "position-specific scores are not on the engine's integer grid (or exceed 8000)"; return SWB_ERR_SCALE; }
-            ps[k] = (int32_t)r;
-        }
-        CUDA_TRY(e, d_pssm.alloc(ps.size() * sizeof(int32_t), e->stream));
-        CUDA_TRY(e, cudaMemcpyAsync(d_pssm.p, ps.data(), ps.size() * sizeof(int32_t), cudaMemcpyHostToDevice, e->stream));
-        CUDA_TRY(e, cudaStreamSynchronize(e->stream));      // ps is a local pageable vector
-        e->stats.h2d_bytes += (double)ps.size() * sizeof(int32_t);
-    }
-    CUDA_TRY(e, d_a.alloc(ca.size(), e->stream)); CUDA_TRY(e, d_b.alloc(cb.size(), e->stream));
-    CUDA_TRY(e, cudaMemcpyAsync(d_a.p, ca.data(), ca.size(), cudaMemcpyHostToDevice, e->stream));
-    CUDA_TRY(e, cudaMemcpyAsync(d_b.p, cb.data(), cb.size(), cudaMemcpyHostToDevice, e->stream));
-    e->stats.h2d_bytes += (double)ca.size() + (double)cb.size();
-    DevBuf d_ra, d_rb;                                // the letters as given: the equal-letter test of the counting form
-    if (souts) {
-        CUDA_TRY(e, d_ra.alloc((size_t)na + 16, e->stream)); CUDA_TRY(e, d_rb.alloc((size_t)nb + 16, e->stream));
-        if (na) CUDA_TRY(e, cudaMemcpyAsync(d_ra.p, a_all, na, cudaMemcpyHostToDevice, e->stream));
-        if (nb) CUDA_TRY(e, cudaMemcpyAsync(d_rb.p, b_all, nb, cudaMemcpyHostToDevice, e->stream));
-        e->stats.h2d_bytes += (double)na + (double)nb;
-    }
-
-    const int64_t budget = dir_budget();
-    if (!pssm) {                                      // pairs whose direction bytes do not fit: checkpointed traceback, one at a time
-        std::vector<int64_t> rest;
-        for (int64_t k : work) {
-            const int32_t la = (int32_t)(off_a[k + 1] - off_a[k]), lb = (int32_t)(off_b[k + 1] - off_b[k]);
-            if (kw_dir_bytes(la, lb, 8) <= budget) { rest.push_back(k); continue; }
-            KWResult R; std::vector<int64_t> xa, xb; std::string ra, rb;
-            int rc = align_ckpt_pair(e, d_a.as<uint8_t>(), d_b.as<uint8_t>(), off_a[k], off_b[k], la, lb, budget, &R, xa, xb);
-            if (rc != SWB_OK) return rc;
-            e->stats.ckpt_pairs += 1;
-            if (souts) {                              // counting form: the same counts KT takes on the device, from the lists
-                KTStats S; S.ncols = (int32_t)xa.size(); S.na = 0; S.nb = 0; S.match = 0; S.s1 = S.e1 = S.s2 = S.e2 = -1;
-                for (size_t c = 0; c < xa.size(); ++c) {
-                    if (xa[c] >= 0) { if (S.s1 < 0) S.s1 = (int32_t)xa[c]; S.e1 = (int32_t)xa[c]; ++S.na; }
-                    if (xb[c] >= 0) { if (S.s2 < 0) S.s2 = (int32_t)xb[c]; S.e2 = (int32_t)xb[c]; ++S.nb; }
-                    if (xa[c] >= 0 && xb[c] >= 0 && a_all[off_a[k] + xa[c]] == b_all[off_b[k] + xb[c]]) ++S.match;
-                }
-                souts[k].score = to_f(R.score); souts[k].end_a = R.end_i; souts[k].end_b = R.end_j;
-                swb_compose_stats(&souts[k], e->mode, retain_all, la, lb, S);
-                continue;
-            }
-            inflate(a_all + off_a[k], la, b_all + off_b[k], lb, xa.data(), xb.data(), (int64_t)xa.size(), e->mode, retain_all, ra, rb);
-            rc = fill_out(&outs[k], to_f(R.score), R.end_i, R.end_j, xa, xb, ra, rb);
-            if (rc != SWB_OK) { e->err = "out of memory"; return rc; }
-        }
-        work.swap(rest);
     }
     size_t pos = 0;
     while (pos < work.size()) {
@@ -307,13 +251,12 @@ static int align_batch_impl(swb_engine *e, const char *a_all, const int64_t *off
         int64_t dir_total = 0, out_total = 0;
         size_t end = pos;
         while (end < work.size()) {
-            const int64_t k = work[end];
-            const int32_t la = (int32_t)(off_a[k + 1] - off_a[k]), lb = (int32_t)(off_b[k + 1] - off_b[k]);
-            const int64_t db = kw_dir_bytes(la, lb, 8);              // upper bound over both strip widths
+            const AlnJob &J = jobs[work[end]];
+            const int64_t db = kw_dir_bytes(J.la, J.lb, 8);              // upper bound over both strip widths
             if (!hp.empty() && dir_total + db > budget) break;
-            KWPair P; P.a_off = off_a[k]; P.b_off = off_b[k]; P.la = la; P.lb = lb; P.dir_off = dir_total; P.bnd_off = 0; P.scr_off = 0; P.pssm_off = pssm ? 0 : -1;
+            KWPair P; P.a_off = J.a_off; P.b_off = J.b_off; P.la = J.la; P.lb = J.lb; P.dir_off = dir_total; P.bnd_off = 0; P.scr_off = 0; P.pssm_off = d_pssm ? 0 : -1;
             hp.push_back(P); out_off.push_back(out_total);
-            dir_total += db; out_total += (int64_t)la + lb + 1;
+            dir_total += db; out_total += (int64_t)J.la + J.lb + 1;
             ++end;
         }
         const int np = (int)hp.size();
@@ -341,11 +284,11 @@ static int align_batch_impl(swb_engine *e, const char *a_all, const int64_t *off
         }
         CUDA_TRY(e, cudaMemcpyAsync(d_pairs.p, hp.data(), np * sizeof(KWPair), cudaMemcpyHostToDevice, e->stream));
         CUDA_TRY(e, cudaEventRecord(e->ev0, e->stream));
-        CUDA_TRY(e, kw_launch(e, d_a.as<uint8_t>(), d_b.as<uint8_t>(), d_pairs.as<KWPair>(), np, plan, (uint8_t *)e->d_dir,
-                              d_bnd.as<int4>(), d_scr.as<int>(), d_res.as<KWResult>(), e->stream, d_pssm.as<int32_t>()));
+        CUDA_TRY(e, kw_launch(e, d_a, d_b, d_pairs.as<KWPair>(), np, plan, (uint8_t *)e->d_dir,
+                              d_bnd.as<int4>(), d_scr.as<int>(), d_res.as<KWResult>(), e->stream, d_pssm));
         if (souts)
             CUDA_TRY(e, kt_stats_launch(e, d_pairs.as<KWPair>(), d_res.as<KWResult>(), np, (const uint8_t *)e->d_dir, plan.cols,
-                                        d_ra.as<uint8_t>(), d_rb.as<uint8_t>(), d_st.as<KTStats>(), e->stream));
+                                        d_ra, d_rb, d_st.as<KTStats>(), e->stream));
         else
             CUDA_TRY(e, kt_launch(e, d_pairs.as<KWPair>(), d_res.as<KWResult>(), np, (const uint8_t *)e->d_dir, plan.cols, d_off.as<int64_t>(),
                                   d_xa.as<int32_t>(), d_xb.as<int32_t>(), d_nc.as<int32_t>(), e->stream));
@@ -375,11 +318,11 @@ static int align_batch_impl(swb_engine *e, const char *a_all, const int64_t *off
         e->stats.d2h_bytes += (double)np * (sizeof(KWResult) + (souts ? sizeof(KTStats) : 4)) + 8.0 * out_total;
         if (souts) {
             for (int t = 0; t < np; ++t) {
-                const int64_t k = work[pos + t];
-                swb_aln_stats *o = &souts[k];
+                const AlnJob &J = jobs[work[pos + t]];
+                swb_aln_stats *o = &souts[J.out];
                 o->score = to_f(hr[t].score); o->end_a = hr[t].end_i; o->end_b = hr[t].end_j;
                 if (hst[t].ncols < 0) { o->status = SWB_ERR_EMPTY; continue; }      // the reference panics on this pair (SA.rs:360-371)
-                swb_compose_stats(o, e->mode, retain_all, hp[t].la, hp[t].lb, hst[t]);
+                swb_compose_stats(o, e->mode, retain_all, J.la_full, J.lb_full, hst[t]);
             }
             pos = end;
             continue;
@@ -390,7 +333,7 @@ static int align_batch_impl(swb_engine *e, const char *a_all, const int64_t *off
             for (;;) {
                 const int t = next.fetch_add(1);
                 if (t >= np || fail.load() != SWB_OK) return;
-                const int64_t k = work[pos + t];
+                const AlnJob &J = jobs[work[pos + t]];
                 if (hnc[t] < 0) { fail.store(SWB_ERR_EMPTY); return; }
                 const int64_t nc = hnc[t];
                 std::vector<int64_t> xa(nc), xb(nc);
@@ -398,8 +341,8 @@ static int align_batch_impl(swb_engine *e, const char *a_all, const int64_t *off
                     xa[c] = hxa[out_off[t] + nc - 1 - c]; xb[c] = hxb[out_off[t] + nc - 1 - c];
                 }
                 std::string ra, rb;
-                inflate(a_all + off_a[k], hp[t].la, b_all + off_b[k], hp[t].lb, xa.data(), xb.data(), nc, e->mode, retain_all, ra, rb);
-                if (fill_out(&outs[k], to_f(hr[t].score), hr[t].end_i, hr[t].end_j, xa, xb, ra, rb) != SWB_OK) { fail.store(SWB_ERR_NOMEM); return; }
+                inflate(J.ra, J.la_full, J.rb, J.lb_full, xa.data(), xb.data(), nc, e->mode, retain_all, ra, rb);
+                if (fill_out(&outs[J.out], to_f(hr[t].score), hr[t].end_i, hr[t].end_j, xa, xb, ra, rb) != SWB_OK) { fail.store(SWB_ERR_NOMEM); return; }
             }
         };
         const int n_thr = (np >= 8) ? (int)std::min<unsigned>(std::max(1u, std::thread::hardware_concurrency()), 16u) : 1;
@@ -413,6 +356,115 @@ static int align_batch_impl(swb_engine *e, const char *a_all, const int64_t *off
         pos = end;
     }
     return SWB_OK;
+}
+
+// Releases what a failed batch call has already filled in (the caller's array goes back to all-zero records).
+static void free_outs(swb_alignment *outs, int64_t n)
+{
+    if (!outs) return;
+    for (int64_t k = 0; k < n; ++k) swb_alignment_free(&outs[k]);
+}
+
+// outs: full alignments (lists + strings); souts: the counting form (swb_align_stats_batch).  Exactly one is non-null.
+// full_a / full_b (may be null): lengths of the whole sequences when a_all / b_all hold only the prefixes to align
+// (align_partial's partial_region, SA.rs:396-405: the DP runs on the prefixes, the padding loops over the whole sequences).
+static int align_batch_core(swb_engine *e, const char *a_all, const int64_t *off_a, const char *b_all,
+                            const int64_t *off_b, int64_t n, unsigned flags, swb_alignment *outs, const float *pssm,
+                            swb_aln_stats *souts, const int64_t *part_a, const int64_t *part_b)
+{
+    const bool retain_all = (flags & SWB_RETAIN_ALL) != 0;
+    const float inv = 1.0f / (float)e->scale;
+    const bool dyadic = (e->scale & (e->scale - 1)) == 0;
+    auto to_f = [&](int64_t s) { return dyadic ? (float)s * inv : (float)((double)s / e->scale); };
+    e->stats = swb_stats{}; e->stats.scale = e->scale; e->stats.exact_scale = e->exact_scale;
+
+    // encode on the host (small inputs on this path); unknown letters as SA.rs:669-679
+    const int64_t na = n ? off_a[n] : 0, nb = n ? off_b[n] : 0;
+    std::vector<uint8_t> ca(na + 16), cb(nb + 16);
+    for (int64_t k = 0; k < na && !pssm; ++k) { int c = e->code_of[(unsigned char)a_all[k]]; if (c < 0) { e->err = std::string("unknown letter ") + a_all[k] + ". please set X to allow scoring for undefined letter pair."; return SWB_ERR_LETTER; } ca[k] = (uint8_t)c; }
+    for (int64_t k = 0; k < nb && !pssm; ++k) { int c = e->code_of[(unsigned char)b_all[k]]; if (c < 0) { e->err = std::string("unknown letter ") + b_all[k] + ". please set X to allow scoring for undefined letter pair."; return SWB_ERR_LETTER; } cb[k] = (uint8_t)c; }
+
+    // int32 lanes: the scores of a pair must stay well inside +-2^29 (the PAD score of the wavefront kernel)
+    std::vector<AlnJob> jobs;                        // pairs that need the device
+    for (int64_t k = 0; k < n; ++k) {
+        const int64_t la_full = off_a[k + 1] - off_a[k], lb_full = off_b[k + 1] - off_b[k];
+        if (la_full < 0 || lb_full < 0 || la_full > 0x3FFFFFF0 || lb_full > 0x3FFFFFF0) { e->err = "bad offsets"; return SWB_ERR_ARG; }
+        // partial_region (SA.rs:396-405): the DP sees the prefixes, the padding the whole sequences
+        const int64_t la = part_a ? std::min(std::max<int64_t>(part_a[k], 0), la_full) : la_full;
+        const int64_t lb = part_b ? std::min(std::max<int64_t>(part_b[k], 0), lb_full) : lb_full;
+        if (!swb_range_ok(e, la, lb, pssm ? 8000 : -1)) { e->err = "scores of a pair this long do not fit the int32 lanes"; return SWB_ERR_RANGE; }
+        e->stats.cells += (double)la * (double)lb;
+        if (la > 0 && lb > 0) {
+            AlnJob J; J.a_off = off_a[k]; J.b_off = off_b[k]; J.la = (int32_t)la; J.lb = (int32_t)lb;
+            J.ra = a_all + off_a[k]; J.rb = b_all + off_b[k]; J.la_full = la_full; J.lb_full = lb_full; J.out = k;
+            jobs.push_back(J);
+            continue;
+        }
+        // an empty sequence: the walk runs along the boundary row/column only (SA.rs:100-118, 296-383)
+        std::vector<int64_t> xa, xb; std::string ra, rb; float score = 0.0f; int64_t ei = -1, ej = -1;
+        if (e->mode != SWB_LOCAL) {
+            if (la == 0 && lb == 0) { e->err = "both sequences are empty (the reference panics here, SA.rs:360-363)"; return SWB_ERR_EMPTY; }
+            const int32_t so = (e->mode == SWB_GLOBAL) ? e->o : 0, se = (e->mode == SWB_GLOBAL) ? e->e : 0;
+            score = to_f((la + lb) * (int64_t)se + (so - se)); ei = la; ej = lb;
+            if (10 * e->o + 10 * e->e == 0) { e->err = "zero gap penalties with an empty sequence (the reference panics here)"; return SWB_ERR_EMPTY; }
+            for (int64_t t = 0; t < la; ++t) { xa.push_back(t); xb.push_back(-1); }
+            for (int64_t t = 0; t < lb; ++t) { xa.push_back(-1); xb.push_back(t); }
+        }
+        if (souts) {
+            KTStats S; S.ncols = (int32_t)xa.size(); S.na = (int32_t)la; S.nb = (int32_t)lb; S.match = 0;
+            S.s1 = la ? 0 : -1; S.e1 = (int32_t)la - 1; S.s2 = lb ? 0 : -1; S.e2 = (int32_t)lb - 1;
+            if (e->mode == SWB_LOCAL) { S.ncols = 0; S.na = 0; S.nb = 0; S.s1 = S.s2 = S.e1 = S.e2 = -1; }
+            souts[k].score = score; souts[k].end_a = ei; souts[k].end_b = ej;
+            swb_compose_stats(&souts[k], e->mode, retain_all, la_full, lb_full, S);
+            continue;
+        }
+        inflate(a_all + off_a[k], la_full, b_all + off_b[k], lb_full, xa.data(), xb.data(), (int64_t)xa.size(), e->mode, retain_all, ra, rb);
+        int rc = fill_out(&outs[k], score, ei, ej, xa, xb, ra, rb);
+        if (rc != SWB_OK) { e->err = "out of memory"; return rc; }
+    }
+    if (jobs.empty()) return SWB_OK;
+
+    DevBuf d_a, d_b, d_pssm;
+    if (pssm) {                                      // PositionSpecificMatrix (SA.rs:583-623): scores[a + b*a_length] on the engine's grid
+        const size_t np_ = (size_t)na * (size_t)nb;
+        std::vector<int32_t> ps(np_ ? np_ : 1);
+        for (size_t k = 0; k < np_; ++k) {
+            const double v = (double)pssm[k] * e->scale, r = std::nearbyint(v);
+            if (std::fabs(v - r) > 1e-4 * e->scale || std::fabs(r) > 8000) { e->err = "position-specific scores are not on the engine's integer grid (or exceed 8000)"; return SWB_ERR_SCALE; }
+            ps[k] = (int32_t)r;
+        }
+        CUDA_TRY(e, d_pssm.alloc(ps.size() * sizeof(int32_t), e->stream));
+        CUDA_TRY(e, cudaMemcpyAsync(d_pssm.p, ps.data(), ps.size() * sizeof(int32_t), cudaMemcpyHostToDevice, e->stream));
+        CUDA_TRY(e, cudaStreamSynchronize(e->stream));      // ps is a local pageable vector
+        e->stats.h2d_bytes += (double)ps.size() * sizeof(int32_t);
+    }
+    CUDA_TRY(e, d_a.alloc(ca.size(), e->stream)); CUDA_TRY(e, d_b.alloc(cb.size(), e->stream));
+    CUDA_TRY(e, cudaMemcpyAsync(d_a.p, ca.data(), ca.size(), cudaMemcpyHostToDevice, e->stream));
+    CUDA_TRY(e, cudaMemcpyAsync(d_b.p, cb.data(), cb.size(), cudaMemcpyHostToDevice, e->stream));
+    e->stats.h2d_bytes += (double)ca.size() + (double)cb.size();
+    DevBuf d_ra, d_rb;                                // the letters as given: the equal-letter test of the counting form
+    if (souts) {
+        CUDA_TRY(e, d_ra.alloc((size_t)na + 16, e->stream)); CUDA_TRY(e, d_rb.alloc((size_t)nb + 16, e->stream));
+        if (na) CUDA_TRY(e, cudaMemcpyAsync(d_ra.p, a_all, na, cudaMemcpyHostToDevice, e->stream));
+        if (nb) CUDA_TRY(e, cudaMemcpyAsync(d_rb.p, b_all, nb, cudaMemcpyHostToDevice, e->stream));
+        e->stats.h2d_bytes += (double)na + (double)nb;
+    }
+    return align_jobs_device(e, d_a.as<uint8_t>(), d_b.as<uint8_t>(), jobs, retain_all, outs, souts,
+                             pssm ? d_pssm.as<int32_t>() : nullptr, d_ra.as<uint8_t>(), d_rb.as<uint8_t>());
+}
+
+static int align_batch_impl(swb_engine *e, const char *a_all, const int64_t *off_a, const char *b_all,
+                            const int64_t *off_b, int64_t n, unsigned flags, swb_alignment *outs, const float *pssm,
+                            swb_aln_stats *souts = nullptr, const int64_t *part_a = nullptr, const int64_t *part_b = nullptr)
+{
+    if (!e) return SWB_ERR_ARG;
+    if (n < 0 || (n > 0 && (!off_a || !off_b || (!outs && !souts)))) { e->err = "bad argument"; return SWB_ERR_ARG; }
+    CUDA_TRY(e, cudaSetDevice(e->device));
+    if (outs) memset(outs, 0, sizeof(swb_alignment) * (size_t)n);
+    if (souts) memset(souts, 0, sizeof(swb_aln_stats) * (size_t)n);
+    const int rc = align_batch_core(e, a_all, off_a, b_all, off_b, n, flags, outs, pssm, souts, part_a, part_b);
+    if (rc != SWB_OK) free_outs(outs, n);            // nothing half-filled is handed back (the records are all-zero again)
+    return rc;
 }
 
 extern "C" int swb_align_batch(swb_engine *e, const char *a_all, const int64_t *off_a, const char *b_all,
@@ -440,6 +492,32 @@ extern "C" int swb_align_pssm(swb_engine *e, const float *scores, const char *a,
     if (!out || !scores || la < 1 || lb < 1 || !a || !b) { e->err = "bad argument (position-specific alignment needs two non-empty sequences)"; return SWB_ERR_ARG; }
     const int64_t oa[2] = {0, la}, ob[2] = {0, lb};
     return align_batch_impl(e, a, oa, b, ob, 1, retain_all ? SWB_RETAIN_ALL : 0u, out, scores);
+}
+
+// align_partial (SA.rs:393-551): DP on the prefixes a[0..pa), b[0..pb); the retain_all padding runs over the whole
+// sequences (SA.rs:512-549); score_only returns after the score scan (SA.rs:438-467) with empty strings.
+extern "C" int swb_align_partial(swb_engine *e, const char *a, int64_t la, const char *b, int64_t lb, int64_t pa, int64_t pb,
+                                 int retain_all, int score_only, swb_alignment *out)
+{
+    if (!e) return SWB_ERR_ARG;
+    if (!out || la < 0 || lb < 0 || pa < 0 || pb < 0) { e->err = "bad argument"; return SWB_ERR_ARG; }
+    static const char empty[1] = {0};
+    pa = std::min(pa, la); pb = std::min(pb, lb);
+    const int64_t oa[2] = {0, la}, ob[2] = {0, lb};
+    if (score_only) {
+        memset(out, 0, sizeof(*out));
+        if (e->mode != SWB_LOCAL && pa == 0 && pb == 0) { e->err = "both sequences are empty (the reference panics here, SA.rs:360-363)"; return SWB_ERR_EMPTY; }
+        const int64_t pa2[2] = {0, pa}, pb2[2] = {0, pb};
+        float sc = 0; int64_t ea = -1, eb = -1;
+        int rc = swb_score_batch(e, a ? a : empty, pa2, b ? b : empty, pb2, 1, &sc, &ea, &eb);
+        if (rc != SWB_OK) return rc;
+        out->score = sc; out->end_a = ea; out->end_b = eb;
+        out->idx_a = (int64_t *)malloc(sizeof(int64_t)); out->idx_b = (int64_t *)malloc(sizeof(int64_t));
+        out->aln_a = dup_n(std::string()); out->aln_b = dup_n(std::string());
+        if (!out->idx_a || !out->idx_b || !out->aln_a || !out->aln_b) { swb_alignment_free(out); e->err = "out of memory"; return SWB_ERR_NOMEM; }
+        return SWB_OK;
+    }
+    return align_batch_impl(e, a ? a : empty, oa, b ? b : empty, ob, 1, retain_all ? SWB_RETAIN_ALL : 0u, out, nullptr, nullptr, &pa, &pb);
 }
 
 extern "C" int swb_align(swb_engine *e, const char *a, int64_t la, const char *b, int64_t lb, int retain_all,

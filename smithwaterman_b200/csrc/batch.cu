@@ -42,6 +42,7 @@ struct BatchDev {                  // device-only members that do not fit the pl
     cudaEvent_t ev_trace = nullptr;                          // SWB_TRACE only: residues and offsets have landed
     cudaStream_t alloc_stream = nullptr;                     // stream of the batch's allocations (and of their release)
     bool launched = false, done_recorded = false;
+    bool borrow_b = false, borrow_items = false, borrow_res = false;   // resident database: codes_b / off_b, the K2 items, d_res belong to the swb_db
 };
 static BatchDev *dev_of(swb_batch *b) { return b->dev; }
 
@@ -91,6 +92,8 @@ __global__ void SWB_HELPER scan_kernel(const T *__restrict__ in, T *__restrict__
         __syncthreads();
     }
 }
+static int64_t pad16(int64_t x) { return (x + 15) / 16 * 16; }
+
 __global__ void SWB_HELPER encode_kernel(uint8_t *buf, int64_t nbytes, const int16_t *__restrict__ code_of, int32_t *err, int pad)
 {
     __shared__ int16_t tab[256];
@@ -116,6 +119,13 @@ __global__ void SWB_HELPER encode_kernel(uint8_t *buf, int64_t nbytes, const int
         if (bad) atomicExch(err, 1);
         *reinterpret_cast<uint4 *>(buf + base) = make_uint4(w[0], w[1], w[2], w[3]);
     }
+}
+
+cudaError_t batch_encode(swb_engine *e, uint8_t *d_buf, int64_t nbytes, int32_t *d_err, cudaStream_t st)
+{
+    const int64_t np = pad16(nbytes) + 16;
+    encode_kernel<<<(int)std::min<int64_t>((np / 16 + HELPER_THREADS - 1) / HELPER_THREADS, e->sm_count * 16), HELPER_THREADS, 0, st>>>(d_buf, nbytes, e->d_code_tab, d_err, e->n);
+    return cudaGetLastError();
 }
 
 // One block per K1 work item: gathers the 32 pairs' residues into the [4-row block][lane] row layout
@@ -203,24 +213,24 @@ static K1Take k1_take_rule(const swb_engine *e)
 }
 
 __device__ __forceinline__ bool sort_take(const int64_t *__restrict__ off_a, const int64_t *__restrict__ off_b, int64_t k,
-                                          int shared_la, int la_cap, int pass_cap, const K1Take &T, int &la, int &np, int &bucket)
+                                          int shared_la, int la_cap, int la_gran, int pass_cap, const K1Take &T, int &la, int &np, int &bucket)
 {
     const int64_t la64 = shared_la >= 0 ? (int64_t)shared_la : off_a[k + 1] - off_a[k], lb64 = off_b[k + 1] - off_b[k];
     if (!k1_take(la64, lb64, T)) return false;
     la = (int)la64; np = ((int)lb64 + K1_STRIP - 1) / K1_STRIP;
-    bucket = (pass_cap - np) * (la_cap + 1) + (la_cap - la);
+    bucket = (pass_cap - np) * (la_cap / la_gran + 1) + (la_cap - la) / la_gran;     // la in steps of la_gran: at most 65536 buckets
     return true;
 }
 
 // SCATTER == false: histogram of the buckets; true: order[cursor[bucket]++] = pair.  One atomic per distinct bucket of a warp.
 template <bool SCATTER>
 __global__ void SWB_HELPER sort_count_kernel(const int64_t *__restrict__ off_a, const int64_t *__restrict__ off_b, int64_t n, int shared_la,
-                                  int la_cap, int pass_cap, K1Take T, int32_t *__restrict__ cnt, int32_t *__restrict__ order)
+                                  int la_cap, int la_gran, int pass_cap, K1Take T, int32_t *__restrict__ cnt, int32_t *__restrict__ order)
 {
     const int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     const int lane = threadIdx.x & 31;
     int la = 0, np = 0, bucket = -1;
-    const bool take = k < n && sort_take(off_a, off_b, k, shared_la, la_cap, pass_cap, T, la, np, bucket);
+    const bool take = k < n && sort_take(off_a, off_b, k, shared_la, la_cap, la_gran, pass_cap, T, la, np, bucket);
     const unsigned takers = __ballot_sync(0xffffffffu, take);
     if (!take) return;
     const unsigned peers = __match_any_sync(takers, bucket);
@@ -286,6 +296,28 @@ __global__ void SWB_HELPER finalize_kw_kernel(const KWResult *__restrict__ res, 
     sc[k] = score_to_f(r.score, scale, inv, dyadic != 0); ea[k] = r.end_i; eb[k] = r.end_j;
 }
 
+// KW results -> the unified per-pair record array (database search: the top-K selection reads one array)
+__global__ void SWB_HELPER collect_kw_kernel(const KWResult *__restrict__ res, const int32_t *__restrict__ idx, int n_kw, K1Result *__restrict__ out)
+{
+    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= n_kw) return;
+    const KWResult r = res[t];
+    K1Result o; o.score = r.score; o.end_i = r.end_i; o.end_j = r.end_j; o.flags = 0;
+    out[idx[t]] = o;
+}
+cudaError_t batch_collect_kw(swb_engine *e, swb_batch *b, cudaStream_t st)
+{
+    BatchDev *d = b->dev;
+    if (!d->n_kw) return cudaSuccess;
+    collect_kw_kernel<<<(d->n_kw + HELPER_THREADS - 1) / HELPER_THREADS, HELPER_THREADS, 0, st>>>(d->kw_res, d->d_kw_idx, d->n_kw, b->d_res);
+    return cudaGetLastError();
+}
+int batch_device_views(swb_batch *b, const uint8_t **codes_a, const uint8_t **codes_b)
+{
+    *codes_a = b->dev->codes_a; *codes_b = b->dev->codes_b;
+    return SWB_OK;
+}
+
 // cudaHostAlloc'ed / registered host memory: an asynchronous copy to it does not stall the host
 static bool host_pinned(const void *p, size_t bytes)
 {
@@ -297,8 +329,6 @@ static bool host_pinned(const void *p, size_t bytes)
     }
     return at0.type == cudaMemoryTypeHost && at1.type == cudaMemoryTypeHost;
 }
-
-static int64_t pad16(int64_t x) { return (x + 15) / 16 * 16; }
 
 // Device memory comes from the stream-ordered pool of the engine's device (cudaMallocAsync): after the first call the
 // allocations of a batch cost microseconds and never synchronise the device.
@@ -317,12 +347,63 @@ static void *stage_alloc(swb_engine *e, size_t bytes)
 }
 
 static cudaStream_t kstream(const swb_engine *e, const swb_batch *b);
+// K2 work items: subjects of >= 32 passes take a warp each (several sweeps), the others are bin-packed (first fit,
+// longest first) into warps of 32 lanes, one lane per 32-column pass.
+size_t k2_items_cap(const std::vector<int32_t> &lb, const std::vector<int32_t> &idx)
+{
+    size_t longs = 0, small_passes = 0;
+    for (int32_t k : idx) {
+        const int np = (lb[k] + K1_STRIP - 1) / K1_STRIP;
+        if (np >= 32) ++longs; else small_passes += (size_t)np;
+    }
+    return longs + small_passes / 32 + small_passes / 256 + 64;    // first fit wastes < 12 %
+}
+int64_t k2_build_items(const std::vector<int32_t> &lb, const std::vector<int32_t> &idx, int32_t *h_items, int32_t *h_sweeps, size_t cap_items)
+{
+    std::vector<std::vector<int32_t>> bucket(32);
+    std::vector<int32_t> longs;
+    for (int32_t k : idx) {
+        const int np = (lb[k] + K1_STRIP - 1) / K1_STRIP;
+        if (np >= 32) longs.push_back(k); else bucket[np].push_back(k);
+    }
+    std::sort(longs.begin(), longs.end(), [&](int32_t x, int32_t y) { return lb[x] > lb[y]; });
+    unsigned mask = 0;
+    for (int p = 1; p < 32; ++p) if (!bucket[p].empty()) mask |= 1u << p;
+    size_t ni = 0;
+    for (int32_t k : longs) {
+        if (ni >= cap_items) return -1;
+        for (int l = 0; l < 32; ++l) h_items[ni * 32 + l] = k;
+        h_sweeps[ni++] = ((lb[k] + K1_STRIP - 1) / K1_STRIP + 31) / 32;
+    }
+    while (mask) {
+        int cap = 32, l = 0;
+        if (ni >= cap_items) return -1;
+        while (cap > 0) {
+            const unsigned fit = mask & ((cap >= 31) ? 0xFFFFFFFFu : ((2u << cap) - 1u));
+            if (!fit) break;
+            const int p = 31 - __builtin_clz(fit);
+            const int32_t k = bucket[p].back(); bucket[p].pop_back();
+            if (bucket[p].empty()) mask &= ~(1u << p);
+            for (int t = 0; t < p; ++t) h_items[ni * 32 + l++] = k;
+            cap -= p;
+        }
+        for (; l < 32; ++l) h_items[ni * 32 + l] = -1;
+        h_sweeps[ni++] = 1;
+    }
+    return (int64_t)ni;
+}
+
 // The blocks go back to the pool on the stream they were allocated on: a block freed on a compute stream would be ordered
 // behind whatever kernels are queued there (the K1 of a later chunk), and the next chunk's allocations on the upload
 // stream, which reuse it, would wait for those kernels.  The batch's own work is ordered before the free by its events.
-static void batch_release(swb_engine *e, swb_batch *b)
+void batch_release(swb_engine *e, swb_batch *b)
 {
     if (!b) return;
+    if (b->dev) {                                     // what belongs to a resident database is not the batch's to free
+        if (b->dev->borrow_b) { b->dev->codes_b = nullptr; b->dev->off_b = nullptr; }
+        if (b->dev->borrow_items) { b->dev->items = nullptr; b->dev->sweeps = nullptr; }
+        if (b->dev->borrow_res) b->d_res = nullptr;
+    }
     cudaSetDevice(e->device);
     BatchDev *d = dev_of(b);
     cudaStream_t fs = (d && d->alloc_stream) ? d->alloc_stream : e->stream;
@@ -391,9 +472,11 @@ static cudaStream_t kstream(const swb_engine *e, const swb_batch *b) { return b-
 // Upload = shape sort + work-item table on the host, then (all asynchronous on the engine's stream) H2D of the raw
 // residues and offsets, in-place encoding, packing into the K1 layout.  `off_*` are the caller's absolute offsets;
 // residues are taken from a_all[off_a[0] .. off_a[n]).  use_arena: results staging comes from the engine's arena.
-static int batch_upload_impl(swb_engine *e, const char *a_all, const int64_t *off_a, const char *b_all,
-                             const int64_t *off_b, int64_t n, int64_t shared_la, bool use_arena, cudaStream_t up, cudaStream_t hs, swb_batch **out)
+int batch_upload_impl(swb_engine *e, const char *a_all, const int64_t *off_a, const char *b_all,
+                      const int64_t *off_b, int64_t n, int64_t shared_la, bool use_arena, cudaStream_t up, cudaStream_t hs, swb_batch **out,
+                      const swb_db *rdb)
 {
+    if (rdb) { off_b = rdb->h_off.data(); b_all = nullptr; n = rdb->n; }
     *out = nullptr;
     swb_batch *b = new swb_batch();
     BatchDev *d = new BatchDev();
@@ -415,32 +498,33 @@ static int batch_upload_impl(swb_engine *e, const char *a_all, const int64_t *of
     };
     d->base_a = (n && !shared) ? off_a[0] : 0; d->base_b = n ? off_b[0] : 0;
     const int64_t na = shared ? shared_la : (n ? off_a[n] - d->base_a : 0), nb = n ? off_b[n] - d->base_b : 0;
-    if (na < 0 || nb < 0 || (na > 0 && !a_all) || (nb > 0 && !b_all)) { e->err = "bad sequence buffer / offsets"; return SWB_ERR_ARG; }
+    if (na < 0 || nb < 0 || (na > 0 && !a_all) || (nb > 0 && !b_all && !rdb)) { e->err = "bad sequence buffer / offsets"; return SWB_ERR_ARG; }
     const bool use_k1 = ((e->mode == SWB_LOCAL || e->mode == SWB_GLOBAL) && e->o <= e->e);   // the packed Gotoh cell needs |open| >= |ext|
     const K1Take take = k1_take_rule(e);
 
     // ---- device buffers + H2D of the raw residues first (stream-ordered, no host synchronisation): the copy engine works
     //      while the host sorts
     const int64_t na_p = pad16(na) + 16, nb_p = pad16(nb) + 16;
-    DEV_ALLOC_ON(e, up, d->codes_a, na_p); DEV_ALLOC_ON(e, up, d->codes_b, nb_p);
+    DEV_ALLOC_ON(e, up, d->codes_a, na_p);
+    if (rdb) { d->codes_b = rdb->d_codes; d->off_b = rdb->d_off; d->borrow_b = true; }       // resident: nothing to copy or encode
+    else { DEV_ALLOC_ON(e, up, d->codes_b, nb_p); DEV_ALLOC_ON(e, up, d->off_b, (n + 1) * sizeof(int64_t)); }
     if (!shared) DEV_ALLOC_ON(e, up, d->off_a, (n + 1) * sizeof(int64_t));
-    DEV_ALLOC_ON(e, up, d->off_b, (n + 1) * sizeof(int64_t));
     DEV_ALLOC_ON(e, up, d->err, sizeof(int32_t));
     if (na) CUDA_TRY(e, cudaMemcpyAsync(d->codes_a, a_all + d->base_a, na, cudaMemcpyHostToDevice, up));
-    if (nb) CUDA_TRY(e, cudaMemcpyAsync(d->codes_b, b_all + d->base_b, nb, cudaMemcpyHostToDevice, up));
+    if (nb && !rdb) CUDA_TRY(e, cudaMemcpyAsync(d->codes_b, b_all + d->base_b, nb, cudaMemcpyHostToDevice, up));
     if (n) {
         if (!shared) CUDA_TRY(e, cudaMemcpyAsync(d->off_a, off_a, (n + 1) * sizeof(int64_t), cudaMemcpyHostToDevice, up));
-        CUDA_TRY(e, cudaMemcpyAsync(d->off_b, off_b, (n + 1) * sizeof(int64_t), cudaMemcpyHostToDevice, up));
+        if (!rdb) CUDA_TRY(e, cudaMemcpyAsync(d->off_b, off_b, (n + 1) * sizeof(int64_t), cudaMemcpyHostToDevice, up));
     }
-    e->stats.h2d_bytes += (double)na + (double)nb + 2.0 * (n + 1) * sizeof(int64_t);
+    e->stats.h2d_bytes += (double)na + (rdb ? 0.0 : (double)nb + (double)(n + 1) * sizeof(int64_t)) + (shared ? 0.0 : (double)(n + 1) * sizeof(int64_t));
     if (getenv("SWB_TRACE")) { cudaEventCreate(&d->ev_trace); cudaEventRecord(d->ev_trace, up); }
     CUDA_TRY(e, join());
     // (own kernels instead of cudaMemsetAsync: see SWB_HELPER)
     CUDA_TRY(e, zero_async(d->err, sizeof(int32_t), hs));
     CUDA_TRY(e, zero_async(d->codes_a + pad16(na), 16, hs));       // the slack behind the residues
-    CUDA_TRY(e, zero_async(d->codes_b + pad16(nb), 16, hs));
+    if (!rdb) CUDA_TRY(e, zero_async(d->codes_b + pad16(nb), 16, hs));
     if (na) encode_kernel<<<(int)std::min<int64_t>((na_p / 16 + HELPER_THREADS - 1) / HELPER_THREADS, e->sm_count * 16), HELPER_THREADS, 0, hs>>>(d->codes_a, na, e->d_code_tab, d->err, e->n);
-    if (nb) encode_kernel<<<(int)std::min<int64_t>((nb_p / 16 + HELPER_THREADS - 1) / HELPER_THREADS, e->sm_count * 16), HELPER_THREADS, 0, hs>>>(d->codes_b, nb, e->d_code_tab, d->err, e->n);
+    if (nb && !rdb) encode_kernel<<<(int)std::min<int64_t>((nb_p / 16 + HELPER_THREADS - 1) / HELPER_THREADS, e->sm_count * 16), HELPER_THREADS, 0, hs>>>(d->codes_b, nb, e->d_code_tab, d->err, e->n);
     CUDA_TRY(e, cudaGetLastError());
 
     // ---- routing (one streaming pass over the offsets); the shape sort itself runs on the device
@@ -451,7 +535,12 @@ static int batch_upload_impl(swb_engine *e, const char *a_all, const int64_t *of
     int la_cap = 0, pass_cap = 0;
     int64_t n_k1 = 0, sum_blk = 0, sum_np = 0;                 // K1 pairs, their row-block words and passes (buffer bounds)
     b->cells = 0;
-    for (int64_t k = 0; k < n; ++k) {
+    const bool cached_k2 = rdb && use_k2 && rdb->d_items;      // the routing of a resident database under K2 does not depend on the query
+    if (cached_k2) {
+        d->degenerate = rdb->degenerate;
+        b->cells = (double)shared_la * (double)rdb->n_res;
+    }
+    for (int64_t k = 0; k < n && !cached_k2; ++k) {
         const int64_t la = shared ? shared_la : off_a[k + 1] - off_a[k], lb = off_b[k + 1] - off_b[k];
         if (la < 0 || lb < 0 || la > 0x3FFFFFFF || lb > 0x3FFFFFFF) { e->err = "bad offsets"; return SWB_ERR_ARG; }
         b->la[k] = (int32_t)la; b->lb[k] = (int32_t)lb;
@@ -462,7 +551,10 @@ static int batch_upload_impl(swb_engine *e, const char *a_all, const int64_t *of
             const int np = (int)((lb + K1_STRIP - 1) / K1_STRIP);
             ++n_k1; sum_blk += (la + 1 + 3) / 4 + 1; sum_np += np;
             la_cap = std::max(la_cap, (int)la); pass_cap = std::max(pass_cap, np);
-        } else d->kw_idx.push_back((int32_t)k);
+        } else {
+            if (!swb_range_ok(e, la, lb)) { e->err = "scores of a pair this long do not fit the int32 lanes"; return SWB_ERR_RANGE; }
+            d->kw_idx.push_back((int32_t)k);
+        }
     }
     d->n_k1 = (int)n_k1;
     if (d->n_k1) {
@@ -471,17 +563,21 @@ static int batch_upload_impl(swb_engine *e, const char *a_all, const int64_t *of
         // Upper bounds of the packed blocks: an item is as tall as its longest a and as wide as its widest b.  In the sorted
         // order the excess over the pairs' own sizes telescopes inside a bucket of equal passes; items that straddle two
         // buckets and the last partial item add at most one full item each.
+        // The sort key holds la in steps of la_gran so that the one-block scan over the buckets stays short (long pairs:
+        // 8192 x 256 passes would be 2.1 M buckets); inside a step the order is arbitrary, which costs an item at most
+        // la_gran - 1 extra rows per pair.
+        const int la_gran = (int)(((int64_t)(pass_cap + 1) * (la_cap + 1) + 65535) / 65536);
         const int64_t blk_cap = (la_cap + 1 + 3) / 4 + 1;
-        b->a_bytes = (size_t)(shared ? blk_cap * 128 : 4 * (sum_blk + 32 * blk_cap * (2 * (int64_t)pass_cap + 1)));
+        b->a_bytes = (size_t)(shared ? blk_cap * 128 : 4 * (sum_blk + n_k1 * ((la_gran + 2) / 4 + 1) + 32 * blk_cap * (2 * (int64_t)pass_cap + 1)));
         b->b_bytes = (size_t)(32 * (sum_np + 64 * (int64_t)pass_cap));
-        const int64_t n_buckets = (int64_t)(pass_cap + 1) * (la_cap + 1);
+        const int64_t n_buckets = (int64_t)(pass_cap + 1) * (la_cap / la_gran + 1);
         DEV_ALLOC_ON(e, up, d->sort_cnt, 2 * n_buckets * sizeof(int32_t));       // histogram | cursors
         DEV_ALLOC_ON(e, up, d->sort_sz, 4 * (size_t)ng * sizeof(int64_t));      // asz | bsz | aoff | boff
         DEV_ALLOC_ON(e, up, b->d_a, b->a_bytes + 32 * 16);        // one block of slack: K1 prefetches a row block ahead
         DEV_ALLOC_ON(e, up, b->d_b, b->b_bytes);
         DEV_ALLOC_ON(e, up, b->d_groups, ng * sizeof(K1Group));
         DEV_ALLOC_ON(e, up, b->d_la, d->n_k1 * sizeof(int32_t)); DEV_ALLOC_ON(e, up, b->d_lb, d->n_k1 * sizeof(int32_t));
-        DEV_ALLOC_ON(e, up, b->d_res, n * sizeof(K1Result));
+        if (rdb) { b->d_res = rdb->d_res; d->borrow_res = true; } else DEV_ALLOC_ON(e, up, b->d_res, n * sizeof(K1Result));
         CUDA_TRY(e, join());
         if (n_k1 < n) CUDA_TRY(e, zero_async(b->d_res, n * sizeof(K1Result), hs));      // pairs K1 does not take keep flags == 0
         DEV_ALLOC_ON(e, up, b->d_counter, sizeof(int32_t));
@@ -493,9 +589,9 @@ static int batch_upload_impl(swb_engine *e, const char *a_all, const int64_t *of
         const int nblk = (int)((n + HELPER_THREADS - 1) / HELPER_THREADS);
         CUDA_TRY(e, join());
         CUDA_TRY(e, zero_async(cnt, n_buckets * sizeof(int32_t), hs));
-        sort_count_kernel<false><<<nblk, HELPER_THREADS, 0, hs>>>(d->off_a, d->off_b, n, sla, la_cap, pass_cap, take, cnt, nullptr);
+        sort_count_kernel<false><<<nblk, HELPER_THREADS, 0, hs>>>(d->off_a, d->off_b, n, sla, la_cap, la_gran, pass_cap, take, cnt, nullptr);
         scan_kernel<int32_t><<<1, HELPER_THREADS, 0, hs>>>(cnt, cur, n_buckets);
-        sort_count_kernel<true><<<nblk, HELPER_THREADS, 0, hs>>>(d->off_a, d->off_b, n, sla, la_cap, pass_cap, take, cur, d->order);
+        sort_count_kernel<true><<<nblk, HELPER_THREADS, 0, hs>>>(d->off_a, d->off_b, n, sla, la_cap, la_gran, pass_cap, take, cur, d->order);
         sort_groups_kernel<<<(ng + HELPER_THREADS / 32 - 1) / (HELPER_THREADS / 32), HELPER_THREADS, 0, hs>>>(d->off_a, d->off_b, sla, d->order, d->n_k1, ng, b->d_groups, asz, bsz);
         scan_kernel<int64_t><<<1, HELPER_THREADS, 0, hs>>>(asz, aoff, ng);
         scan_kernel<int64_t><<<1, HELPER_THREADS, 0, hs>>>(bsz, boff, ng);
@@ -506,18 +602,16 @@ static int batch_upload_impl(swb_engine *e, const char *a_all, const int64_t *of
     }
     // ---- K2 work items: subjects of >= 32 passes take a warp each (several sweeps), the others are bin-packed
     //      (first fit, longest first) into warps of 32 lanes, one lane per 32-column pass
-    d->n_k2 = (int)k2_idx.size();
-    if (d->n_k2) {
-        std::vector<std::vector<int32_t>> bucket(32);
-        std::vector<int32_t> longs;
-        for (int32_t k : k2_idx) {
-            const int np = (b->lb[k] + K1_STRIP - 1) / K1_STRIP;
-            if (np >= 32) longs.push_back(k); else bucket[np].push_back(k);
-        }
-        std::sort(longs.begin(), longs.end(), [&](int32_t x, int32_t y) { return b->lb[x] > b->lb[y]; });
-        size_t small_passes = 0; unsigned mask = 0;
-        for (int p = 1; p < 32; ++p) { small_passes += bucket[p].size() * (size_t)p; if (!bucket[p].empty()) mask |= 1u << p; }
-        const size_t cap_items = longs.size() + small_passes / 32 + small_passes / 256 + 64;    // first fit wastes < 12 %
+    d->n_k2 = cached_k2 ? rdb->n_k2 : (int)k2_idx.size();
+    if (cached_k2 && d->n_k2) {
+        d->items = rdb->d_items; d->sweeps = rdb->d_sweeps; d->n_items = rdb->n_items; d->borrow_items = true;
+        b->d_res = rdb->d_res; d->borrow_res = true;
+        CUDA_TRY(e, join());
+        if (d->n_k2 < n) CUDA_TRY(e, zero_async(b->d_res, n * sizeof(K1Result), hs));
+        DEV_ALLOC_ON(e, up, b->d_counter, sizeof(int32_t));
+        { int rc_ = ensure_bnd(e, k2_bnd_bytes(e->sm_count, (int)shared_la)); if (rc_ != SWB_OK) return rc_; }
+    } else if (d->n_k2) {
+        const size_t cap_items = k2_items_cap(b->lb, k2_idx);
         int32_t *h_items = nullptr, *h_sweeps = nullptr;
         const size_t items_bytes = (cap_items * 33) * sizeof(int32_t);
         if (items_bytes > e->items_bytes) {
@@ -529,29 +623,12 @@ static int batch_upload_impl(swb_engine *e, const char *a_all, const int64_t *of
         }
         else if (e->ev_items) CUDA_TRY(e, cudaEventSynchronize(e->ev_items));   // an earlier chunk's copy out of this buffer
         h_items = (int32_t *)e->h_items; h_sweeps = h_items + cap_items * 32;
-        size_t ni = 0;
-        for (int32_t k : longs) {
-            for (int l = 0; l < 32; ++l) h_items[ni * 32 + l] = k;
-            h_sweeps[ni++] = ((b->lb[k] + K1_STRIP - 1) / K1_STRIP + 31) / 32;
-        }
-        while (mask) {
-            int cap = 32, l = 0;
-            if (ni >= cap_items) { e->err = "K2 item table overflow"; return SWB_ERR_NOMEM; }
-            while (cap > 0) {
-                const unsigned fit = mask & ((cap >= 31) ? 0xFFFFFFFFu : ((2u << cap) - 1u));
-                if (!fit) break;
-                const int p = 31 - __builtin_clz(fit);
-                const int32_t k = bucket[p].back(); bucket[p].pop_back();
-                if (bucket[p].empty()) mask &= ~(1u << p);
-                for (int t = 0; t < p; ++t) h_items[ni * 32 + l++] = k;
-                cap -= p;
-            }
-            for (; l < 32; ++l) h_items[ni * 32 + l] = -1;
-            h_sweeps[ni++] = 1;
-        }
+        const int64_t ni_ = k2_build_items(b->lb, k2_idx, h_items, h_sweeps, cap_items);
+        if (ni_ < 0) { e->err = "K2 item table overflow"; return SWB_ERR_NOMEM; }
+        const size_t ni = (size_t)ni_;
         d->n_items = (int)ni;
         DEV_ALLOC_ON(e, up, d->items, ni * 32 * sizeof(int32_t)); DEV_ALLOC_ON(e, up, d->sweeps, ni * sizeof(int32_t));
-        DEV_ALLOC_ON(e, up, b->d_res, n * sizeof(K1Result));
+        if (rdb) { b->d_res = rdb->d_res; d->borrow_res = true; } else DEV_ALLOC_ON(e, up, b->d_res, n * sizeof(K1Result));
         CUDA_TRY(e, join());
         if (d->n_k2 < n) CUDA_TRY(e, zero_async(b->d_res, n * sizeof(K1Result), hs));
         DEV_ALLOC_ON(e, up, b->d_counter, sizeof(int32_t));
@@ -579,6 +656,11 @@ static int batch_upload_impl(swb_engine *e, const char *a_all, const int64_t *of
         DEV_ALLOC_ON(e, up, d->kw_scr, d->kw_plan_.scratch_ints * sizeof(int));
         CUDA_TRY(e, cudaMemcpyAsync(d->kw_pairs, d->h_kw.data(), d->n_kw * sizeof(KWPair), cudaMemcpyHostToDevice, up));
         e->stats.h2d_bytes += (double)d->n_kw * sizeof(KWPair);
+    }
+    if (rdb && !b->d_res) {                                    // KW-only routing (non-local modes, open < extend): results are collected into the database's array
+        b->d_res = rdb->d_res; d->borrow_res = true;
+        CUDA_TRY(e, join());
+        CUDA_TRY(e, zero_async(b->d_res, n * sizeof(K1Result), hs));
     }
     CUDA_TRY(e, cudaEventCreate(&d->ev0)); CUDA_TRY(e, cudaEventCreate(&d->ev1));
     CUDA_TRY(e, cudaEventCreateWithFlags(&d->ev_done, cudaEventDisableTiming));
@@ -629,7 +711,7 @@ extern "C" int swb_batch_upload(swb_engine *e, const char *a_all, const int64_t 
     return SWB_OK;
 }
 
-static int batch_launch(swb_engine *e, swb_batch *b, int64_t *launches)
+int batch_launch(swb_engine *e, swb_batch *b, int64_t *launches)
 {
     BatchDev *d = b->dev;
     cudaStream_t st = kstream(e, b);

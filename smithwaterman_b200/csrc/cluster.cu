@@ -84,6 +84,9 @@ extern "C" int swb_cluster(swb_engine *e, const char *seq_all, const int64_t *of
     }
     std::iota(order, order + n, (int64_t)0);
     std::stable_sort(order, order + n, [&](int64_t x, int64_t y) { return len[x] > len[y]; });
+    if (!swb_range_ok(e, len[order[0]], n > 1 ? len[order[1]] : len[order[0]])) {     // the two longest: the largest pair the loop can form
+        e->err = "scores of a pair this long do not fit the int32 lanes"; return SWB_ERR_RANGE;
+    }
     // ---- the sequences in sorted order: letters as given + encoded, resident on the device for the whole run
     std::vector<int64_t> so(n + 1, 0);
     for (int64_t k = 0; k < n; ++k) so[k + 1] = so[k] + len[order[k]];

@@ -8,7 +8,7 @@
 
 #include "swb_internal.h"
 
-static std::string g_create_err;
+static thread_local std::string g_create_err;      // per thread: distinct engines may be created concurrently
 
 // BLOSUM62 as published by NCBI (the table the reference embeds at SA.rs:706-730), letter order
 // A R N D C Q E G H I L K M F P S T W Y V B Z X *.
@@ -176,6 +176,7 @@ extern "C" void swb_engine_destroy(swb_engine *e)
     if (e->h_items) cudaFreeHost(e->h_items);
     if (e->h_tb) cudaFreeHost(e->h_tb);
     if (e->ev_items) cudaEventDestroy(e->ev_items);
+    if (e->ev_team) cudaEventDestroy(e->ev_team);
     if (e->ev0) cudaEventDestroy(e->ev0);
     if (e->ev1) cudaEventDestroy(e->ev1);
     if (e->stream) cudaStreamDestroy(e->stream);

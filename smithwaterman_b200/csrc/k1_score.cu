@@ -45,6 +45,10 @@ constexpr int kBlkUnroll = K1_BLK_UNROLL;
 #ifndef K1_NOTRACK
 #define K1_NOTRACK 0
 #endif
+// K1_VOTE=1: the per-row improvement test becomes a warp-uniform branch (VOTE.ANY + BRA.U, no BSSY/BSYNC pair per row).
+#ifndef K1_VOTE
+#define K1_VOTE 0
+#endif
 
 // One packed cell-vector.  The only loop-carried dependency along k is the single VIADDMNMX of E:
 //   G  = max(Hdiag + s, F, 0)                 (independent of the row chain)
@@ -173,7 +177,11 @@ k1_local_kernel(const uint8_t *__restrict__ a_pk, const uint8_t *__restrict__ b_
 #if K1_NOTRACK == 1
                     thr2 = rm;      // timing experiment only: no end cell
 #else
+#if K1_VOTE
+                    if (__any_sync(0xffffffffu, rm != thr2)) {
+#else
                     if (rm != thr2) {
+#endif
                         // Rare path (the running best of some lane improves).  Only the row and the half are decided
                         // here; the 16 packed Ho words of the step are parked in shared memory (16 STS of the lanes
                         // that improved; scalar stores: vector stores made the compiler shuffle Ho into aligned quads in the hot path) and the column is read off them once, after the last pass.

@@ -20,6 +20,11 @@
 // SA.rs:354-357) are stored step-major: the warp writes 32*KW_C contiguous bytes per step.
 #include <algorithm>
 #include <cstdlib>
+#include <map>
+#include <mutex>
+#include <tuple>
+
+#include <cuda/atomic>
 
 #include "swb_internal.h"
 
@@ -66,11 +71,14 @@ __device__ __forceinline__ void kw_cell(int hd, unsigned amd, int tM, int tX, in
 // Team scheduling: a pair is swept by a TEAM of T warps (T = 1 for batches of many pairs; up to several hundred for a
 // few long pairs).  Warp w of the team takes the column strips w, w+T, w+2T, ...; strip s consumes the last column of
 // strip s-1 row by row through a ring of T+1 column buffers in global memory (L2 resident) guarded by a per-strip
-// progress counter (rows published, release/acquire through __threadfence + volatile accesses).  Waits only ever point
-// to a lower strip, so there is no cycle; the launcher sizes the grid so that every warp of every team is resident.
+// progress counter (rows published: a release store of cuda::atomic_ref<int, thread_scope_device> after the rows are
+// written, an acquire load before they are read -- not the fence-less spinning of the reference, OCL.rs:374-376).  Waits
+// only ever point to a lower strip, so there is no cycle, and every warp of every team is resident: team launches are
+// COOPERATIVE launches (an oversubscribed grid is an error, not a hang), sized from the occupancy of the exact
+// instantiation that is launched, and serialised among themselves through the engine's team event.
 // C = columns per lane (strip width 32*C): 8 for batches (fewest instructions per cell), 2 when a few long pairs must be
 // spread over many warps (the per-step dependency chain, not the issue rate, bounds a lone warp).
-__device__ __forceinline__ int ld_volatile(const int *p) { return *reinterpret_cast<const volatile int *>(p); }
+typedef cuda::atomic_ref<int, cuda::thread_scope_device> kw_flag;
 
 template <int C> struct KWCodes;
 template <> struct KWCodes<8> { typedef unsigned long long T; };
@@ -159,8 +167,8 @@ kw_kernel(const uint8_t *__restrict__ a_all, const uint8_t *__restrict__ b_all, 
                     if (wait_prev && t < la) {                 // rows t+1 .. t+32 are consumed by lane 0 in the next 32 steps
                         const int need = min(la, t + 32);
                         if (lane == 0) {
-                            while (ld_volatile(prog + sidx - 1) < need) __nanosleep(32);
-                            __threadfence();
+                            kw_flag f(prog[sidx - 1]);
+                            while (f.load(cuda::memory_order_acquire) < need) __nanosleep(32);
                         }
                     }
                     __syncwarp();
@@ -228,10 +236,8 @@ kw_kernel(const uint8_t *__restrict__ a_all, const uint8_t *__restrict__ b_all, 
                     }
                     if (lane == 31 && sidx + 1 < n_strips) {
                         bnd_out[i] = make_int4(lastM, lastX, lastY, 0);
-                        if (team_warps > 1 && ((i & 31) == 0 || i == la)) {       // publish rows 1..i of this strip's last column
-                            __threadfence();
-                            *reinterpret_cast<volatile int *>(prog + sidx) = i;
-                        }
+                        if (team_warps > 1 && ((i & 31) == 0 || i == la))         // publish rows 1..i of this strip's last column
+                            kw_flag(prog[sidx]).store(i, cuda::memory_order_release);
                     }
                     if (DIRS) *reinterpret_cast<codes_t *>(dstrip + (int64_t)t * SW) = codes;
                 }
@@ -257,15 +263,14 @@ kw_kernel(const uint8_t *__restrict__ a_all, const uint8_t *__restrict__ b_all, 
                 int arrived = 0;
                 if (lane == 0) {
                     cand[w * 4 + 0] = best; cand[w * 4 + 1] = bi; cand[w * 4 + 2] = bj;
-                    __threadfence();
-                    arrived = atomicAdd(counter, 1);
+                    arrived = kw_flag(*counter).fetch_add(1, cuda::memory_order_acq_rel);   // releases this warp's candidate, acquires the earlier ones
                 }
                 arrived = __shfl_sync(0xffffffffu, arrived, 0);
+                __syncwarp();
                 if (arrived == team_warps - 1) {                                  // last warp of the team: merge the candidates
-                    __threadfence();
                     int cb = 0, ci = -1, cj = -1;
                     for (int k = lane; k < team_warps; k += 32) {
-                        const int ob = ld_volatile(cand + k * 4), oi = ld_volatile(cand + k * 4 + 1), oj = ld_volatile(cand + k * 4 + 2);
+                        const int ob = __ldcg(cand + k * 4), oi = __ldcg(cand + k * 4 + 1), oj = __ldcg(cand + k * 4 + 2);
                         if (ob > cb || (ob == cb && ob > 0 && (oi < ci || (oi == ci && oj < cj)))) { cb = ob; ci = oi; cj = oj; }
                     }
 #pragma unroll
@@ -293,26 +298,41 @@ kw_kernel(const uint8_t *__restrict__ a_all, const uint8_t *__restrict__ b_all, 
 }
 
 // Host-side plan: columns per lane, team size, grid, scratch and direction-byte offsets.  Fills bnd_off / scr_off /
-// dir_off of the pairs.  Resident blocks per SM: minimum over all instantiations (teams spin on each other, so every
-// block of a team launch must be resident at once; the value is queried from the runtime, not assumed).
-#define KW_FOR_MODES(X, C) X(SWB_GLOBAL, true, C) X(SWB_GLOBAL, false, C) X(SWB_GLOCAL, true, C) X(SWB_GLOCAL, false, C) \
-    X(SWB_LOCAL, true, C) X(SWB_LOCAL, false, C)
+// dir_off of the pairs.  Teams spin on each other, so every block of a team launch must be resident at once: the
+// resident blocks per SM are those of the EXACT instantiation that will be launched (mode, direction bytes, strip
+// width, band form -- their register counts differ), queried from the runtime per device, and the launch is cooperative.
+template <int MODE, bool DIRS, int C, bool BAND>
+static const void *kw_fn() { return reinterpret_cast<const void *>(&kw_kernel<MODE, DIRS, C, BAND>); }
 
-static int kw_blocks_per_sm(const swb_engine *e, int cols)
+static const void *kw_pick(int mode, bool dirs, int cols, bool band)
 {
-    static int cached[2][64] = {{0}};
-    const int nl = e->n + 1, which = (cols == 2) ? 1 : 0;
-    if (cached[which][nl]) return cached[which][nl];
-    const size_t smem = (size_t)nl * nl * sizeof(int);
-    int best = 1 << 30, v = 0;
-#define KW_OCC(M, D, C) if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&v, kw_kernel<M, D, C, false>, KW_WARPS * 32, smem) == cudaSuccess) best = std::min(best, v); else best = 0;
-    if (which) { KW_FOR_MODES(KW_OCC, 2) } else { KW_FOR_MODES(KW_OCC, 8) }
-#undef KW_OCC
-    cached[which][nl] = std::max(1, std::min(best, 8));
-    return cached[which][nl];
+#define KW_P(M) (dirs ? (cols == 2 ? (band ? kw_fn<M, true, 2, true>() : kw_fn<M, true, 2, false>()) : (band ? kw_fn<M, true, 8, true>() : kw_fn<M, true, 8, false>())) \
+                      : (cols == 2 ? (band ? kw_fn<M, false, 2, true>() : kw_fn<M, false, 2, false>()) : (band ? kw_fn<M, false, 8, true>() : kw_fn<M, false, 8, false>())))
+    switch (mode) {
+    case SWB_GLOBAL: return KW_P(SWB_GLOBAL);
+    case SWB_GLOCAL: return KW_P(SWB_GLOCAL);
+    default: return KW_P(SWB_LOCAL);
+    }
+#undef KW_P
 }
 
-void kw_plan(const swb_engine *e, KWPair *pairs, int n_pairs, bool with_dirs, KWPlan *plan, int force_cols)
+int kw_blocks_per_sm(const swb_engine *e, int cols, bool dirs, bool band)
+{
+    static std::mutex mu;
+    static std::map<std::tuple<int, int, int, int, int, int>, int> cache;       // (device, mode, dirs, cols, band, nl)
+    const int nl = e->n + 1;
+    const auto key = std::make_tuple(e->device, e->mode, (int)dirs, cols == 2 ? 2 : 8, (int)band, nl);
+    std::lock_guard<std::mutex> lk(mu);
+    auto it = cache.find(key);
+    if (it != cache.end()) return it->second;
+    int v = 0;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&v, kw_pick(e->mode, dirs, cols == 2 ? 2 : 8, band), KW_WARPS * 32, (size_t)nl * nl * sizeof(int)) != cudaSuccess) { cudaGetLastError(); v = 1; }
+    v = std::max(1, std::min(v, 8));
+    cache[key] = v;
+    return v;
+}
+
+void kw_plan(const swb_engine *e, KWPair *pairs, int n_pairs, bool with_dirs, KWPlan *plan, int force_cols, bool band)
 {
     // Strip width.  Score only: 8 columns per lane -- with whole-round teams (cost model below) a step of 8 cells per lane
     // costs the same 0.44 us as a step of 2 (the step is bound by its shuffle / staging latency), so the wide strip wins:
@@ -320,10 +340,10 @@ void kw_plan(const swb_engine *e, KWPair *pairs, int n_pairs, bool with_dirs, KW
     // latency-bound (0.71 us vs 0.51 us per step): a few long pairs then run better on 2-column strips and 4x the warps.
     int64_t strips8 = 0;
     for (int k = 0; k < n_pairs; ++k) strips8 += (pairs[k].lb + 255) / 256;
-    int cols = (with_dirs && n_pairs > 0 && strips8 * 3 < e->sm_count * kw_blocks_per_sm(e, 8) * KW_WARPS) ? 2 : 8;
+    int cols = (with_dirs && n_pairs > 0 && strips8 * 3 < e->sm_count * kw_blocks_per_sm(e, 8, with_dirs, band) * KW_WARPS) ? 2 : 8;
     if (force_cols == 2 || force_cols == 8) cols = force_cols;
     if (const char *f = getenv("SWB_KW_COLS")) { if (atoi(f) == 2) cols = 2; else if (atoi(f) == 8) cols = 8; }   // tests force both widths
-    const int capacity = e->sm_count * kw_blocks_per_sm(e, cols) * KW_WARPS;   // warps that are guaranteed to be co-resident
+    const int capacity = e->sm_count * kw_blocks_per_sm(e, cols, with_dirs, band) * KW_WARPS;   // warps that a cooperative launch keeps co-resident
     const int sw = 32 * cols;
     int T = 1;
     if (n_pairs > 0 && n_pairs < capacity / 4) {
@@ -364,24 +384,44 @@ void kw_plan(const swb_engine *e, KWPair *pairs, int n_pairs, bool with_dirs, KW
     plan->dir_bytes = dirb;
 }
 
-template <int MODE, int C>
-static cudaError_t kw_launch_mode(const swb_engine *e, const uint8_t *d_a, const uint8_t *d_b, const KWPair *d_pairs,
-                                  int n_pairs, const KWPlan &pl, uint8_t *d_dir, int4 *d_bnd, int *d_scratch,
-                                  KWResult *d_res, cudaStream_t st, const int32_t *d_pssm)
+// Team launches (team_warps > 1) are cooperative: the runtime refuses a grid that cannot be resident at once (instead of
+// letting its warps wait for blocks that are never scheduled), and they are chained through the engine's team event so
+// that two of them never share the GPU, whatever streams they were issued on.
+template <int MODE, bool DIRS, int C, bool BAND>
+static cudaError_t kw_go(const swb_engine *e, const uint8_t *d_a, const uint8_t *d_b, const KWPair *d_pairs, int n_pairs,
+                         const KWPlan &pl, const KWBand &band, uint8_t *d_dir, int4 *d_bnd, int *d_scratch, KWResult *d_res,
+                         cudaStream_t st, const int32_t *d_pssm)
 {
     const int nl = e->n + 1;
     const size_t smem = (size_t)nl * nl * sizeof(int);
     cudaError_t err = cudaMemsetAsync(d_scratch, 0, (size_t)pl.scratch_ints * sizeof(int), st);
     if (err != cudaSuccess) return err;
-    if (d_dir)
-        kw_kernel<MODE, true, C, false><<<pl.blocks, KW_WARPS * 32, smem, st>>>(d_a, d_b, d_pairs, n_pairs, pl.team_warps, pl.n_teams,
-                                                                                e->d_mat, nl, e->o, e->e, e->scale, d_dir, d_bnd,
-                                                                                d_scratch, d_res, d_pssm, KWBand());
-    else
-        kw_kernel<MODE, false, C, false><<<pl.blocks, KW_WARPS * 32, smem, st>>>(d_a, d_b, d_pairs, n_pairs, pl.team_warps, pl.n_teams,
-                                                                                 e->d_mat, nl, e->o, e->e, e->scale, d_dir, d_bnd,
-                                                                                 d_scratch, d_res, d_pssm, KWBand());
-    return cudaGetLastError();
+    if (pl.team_warps <= 1) {
+        kw_kernel<MODE, DIRS, C, BAND><<<pl.blocks, KW_WARPS * 32, smem, st>>>(d_a, d_b, d_pairs, n_pairs, pl.team_warps, pl.n_teams, e->d_mat, nl,
+                                                                             e->o, e->e, e->scale, d_dir, d_bnd, d_scratch, d_res, d_pssm, band);
+        return cudaGetLastError();
+    }
+    if (pl.blocks > e->sm_count * kw_blocks_per_sm(e, C, DIRS, BAND)) return cudaErrorCooperativeLaunchTooLarge;
+    swb_engine *me = const_cast<swb_engine *>(e);
+    if (!me->ev_team) { if ((err = cudaEventCreateWithFlags(&me->ev_team, cudaEventDisableTiming)) != cudaSuccess) return err; }
+    else if ((err = cudaStreamWaitEvent(st, me->ev_team, 0)) != cudaSuccess) return err;
+    int team_warps = pl.team_warps, n_teams = pl.n_teams, o = e->o, ee = e->e, unit = e->scale, nl_ = nl;
+    const int32_t *mat = e->d_mat;
+    KWBand bnd_arg = band;
+    void *args[] = {(void *)&d_a, (void *)&d_b, (void *)&d_pairs, (void *)&n_pairs, (void *)&team_warps, (void *)&n_teams, (void *)&mat, (void *)&nl_,
+                    (void *)&o, (void *)&ee, (void *)&unit, (void *)&d_dir, (void *)&d_bnd, (void *)&d_scratch, (void *)&d_res, (void *)&d_pssm, (void *)&bnd_arg};
+    err = cudaLaunchCooperativeKernel(reinterpret_cast<const void *>(&kw_kernel<MODE, DIRS, C, BAND>), dim3(pl.blocks), dim3(KW_WARPS * 32), args, smem, st);
+    if (err != cudaSuccess) return err;
+    return cudaEventRecord(me->ev_team, st);
+}
+
+template <int MODE, int C>
+static cudaError_t kw_launch_mode(const swb_engine *e, const uint8_t *d_a, const uint8_t *d_b, const KWPair *d_pairs,
+                                  int n_pairs, const KWPlan &pl, uint8_t *d_dir, int4 *d_bnd, int *d_scratch,
+                                  KWResult *d_res, cudaStream_t st, const int32_t *d_pssm)
+{
+    if (d_dir) return kw_go<MODE, true, C, false>(e, d_a, d_b, d_pairs, n_pairs, pl, KWBand(), d_dir, d_bnd, d_scratch, d_res, st, d_pssm);
+    return kw_go<MODE, false, C, false>(e, d_a, d_b, d_pairs, n_pairs, pl, KWBand(), d_dir, d_bnd, d_scratch, d_res, st, d_pssm);
 }
 
 template <int MODE, int C>
@@ -389,17 +429,8 @@ static cudaError_t kw_launch_band_mode(const swb_engine *e, const uint8_t *d_a, 
                                        const KWPlan &pl, const KWBand &band, uint8_t *d_dir, int4 *d_bnd, int *d_scratch,
                                        KWResult *d_res, cudaStream_t st)
 {
-    const int nl = e->n + 1;
-    const size_t smem = (size_t)nl * nl * sizeof(int);
-    cudaError_t err = cudaMemsetAsync(d_scratch, 0, (size_t)pl.scratch_ints * sizeof(int), st);
-    if (err != cudaSuccess) return err;
-    if (d_dir)
-        kw_kernel<MODE, true, C, true><<<pl.blocks, KW_WARPS * 32, smem, st>>>(d_a, d_b, d_pair, 1, pl.team_warps, pl.n_teams, e->d_mat, nl,
-                                                                               e->o, e->e, e->scale, d_dir, d_bnd, d_scratch, d_res, nullptr, band);
-    else
-        kw_kernel<MODE, false, C, true><<<pl.blocks, KW_WARPS * 32, smem, st>>>(d_a, d_b, d_pair, 1, pl.team_warps, pl.n_teams, e->d_mat, nl,
-                                                                                e->o, e->e, e->scale, d_dir, d_bnd, d_scratch, d_res, nullptr, band);
-    return cudaGetLastError();
+    if (d_dir) return kw_go<MODE, true, C, true>(e, d_a, d_b, d_pair, 1, pl, band, d_dir, d_bnd, d_scratch, d_res, st, nullptr);
+    return kw_go<MODE, false, C, true>(e, d_a, d_b, d_pair, 1, pl, band, d_dir, d_bnd, d_scratch, d_res, st, nullptr);
 }
 
 cudaError_t kw_launch_band(const swb_engine *e, const uint8_t *d_a, const uint8_t *d_b, const KWPair *d_pair,

@@ -47,6 +47,7 @@ struct swb_engine {
     cudaStream_t stream2 = nullptr;     // second compute stream: odd chunks of the pipelined host-buffer path
     cudaStream_t stream_up = nullptr;   // upload stream of the pipelined host-buffer path (allocations, H2D, encode, sort, pack)
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    cudaEvent_t ev_team = nullptr;      // completion of the last team (cooperative) wavefront launch: team launches are chained through it
     int sm_count = 0;
     int32_t *d_mat = nullptr;       // (n+1)*(n+1) int32 scaled, PAD row/col included
     int16_t *d_code_tab = nullptr;  // byte -> residue code (device copy of code_of)
@@ -78,6 +79,29 @@ struct swb_batch {
     int32_t la_max = 0;
     float last_ms = 0; int64_t last_launches = 0;
     double cells = 0;
+};
+
+// A database (shard) resident on the device: encoded once, searched many times (search.cu; swb_db_upload / swb_search).
+struct swb_db {
+    int device = 0;
+    int64_t n = 0, n_res = 0;
+    std::vector<char> h_letters;            // the letters as given (host copy: the strings of the hits are spelled from it)
+    std::vector<int64_t> h_off;             // n + 1 offsets into h_letters / d_codes
+    std::vector<int64_t> h_gidx;            // caller (global) index of every subject, ascending
+    std::vector<int32_t> lb;                // subject lengths
+    std::vector<int32_t> degenerate;        // subjects of length 0
+    uint8_t *d_codes = nullptr;             // encoded residues (PAD-filled slack of 32 bytes)
+    int64_t *d_off = nullptr;
+    int64_t *d_gidx = nullptr;
+    // K2 work items (first-fit packing of the subjects' 32-column passes into warps), built once per database
+    int32_t *d_items = nullptr, *d_sweeps = nullptr;
+    int n_items = 0, n_k2 = 0;
+    // per-search scratch, kept between searches
+    K1Result *d_res = nullptr;              // score / end cell / flags per subject (local index)
+    uint8_t *d_query = nullptr; int64_t query_cap = 0;
+    void *d_sel = nullptr;                  // top-K selection state + keys
+    void *h_hits = nullptr;                 // pinned: the hits of the last search + counters
+    int64_t last_lq = -1;                   // query length of the last search (its scores are in d_res)
 };
 
 #define CUDA_TRY(e_, call)                                                                      \
@@ -118,7 +142,8 @@ struct KWPlan {
     int64_t scratch_ints = 0;       // progress counters + candidates of all pairs
     int64_t dir_bytes = 0;          // direction bytes of all pairs (with_dirs)
 };
-void kw_plan(const swb_engine *e, KWPair *pairs, int n_pairs, bool with_dirs, KWPlan *plan, int force_cols = 0);   // also assigns dir_off
+void kw_plan(const swb_engine *e, KWPair *pairs, int n_pairs, bool with_dirs, KWPlan *plan, int force_cols = 0, bool band = false);   // also assigns dir_off
+int kw_blocks_per_sm(const swb_engine *e, int cols, bool dirs, bool band);   // resident blocks per SM of the exact instantiation (runtime query, per device)
 struct KWResult {
     int32_t score;                  // scaled
     int32_t end_i, end_j;           // start cell of the traceback (1-based), -1 = empty
@@ -165,6 +190,35 @@ cudaError_t kt_stats_launch(const swb_engine *e, const KWPair *d_pairs, const KW
 
 // The statistics of the strings align(.., retain_all) would return, from the core alignment's counts (align.cu).
 void swb_compose_stats(swb_aln_stats *o, int mode, bool retain_all, int64_t la, int64_t lb, const KTStats &S);
+
+// ---- batch path internals shared with the search driver (batch.cu) ------------------------------------------------
+// Upload / prepare one batch.  rdb != nullptr: the `b` side is the resident database (nothing is copied or encoded, the
+// cached routing and K2 work items are used); a_all then is the query (shared_la >= 0).
+int batch_upload_impl(swb_engine *e, const char *a_all, const int64_t *off_a, const char *b_all, const int64_t *off_b,
+                      int64_t n, int64_t shared_la, bool use_arena, cudaStream_t up, cudaStream_t hs, swb_batch **out,
+                      const swb_db *rdb = nullptr);
+int batch_launch(swb_engine *e, swb_batch *b, int64_t *launches);
+void batch_release(swb_engine *e, swb_batch *b);
+// K2 work items of a set of subjects (host, first fit, longest first); returns the number of items, fills items[32*cap], sweeps[cap]
+size_t k2_items_cap(const std::vector<int32_t> &lb, const std::vector<int32_t> &idx);
+int64_t k2_build_items(const std::vector<int32_t> &lb, const std::vector<int32_t> &idx, int32_t *h_items, int32_t *h_sweeps, size_t cap_items);
+// unified per-subject results of a launched batch (K1 / K2 write b->d_res directly; this adds the KW pairs)
+cudaError_t batch_collect_kw(swb_engine *e, swb_batch *b, cudaStream_t st);
+int batch_device_views(swb_batch *b, const uint8_t **codes_a, const uint8_t **codes_b);
+
+cudaError_t batch_encode(swb_engine *e, uint8_t *d_buf, int64_t nbytes, int32_t *d_err, cudaStream_t st);   // letters -> codes in place (buffer padded to 16 B)
+
+// ---- traceback core shared by swb_align_batch and the search driver (align.cu) -----------------------------------------
+struct AlnJob {
+    int64_t a_off, b_off;           // offsets into the device code arrays (and the position-specific table when given)
+    int32_t la, lb;                 // DP extents handed to the kernels
+    const char *ra, *rb;            // letters as given
+    int64_t la_full, lb_full;       // lengths of the whole sequences (retain_all padding, SA.rs:512-549)
+    int64_t out;                    // index into outs / souts
+};
+int align_jobs_device(swb_engine *e, const uint8_t *d_a, const uint8_t *d_b, const std::vector<AlnJob> &jobs, bool retain_all,
+                      swb_alignment *outs, swb_aln_stats *souts, const int32_t *d_pssm, const uint8_t *d_ra, const uint8_t *d_rb);
+bool swb_range_ok(const swb_engine *e, int64_t la, int64_t lb, int64_t smax_abs = -1);   // do the scores of a pair fit the int32 lanes of KW?
 
 // K0
 cudaError_t k0_run(int which, int sm_count, double *thread_instr_per_s);

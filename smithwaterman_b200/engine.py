@@ -227,12 +227,22 @@ class SequenceAlignment:
 
     def align_partial(self, s1, s2, retain_all, partial_region=None, score_only=False):
         a, b = _as_seq_bytes(s1), _as_seq_bytes(s2)
-        if partial_region is not None:                        # prefixes only (SA.rs:396-399)
-            a, b = a[:partial_region[0]], b[:partial_region[1]]
+        if self._pssm or (partial_region is None and not score_only):
+            if partial_region is not None:
+                a, b = a[:partial_region[0]], b[:partial_region[1]]
+            res = self.align_raw(a, b, retain_all)
+            return ([], [], res["score"]) if score_only else (list(res["aln_a"]), list(res["aln_b"]), res["score"])
+        # the DP runs on the prefixes (SA.rs:396-405), the padding spells the whole sequences (SA.rs:512-549)
+        pa, pb = (len(a), len(b)) if partial_region is None else (int(partial_region[0]), int(partial_region[1]))
+        out = _lib.Alignment()
+        self._check(self.L.swb_align_partial(self._h, a, len(a), b, len(b), pa, pb, int(bool(retain_all)), int(bool(score_only)),
+                                             ctypes.byref(out)))
+        try:
+            res = self._unpack(out)
+        finally:
+            self.L.swb_alignment_free(ctypes.byref(out))
         if score_only:                                        # SA.rs:438-467
-            sc, _, _ = self.score_batch([a], [b])
-            return [], [], float(sc[0])
-        res = self.align_raw(a, b, retain_all)
+            return [], [], res["score"]
         return list(res["aln_a"]), list(res["aln_b"]), res["score"]
 
     def align_raw(self, a, b, retain_all=True):

@@ -8,15 +8,21 @@ OCL-main.rs:295-316: every `sw.align(ss1, ss2, true)` of one query file against 
 
 Sharding: subjects are dealt round-robin over the length-sorted order, so every rank sees the same
 length mix and nearly the same number of DP cells; shards are independent, the only exchange is one all-gather of the
-per-rank top-K records (K x 24 bytes).  Ties are broken by (score desc, database index asc), which makes the result
+per-rank top-K records (K x 32 bytes).  Ties are broken by (score desc, database index asc), which makes the result
 independent of the number of ranks.
+
+The driver itself is native (csrc/search.cu behind include/swb200.h): `DeviceDatabase` is a shard resident on the GPU
+(swb_db_upload_shard), `swb_search` scans, re-runs s16 overflows and selects the top-K on the device, `swb_search_merge`
+merges the per-rank lists and `swb_search_align` traces the hits the shard owns.  This module is the thin caller that
+adds the torch.distributed collectives; a C / Rust caller does the same with swb_search_sharded or its own gather.
 """
 import ctypes
 import os
 
 import numpy as np
 
-from .engine import SequenceAlignment, _ptr, pack_sequences
+from . import _lib
+from .engine import SequenceAlignment, SwbError, _ptr, pack_sequences
 
 
 class Database:
@@ -126,14 +132,102 @@ class Database:
 
 
 def shard_indices(lengths, world_size, order=None):
-    """Round-robin deal over the length-sorted order (stable, longest first): list of index arrays, one per rank."""
+    """Round-robin deal over the length-sorted order (stable, longest first): list of index arrays, one per rank.
+    (The same deal as swb_db_shard in the library; tests/test_search_dist_cpu.py holds them equal.)"""
     if order is None:
         order = np.argsort(-np.asarray(lengths, np.int64), kind="stable")
     return [np.sort(order[r::world_size]) for r in range(world_size)]
 
 
+def native_shard_indices(offsets, rank, world_size):
+    """swb_db_shard: the index list of shard `rank` (host only, no device needed)."""
+    off = np.ascontiguousarray(offsets, np.int64)
+    n = len(off) - 1
+    idx = np.empty(max(n, 1), np.int64)
+    m = ctypes.c_int64(0)
+    rc = _lib.lib().swb_db_shard(off.ctypes.data, n, int(rank), int(world_size), idx.ctypes.data, ctypes.byref(m))
+    if rc:
+        raise SwbError(rc, "swb_db_shard: bad argument")
+    return idx[:m.value].copy()
+
+
+HIT_DTYPE = np.dtype(_lib.HIT_DTYPE)
+
+
+def merge_hits(parts, k):
+    """swb_search_merge: global top-k of per-shard hit arrays (HIT_DTYPE); key (score desc, database index asc)."""
+    allh = np.ascontiguousarray(np.concatenate(parts)) if len(parts) else np.zeros(0, HIT_DTYPE)
+    out = np.zeros(max(int(k), 1), HIT_DTYPE)
+    m = ctypes.c_int64(0)
+    rc = _lib.lib().swb_search_merge(allh.ctypes.data, len(allh), int(k), out.ctypes.data, ctypes.byref(m))
+    if rc:
+        raise SwbError(rc, "swb_search_merge: bad argument")
+    return out[:m.value].copy()
+
+
+class DeviceDatabase:
+    """A database shard resident on the engine's GPU (swb_db): encoded once, searched many times."""
+
+    def __init__(self, engine, db, rank=0, world_size=1, global_index=None):
+        self.engine, self.h = engine, ctypes.c_void_p()
+        L = engine.L
+        res = np.ascontiguousarray(db.residues)
+        off = np.ascontiguousarray(db.offsets, np.int64)
+        if global_index is not None:                          # `db` already is the shard; global_index ascending
+            gi = np.ascontiguousarray(global_index, np.int64)
+            engine._check(L.swb_db_upload(engine._h, _ptr(res), _ptr(off), db.n, _ptr(gi), ctypes.byref(self.h)))
+        elif world_size > 1:
+            engine._check(L.swb_db_upload_shard(engine._h, _ptr(res), _ptr(off), db.n, int(rank), int(world_size), ctypes.byref(self.h)))
+        else:
+            engine._check(L.swb_db_upload(engine._h, _ptr(res), _ptr(off), db.n, None, ctypes.byref(self.h)))
+        self.n = L.swb_db_count(self.h)
+        self.residues = L.swb_db_residues(self.h)
+
+    def search(self, query, topk=100):
+        """Local top-k of this shard -> numpy record array (HIT_DTYPE), sorted by (score desc, index asc)."""
+        q = query if isinstance(query, (bytes, bytearray)) else query.encode("latin-1")
+        hits = np.zeros(max(int(topk), 1), HIT_DTYPE)
+        m = ctypes.c_int64(0)
+        self.engine._check(self.engine.L.swb_search(self.engine._h, bytes(q), len(q), self.h, int(topk), hits.ctypes.data, ctypes.byref(m)))
+        return hits[:m.value]
+
+    def scores(self):
+        """Full score vector of the last search, local subject order (tests / cross-checks)."""
+        sc = np.empty(self.n, np.float32); eq = np.empty(self.n, np.int64); et = np.empty(self.n, np.int64)
+        self.engine._check(self.engine.L.swb_db_scores(self.engine._h, self.h, _ptr(sc), _ptr(eq), _ptr(et)))
+        return sc, eq, et
+
+    def align(self, query, hits, retain_all=False):
+        """Traceback of the hits this shard owns -> {position in `hits`: alignment dict}."""
+        q = query if isinstance(query, (bytes, bytearray)) else query.encode("latin-1")
+        hits = np.ascontiguousarray(hits, HIT_DTYPE)
+        n = len(hits)
+        outs = (_lib.Alignment * max(n, 1))()
+        owned = np.zeros(max(n, 1), np.int32)
+        self.engine._check(self.engine.L.swb_search_align(self.engine._h, bytes(q), len(q), self.h, hits.ctypes.data, n,
+                                                          1 if retain_all else 0, outs, owned.ctypes.data))
+        try:
+            return {k: SequenceAlignment._unpack(outs[k]) for k in range(n) if owned[k]}
+        finally:
+            for k in range(n):
+                self.engine.L.swb_alignment_free(ctypes.byref(outs[k]))
+
+    def free(self):
+        if self.h is not None and self.h.value:
+            self.engine.L.swb_db_free(self.engine._h, self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            if self.engine._h is not None:
+                self.free()
+        except Exception:
+            pass
+
+
 def topk_records(scores, idx, end_q, end_t, k):
-    """Top-k by (score desc, database index asc) -> structured array."""
+    """Top-k by (score desc, database index asc) -> structured array (host restatement of the device selection: the CPU
+    tests of the multi-rank logic and the cross-checks of the GPU tests use it)."""
     scores = np.asarray(scores, np.float32)
     n = len(scores)
     if n > 4 * k > 0:                                         # linear-time selection first: everything scoring >= the k-th value
@@ -141,45 +235,34 @@ def topk_records(scores, idx, end_q, end_t, k):
         sel = np.nonzero(scores >= kth)[0]
     else:
         sel = np.arange(n)
-    rec = np.empty(len(sel), dtype=[("score", np.float32), ("idx", np.int64), ("end_q", np.int64), ("end_t", np.int64)])
-    rec["score"], rec["idx"], rec["end_q"], rec["end_t"] = scores[sel], np.asarray(idx)[sel], np.asarray(end_q)[sel], np.asarray(end_t)[sel]
-    order = np.lexsort((rec["idx"], -rec["score"].astype(np.float64)))
+    rec = np.zeros(len(sel), HIT_DTYPE)
+    rec["score"], rec["index"], rec["end_q"], rec["end_t"] = scores[sel], np.asarray(idx)[sel], np.asarray(end_q)[sel], np.asarray(end_t)[sel]
+    order = np.lexsort((rec["index"], -rec["score"].astype(np.float64)))
     return rec[order[:k]]
 
 
-def merge_topk(parts, k):
-    allr = np.concatenate(parts) if parts else np.empty(0, dtype=[("score", np.float32), ("idx", np.int64), ("end_q", np.int64), ("end_t", np.int64)])
-    order = np.lexsort((allr["idx"], -allr["score"].astype(np.float64)))
-    return allr[order[:k]]
-
-
-def allgather_topk(local, k, device=None):
-    """One collective: all-gather of the fixed-size per-rank top-k blocks (padded with score = -inf)."""
+def allgather_hits(local, k, device=None):
+    """THE collective of the search: all-gather of the fixed-size per-rank hit blocks (k x 32 bytes, padded)."""
     import torch
     import torch.distributed as dist
     world = dist.get_world_size()
-    buf = np.full((k, 4), -np.inf, np.float64)
-    buf[:len(local), 0] = local["score"]
-    buf[:len(local), 1] = local["idx"]
-    buf[:len(local), 2] = local["end_q"]
-    buf[:len(local), 3] = local["end_t"]
-    t = torch.from_numpy(buf)
+    buf = np.zeros(k, HIT_DTYPE)
+    buf["index"] = -1
+    buf[:len(local)] = local
+    t = torch.from_numpy(buf.view(np.uint8).copy())
     if device is not None:
         t = t.to(device)
     outs = [torch.empty_like(t) for _ in range(world)]
     dist.all_gather(outs, t)
     parts = []
     for o in outs:
-        a = o.cpu().numpy()
-        a = a[np.isfinite(a[:, 0])]
-        rec = np.empty(len(a), dtype=local.dtype)
-        rec["score"], rec["idx"], rec["end_q"], rec["end_t"] = a[:, 0], a[:, 1].astype(np.int64), a[:, 2].astype(np.int64), a[:, 3].astype(np.int64)
-        parts.append(rec)
+        a = o.cpu().numpy().view(HIT_DTYPE)
+        parts.append(a[a["index"] >= 0])
     return parts
 
 
 def search_scores(engine, query, db):
-    """(scores f32, end_q, end_t) of the query against every subject of `db` (one pipelined device call)."""
+    """(scores f32, end_q, end_t) of the query against every subject of `db` (host buffers in and out, one pipelined call)."""
     q = query if isinstance(query, (bytes, bytearray)) else query.encode("latin-1")
     n = db.n
     sc = np.empty(n, np.float32)
@@ -192,31 +275,51 @@ def search_scores(engine, query, db):
 
 
 def search(engine, query, db, topk=100, traceback=True, retain_all=False, rank=0, world_size=1, shard=None, device=None,
-           score_fn=None):
+           score_fn=None, ddb=None, gather_alignments=True):
     """Top-k hits of `query` in `db`.
 
-    world_size > 1: every rank calls this with the full `db` (or its precomputed `shard` = (index array, Database));
-    each scores its shard, one all-gather merges the per-rank top-k, every rank returns the same list.
-    score_fn: replaces the device scoring call (used by the CPU multi-process tests of the host logic).
+    ddb: the rank's resident shard (DeviceDatabase(engine, db, rank, world_size)); built here when absent -- callers that
+    search more than once keep it.  world_size > 1: every rank scans its shard and selects on the device, ONE all-gather
+    merges the per-rank lists (swb_search_merge), every rank traces the hits it owns and the alignments are gathered.
+    score_fn: replaces the device path by a host scoring function over (engine, query, shard Database) -- the CPU
+    multi-process tests of the rank logic.
     Returns a list of dicts: idx, score, end_q, end_t (+ aln_q, aln_t, idx_q, idx_t when traceback).
     """
-    if world_size > 1:
-        if shard is None:
-            idx = shard_indices(db.lengths(), world_size, getattr(db, "order", None))[rank]
-            shard = (idx, db.subset(idx))
-        idx, sub = shard
+    own_ddb = False
+    if score_fn is not None:                                  # host restatement (tests): shard, score, select with numpy
+        if world_size > 1:
+            if shard is None:
+                idx = shard_indices(db.lengths(), world_size, getattr(db, "order", None))[rank]
+                shard = (idx, db.subset(idx))
+            idx, sub = shard
+        else:
+            idx, sub = np.arange(db.n, dtype=np.int64), db
+        sc, eq, et = score_fn(engine, query, sub)
+        local = topk_records(sc, idx, eq, et, topk)
     else:
-        idx, sub = np.arange(db.n, dtype=np.int64), db
-    sc, eq, et = (score_fn or search_scores)(engine, query, sub)
-    local = topk_records(sc, idx, eq, et, topk)
-    if world_size > 1:
-        best = merge_topk(allgather_topk(local, topk, device), topk)
-    else:
-        best = local
-    hits = [{"idx": int(r["idx"]), "score": float(r["score"]), "end_q": int(r["end_q"]), "end_t": int(r["end_t"])} for r in best]
+        own_ddb = ddb is None
+        if own_ddb:
+            ddb = DeviceDatabase(engine, db, rank, world_size)
+        local = ddb.search(query, topk)
+    best = merge_hits(allgather_hits(local, topk, device), topk) if world_size > 1 else local
+    hits = [{"idx": int(r["index"]), "score": float(r["score"]), "end_q": int(r["end_q"]), "end_t": int(r["end_t"])} for r in best]
     if traceback and hits and engine is not None:
-        alns = engine.align_list([query] * len(hits), [db.sequence(h["idx"]) for h in hits], retain_all=retain_all)
-        for h, a in zip(hits, alns):
+        if score_fn is not None:
+            mine = {k: a for k, a in enumerate(engine.align_list([query] * len(hits), [db.sequence(h["idx"]) for h in hits], retain_all=retain_all))}
+        else:
+            mine = ddb.align(query, best, retain_all)         # only the hits whose subject lives in this shard
+        if world_size > 1 and score_fn is None and gather_alignments:
+            import torch.distributed as dist
+            parts = [None] * world_size
+            dist.all_gather_object(parts, {k: (a["aln_a"], a["aln_b"], a["idx_a"], a["idx_b"], a["score"]) for k, a in mine.items()})
+            mine = {k: {"aln_a": v[0], "aln_b": v[1], "idx_a": v[2], "idx_b": v[3], "score": v[4]} for p in parts for k, v in p.items()}
+        for k, h in enumerate(hits):
+            a = mine.get(k)
+            if a is None:
+                continue
             h.update(aln_q=a["aln_a"], aln_t=a["aln_b"], idx_q=a["idx_a"], idx_t=a["idx_b"])
-            assert a["score"] == h["score"], "scan and traceback disagree"
+            if a["score"] != h["score"]:
+                raise SwbError(4, "scan and traceback disagree on subject %d" % h["idx"])
+    if score_fn is None and own_ddb:
+        ddb.free()
     return hits

@@ -857,3 +857,56 @@ def test_cpp_cli_emboss_reports(emboss, tmp_path):
                 assert txt == bodies[("local", r["id"])], r["id"]
             sa, sb = report.starts_of(a["idx_a"], a["idx_b"]) if key == "local" else (1, 1)
             assert txt == report.srspair_body(a["aln_a"], a["aln_b"], a["score"], m, 10.0, 0.5, sa, sb)
+
+
+@pytest.mark.parametrize("mode", [swb.ALIGN_LOCAL, swb.ALIGN_GLOCAL, swb.ALIGN_GLOBAL])
+def test_align_partial_region_pads_over_the_whole_sequences(mode):
+    """align_partial(.., partial_region) (SA.rs:393-551): the DP runs on the prefixes, the retain_all padding loops run
+    over s1.seq.len() / s2.seq.len() -- the tails behind the prefixes appear as overhang (Python mirror and C ABI)."""
+    rng = np.random.default_rng(31 + mode)
+    m = swb.SubstitutionMatrix.get_blosum62_matrix()
+    eng = swb.SequenceAlignment(m, 10.0, 0.5, mode)
+    oeng = O.Engine(_omatrix(m), 10.0, 0.5, mode)
+    for _ in range(12):
+        a, b = _rand_seqs(rng, 1, 30, 120)[0], _rand_seqs(rng, 1, 30, 120)[0]
+        b = b[:10] + a[5:40] + b[10:]
+        pr = (int(rng.integers(1, len(a) + 1)), int(rng.integers(1, len(b) + 1)))
+        for ra in (True, False):
+            r1, r2, s = eng.align_partial(a, b, ra, pr, False)
+            o1, o2, os_ = oeng.align(a.decode(), b.decode(), ra, partial_region=pr)
+            assert ("".join(r1), "".join(r2), s) == ("".join(o1), "".join(o2), os_), (pr, ra)
+            if ra or mode != swb.ALIGN_LOCAL:
+                assert "".join(r1).replace("-", "") == a.decode() and "".join(r2).replace("-", "") == b.decode()
+        _, _, s2 = eng.align_partial(a, b, True, pr, True)
+        assert s2 == oeng.align(a.decode(), b.decode(), True, score_only=True, partial_region=pr)[2]
+    eng.close()
+
+
+@pytest.mark.timeout(600)
+@pytest.mark.parametrize("mode", [swb.ALIGN_LOCAL, swb.ALIGN_GLOCAL, swb.ALIGN_GLOBAL])
+def test_team_launches_from_two_streams_make_progress(mode, monkeypatch):
+    """Forward progress of the team-scheduled wavefront: the pipelined host-buffer call alternates its chunks over two
+    compute streams, and with 1024-pair chunks that each hold 2-3 pairs of more than 8192 residues every chunk launches a
+    TEAM kernel (warps that wait on each other).  Team launches are cooperative and chained through one event, so they
+    can neither oversubscribe the GPU nor interleave; the scores equal the oracle's."""
+    monkeypatch.setenv("SWB_CHUNK_PAIRS", "1024")
+    monkeypatch.setenv("SWB_CHUNK_FIRST", "1024")
+    rng = np.random.default_rng(900 + mode)
+    m = swb.SubstitutionMatrix.get_mat_matrix(2.0, -3.0)
+    eng = swb.SequenceAlignment(m, 5.0, 2.0, mode)
+    n = 5 * 1024
+    sa = _rand_seqs(rng, n, 20, 90, "ACGT"); sb = _rand_seqs(rng, n, 20, 90, "ACGT")
+    longs = []
+    for c in range(5):
+        for t in range(2 + (c & 1)):
+            k = c * 1024 + 100 + 300 * t
+            base = _rand_seqs(rng, 1, 8300 + 400 * t, 8300 + 400 * t, "ACGT")[0]
+            sa[k] = base; sb[k] = _mutate(rng, base, 0.06, 0.02, 0.02)
+            longs.append(k)
+    sc, ea, eb = eng.score_batch(sa, sb)
+    chk = longs + list(rng.choice(n, 300, replace=False))
+    osc, oi, oj = _oracle_scores(m, [sa[k] for k in chk], [sb[k] for k in chk], 5.0, 2.0, mode, scale=1)
+    assert np.array_equal(np.rint(sc[chk].astype(np.float64)).astype(np.int64), osc)
+    nz = osc > 0 if mode == swb.ALIGN_LOCAL else np.ones(len(chk), bool)
+    assert np.array_equal(ea[chk][nz], oi[nz]) and np.array_equal(eb[chk][nz], oj[nz])
+    eng.close()

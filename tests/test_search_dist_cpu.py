@@ -130,3 +130,27 @@ def test_packed_database_file_round_trip(tmp_path):
     open(str(bad), "wb").write(raw[:6000])
     with pytest.raises(ValueError):
         S.Database.load(str(bad))
+
+
+def test_native_shard_and_merge_host_functions():
+    """swb_db_shard / swb_search_merge are host-only entry points of the C ABI: the deal equals the numpy restatement,
+    the merge equals topk over the concatenation with (score desc, index asc)."""
+    rng = np.random.default_rng(3)
+    ln = rng.integers(0, 900, 777)
+    ln[5] = ln[6] = ln[700] = 450                                  # equal lengths: the stable order decides
+    off = np.zeros(len(ln) + 1, np.int64); off[1:] = np.cumsum(ln)
+    for w in (1, 2, 5, 8):
+        for r in range(w):
+            assert np.array_equal(S.native_shard_indices(off, r, w), S.shard_indices(ln, w)[r])
+    parts = []
+    for r in range(3):
+        h = np.zeros(20, S.HIT_DTYPE)
+        h["score"] = rng.integers(10, 30, 20).astype(np.float32) / 2
+        h["index"] = rng.choice(1000, 20, replace=False) * 3 + r
+        h["end_q"] = h["index"] + 1; h["end_t"] = h["index"] + 2
+        parts.append(h)
+    got = S.merge_hits(parts, 25)
+    allh = np.concatenate(parts)
+    order = np.lexsort((allh["index"], -allh["score"].astype(np.float64)))[:25]
+    assert got.tobytes() == allh[order].tobytes()
+    assert len(S.merge_hits(parts, 100)) == 60 and len(S.merge_hits([], 5)) == 0

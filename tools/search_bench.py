@@ -62,12 +62,9 @@ def main():
         if world > 1:
             dist.barrier()
         db = S.Database.load(args.db)
-    idx = S.shard_indices(db.lengths(), world, getattr(db, "order", None))[rank]
-    shard = (idx, db.subset(idx)) if world > 1 else (np.arange(db.n, dtype=np.int64), db)
-    # the shard lives in pinned host memory, as a resident database would
-    shard[1].residues = torch.from_numpy(np.array(shard[1].residues)).pin_memory().numpy()
     eng = swb.SequenceAlignment(swb.SubstitutionMatrix.get_blosum62_matrix(), 10.0, 0.5, swb.ALIGN_LOCAL, device=local_rank)
     dev = torch.device("cuda", local_rank)
+    ddb = S.DeviceDatabase(eng, db, rank, world)               # this rank's shard, resident on its GPU (swb_db_upload_shard)
 
     def barrier():
         if world > 1:
@@ -75,7 +72,7 @@ def main():
         torch.cuda.synchronize()
 
     def one(traceback):
-        return S.search(eng, q, db, topk=args.topk, traceback=traceback, rank=rank, world_size=world, shard=shard, device=dev)
+        return S.search(eng, q, db, topk=args.topk, traceback=traceback, rank=rank, world_size=world, device=dev, ddb=ddb)
 
     hits = one(True)                                           # warm-up (module load, scratch growth)
     t_score, t_full, dev_ms = [], [], []
