@@ -63,3 +63,24 @@ def test_no_oracle_in_product():
             if f.endswith((".py", ".cu", ".h", ".cpp")):
                 txt = open(os.path.join(dp, f), errors="replace").read()
                 assert "import oracle" not in txt and "from oracle" not in txt and "liboracle" not in txt, f
+
+
+def test_rust_sys_crate_declares_every_symbol():
+    """rust/swb200-sys (source only: no cargo in the image) declares exactly the entry points of include/swb200.h, and
+    its #[repr(C)] structs have the fields of the C structs in the same order."""
+    header = open(os.path.join(ROOT, "include", "swb200.h")).read()
+    rs = open(os.path.join(ROOT, "rust", "swb200-sys", "src", "lib.rs")).read()
+    declared = sorted(set(re.findall(r"\b(swb_[a-z0-9_]+)\s*\(", header)))
+    bound = sorted(set(re.findall(r"pub fn (swb_[a-z0-9_]+)\s*\(", rs)))
+    assert bound == declared
+    for name in ("swb_alignment", "swb_stats", "swb_aln_stats", "swb_hit", "swb_matrix"):
+        c_body = re.search(r"typedef struct %s \{(.*?)\} %s;" % (name, name), header, re.S).group(1)
+        c_body = re.sub(r"/\*.*?\*/", "", c_body, flags=re.S)
+        c_fields = [f for decl in c_body.split(";") for f in re.findall(r"\*?\s*([a-z_0-9]+)\s*(?:,|$)", decl.split(None, 1)[1] if len(decl.split(None, 1)) > 1 else "")]
+        c_fields = [f for f in c_fields if f not in ("const", "char", "float")]
+        rs_body = re.search(r"pub struct %s \{(.*?)\n\}" % name, rs, re.S).group(1)
+        rs_fields = re.findall(r"pub ([a-z_0-9]+):", rs_body)
+        assert rs_fields == c_fields, (name, rs_fields, c_fields)
+    wrapper = open(os.path.join(ROOT, "rust", "swb200", "src", "lib.rs")).read()
+    for needed in ("pub fn new(", "pub fn align(", "pub fn align_partial(", "pub fn load_fasta(", "pub fn get_blosum62_matrix(", "pub fn get_mat_matrix(", "pub fn load_from_lines("):
+        assert needed in wrapper

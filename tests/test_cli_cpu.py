@@ -148,3 +148,38 @@ def test_cpp_cli_option_errors():
     for bad in (["-nope", "a", "b"], ["-cluster", "x.fas"], ["-list", "-cluster", "x", "-out", "o"], ["a", "b", "c"]):
         r = subprocess.run([exe] + bad, capture_output=True, text=True)
         assert r.returncode == 1 and "error" in r.stderr, bad
+
+
+def test_perl_harness_rules_on_oracle_records(tmp_path):
+    """test/check_results.pl (the reference's acceptance rules restated) accepts the records of the oracle for all
+    100 pairs x 3 modes and rejects a corrupted one -- the CPU half of the harness test (the GPU half runs swbcli)."""
+    import gzip
+    import json
+    import os
+    import shutil
+    import subprocess
+    import sys
+    from conftest import GOLDEN, ROOT
+    if not shutil.which("perl"):
+        pytest.skip("perl not installed")
+    subprocess.run([sys.executable, os.path.join(ROOT, "test", "materialize.py"), str(tmp_path)], check=True)
+    pairs = json.load(gzip.open(os.path.join(GOLDEN, "emboss.json.gz")))
+    os.makedirs(tmp_path / "res_swb")
+    m = O.Matrix.blosum62()
+    for mode, tag in ((O.ALIGN_LOCAL, "local"), (O.ALIGN_GLOCAL, "glocal"), (O.ALIGN_GLOBAL, "global")):
+        eng = O.Engine(m, 10.0, 0.5, mode)
+        for p in pairs:
+            r1, r2, sc = eng.align(p["seq1"], p["seq2"], True)
+            (tmp_path / "res_swb" / ("seq%d.1.fas.res.%s" % (p["id"], tag))).write_text(O.cli_record("s1", "s2", r1, r2, sc, mode))
+    chk = ["perl", os.path.join(ROOT, "test", "check_results.pl")]
+    r = subprocess.run(chk, cwd=tmp_path, capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr + r.stdout
+    assert r.stdout.splitlines()[-2:] == ["OK", "Checked 300 results"]
+    f = tmp_path / "res_swb" / "seq7.1.fas.res.global"
+    txt = f.read_text().split("\n")
+    k = next(i for i, l in enumerate(txt) if l.startswith(">s2")) + 1
+    pos = txt[k].index("-") if "-" in txt[k] else 5
+    txt[k] = txt[k][:pos] + txt[k][pos + 1:] + "-"                 # move one gap to the end: still spells the input, differs from EMBOSS
+    f.write_text("\n".join(txt))
+    r = subprocess.run(chk, cwd=tmp_path, capture_output=True, text=True)
+    assert r.returncode != 0 and "differs from EMBOSS" in r.stderr

@@ -910,3 +910,23 @@ def test_team_launches_from_two_streams_make_progress(mode, monkeypatch):
     nz = osc > 0 if mode == swb.ALIGN_LOCAL else np.ones(len(chk), bool)
     assert np.array_equal(ea[chk][nz], oi[nz]) and np.array_equal(eb[chk][nz], oj[nz])
     eng.close()
+
+
+def test_perl_harness_over_the_cli(tmp_path):
+    """NS-5: the reference's acceptance harness (test/README.md:18-27) over the compiled drop-in CLI: materialise the data
+    layout from the fixtures, run list mode for the three alignment types (test/run_swb.pl), compare with the EMBOSS
+    results by the reference's rules (test/check_results.pl) -> "OK / Checked 300 results"."""
+    import os
+    import shutil
+    import subprocess
+    import sys
+    from conftest import ROOT
+    if not shutil.which("perl"):
+        pytest.skip("perl not installed")
+    cli = _swbcli()
+    subprocess.run([sys.executable, os.path.join(ROOT, "test", "materialize.py"), str(tmp_path)], check=True)
+    r = subprocess.run(["perl", os.path.join(ROOT, "test", "run_swb.pl"), cli], cwd=tmp_path, capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr + r.stdout
+    r = subprocess.run(["perl", os.path.join(ROOT, "test", "check_results.pl")], cwd=tmp_path, capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr + r.stdout
+    assert r.stdout.splitlines()[-2:] == ["OK", "Checked 300 results"]
