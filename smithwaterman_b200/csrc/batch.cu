@@ -135,7 +135,7 @@ __global__ void SWB_HELPER k1_pack_kernel(const uint8_t *__restrict__ codes_a, c
                                const int32_t *__restrict__ order, K1Group *groups,
                                uint8_t *__restrict__ a_pk, uint8_t *__restrict__ b_pk, int32_t *__restrict__ la_arr,
                                int32_t *__restrict__ lb_arr, int pad, int64_t base_a, int64_t base_b, int shared_la,
-                               const int64_t *__restrict__ aoff, const int64_t *__restrict__ boff)
+                               const int64_t *__restrict__ aoff, const int64_t *__restrict__ boff, int right_align)
 {
     K1Group G = groups[blockIdx.x];
     G.a_off = shared_la >= 0 ? 0 : aoff[blockIdx.x]; G.b_off = boff[blockIdx.x];     // exclusive sums of the items' block sizes
@@ -162,6 +162,8 @@ __global__ void SWB_HELPER k1_pack_kernel(const uint8_t *__restrict__ codes_a, c
         }
         reinterpret_cast<unsigned *>(a_pk + G.a_off)[c * 32 + lane] = r;
     }
+    // glocal (right_align): b ends at the last column of the item's last pass, PAD columns lead (k1_global.cu)
+    const int shift = right_align ? G.n_pass * K1_STRIP - lb : 0;
     for (int h = sub; h < G.n_pass * 2; h += nsub) {       // 16-byte halves of the 32-column passes
         unsigned w[4];
 #pragma unroll
@@ -169,8 +171,8 @@ __global__ void SWB_HELPER k1_pack_kernel(const uint8_t *__restrict__ codes_a, c
             unsigned r = 0;
 #pragma unroll
             for (int s = 0; s < 4; ++s) {
-                const int col = h * 16 + q * 4 + s;
-                const unsigned code = (col < lb) ? codes_b[ob + col] : (unsigned)pad;
+                const int col = h * 16 + q * 4 + s - shift;
+                const unsigned code = (col >= 0 && col < lb) ? codes_b[ob + col] : (unsigned)pad;
                 r |= code << (8 * s);
             }
             w[q] = r;
@@ -205,7 +207,7 @@ __host__ __device__ __forceinline__ bool k1_take(int64_t la, int64_t lb, const K
 static K1Take k1_take_rule(const swb_engine *e)
 {
     K1Take T;
-    T.global_mode = (e->mode == SWB_GLOBAL) ? 1 : 0;
+    T.global_mode = (e->mode != SWB_LOCAL) ? 1 : 0;     // global and glocal: no clamp, no overflow flag -> static bound
     const int64_t ao = -(int64_t)e->o, ae = -(int64_t)e->e, sp = std::max(e->smax, 0), sn = std::max(-e->smin, 0);
     T.up_per_match = sp; T.up_base = ao + sp + sn + 64;
     T.down_per_res = ae; T.down_base = 3 * ao + (10 * ao + 10 * ae) + sp + sn + 64;
@@ -499,7 +501,7 @@ int batch_upload_impl(swb_engine *e, const char *a_all, const int64_t *off_a, co
     d->base_a = (n && !shared) ? off_a[0] : 0; d->base_b = n ? off_b[0] : 0;
     const int64_t na = shared ? shared_la : (n ? off_a[n] - d->base_a : 0), nb = n ? off_b[n] - d->base_b : 0;
     if (na < 0 || nb < 0 || (na > 0 && !a_all) || (nb > 0 && !b_all && !rdb)) { e->err = "bad sequence buffer / offsets"; return SWB_ERR_ARG; }
-    const bool use_k1 = ((e->mode == SWB_LOCAL || e->mode == SWB_GLOBAL) && e->o <= e->e);   // the packed Gotoh cell needs |open| >= |ext|
+    const bool use_k1 = e->o <= e->e;                // all three modes; the packed Gotoh cell needs |open| >= |ext|
     const K1Take take = k1_take_rule(e);
 
     // ---- device buffers + H2D of the raw residues first (stream-ordered, no host synchronisation): the copy engine works
@@ -596,7 +598,7 @@ int batch_upload_impl(swb_engine *e, const char *a_all, const int64_t *off_a, co
         scan_kernel<int64_t><<<1, HELPER_THREADS, 0, hs>>>(asz, aoff, ng);
         scan_kernel<int64_t><<<1, HELPER_THREADS, 0, hs>>>(bsz, boff, ng);
         k1_pack_kernel<<<ng, HELPER_THREADS, 0, hs>>>(d->codes_a, d->codes_b, d->off_a, d->off_b, d->order, b->d_groups,
-                                                  b->d_a, b->d_b, b->d_la, b->d_lb, e->n, d->base_a, d->base_b, sla, aoff, boff);
+                                                  b->d_a, b->d_b, b->d_la, b->d_lb, e->n, d->base_a, d->base_b, sla, aoff, boff, e->mode == SWB_GLOCAL ? 1 : 0);
         CUDA_TRY(e, cudaGetLastError());
         { int rc_ = ensure_bnd(e, k1_bnd_bytes(e->sm_count, b->la_max)); if (rc_ != SWB_OK) return rc_; }
     }
@@ -718,7 +720,7 @@ int batch_launch(swb_engine *e, swb_batch *b, int64_t *launches)
     CUDA_TRY(e, cudaStreamWaitEvent(st, d->ev_ready, 0));     // upload may have run on the copy stream
     d->launched = true; d->done_recorded = false;
     if (d->n_k1) {
-        CUDA_TRY(e, e->mode == SWB_GLOBAL ? k1_global_launch(e, b, e->sm_count, bnd_slot(e, b), st) : k1_launch(e, b, e->sm_count, bnd_slot(e, b), st));
+        CUDA_TRY(e, e->mode != SWB_LOCAL ? k1_global_launch(e, b, e->sm_count, bnd_slot(e, b), st) : k1_launch(e, b, e->sm_count, bnd_slot(e, b), st));
         ++*launches;
     }
     if (d->n_k2) {

@@ -12,6 +12,17 @@
 // which is why only this mode (not glocal, whose last row / column are free) fits the uniform packed cell.
 // The s16 range is guaranteed by the host's routing (batch.cu k1_take: |scores| bounded from the lengths), not by flags.
 // Cells beyond (la, lb) are computed on PAD residues; they may wrap, but nothing flows from them to a real cell.
+//
+// GLOCAL = true: the reference's glocal mode (SA.rs:74-82: so = se = 0) -- boundary row and column cost nothing, and so do
+// gaps in the last row (SA.rs:166-167) and the last column (SA.rs:169-170).  A free move only ever copies a value along
+// the last row / column, so the three-state maximum at (la, lb) is
+//     max(0, max_i H(i, lb), max_j H(la, j))
+// of the matrix filled with the INTERIOR penalties everywhere (M and the gap state that enters the last row / column are
+// computed from interior cells with interior penalties; the free state is the running maximum of the cells before it).
+// The kernel therefore runs the uniform cell with an all-zero boundary and tracks two maxima.  To keep the last column
+// at a fixed register (word 15, high half, of the last pass) the packer RIGHT-aligns b: the first pass starts with PAD
+// columns, and in this kernel PAD scores 0 -- a zero-score column next to the zero boundary reproduces the boundary
+// exactly (H = max(0 + 0, E, F) = 0 with E, F <= open), so left padding is invisible to the real columns.
 #include <cstdlib>
 
 #include "swb_internal.h"
@@ -31,6 +42,7 @@
         F[k] = Fk;                                                                                   \
     }
 
+template <bool GLOCAL>
 __global__ void __maxnreg__(120)
 k1_global_kernel(const uint8_t *__restrict__ a_pk, const uint8_t *__restrict__ b_pk,
                  const K1Group *__restrict__ groups, int n_groups, const int32_t *__restrict__ la_arr,
@@ -38,8 +50,11 @@ k1_global_kernel(const uint8_t *__restrict__ a_pk, const uint8_t *__restrict__ b
                  uint4 *__restrict__ bnd, int *counter, const int32_t *__restrict__ order, K1Result *__restrict__ res)
 {
     extern __shared__ unsigned T_sh[];               // [nl*nl][32 lanes]: (s - open) & 0xFFFF
-    for (int idx = threadIdx.x; idx < nl * nl * 32; idx += blockDim.x)
-        T_sh[idx] = (unsigned)(mat[idx >> 5] - open) & 0xFFFFu;
+    for (int idx = threadIdx.x; idx < nl * nl * 32; idx += blockDim.x) {
+        const int cell = idx >> 5;
+        const bool is_pad = (cell % nl == nl - 1) || (cell / nl == nl - 1);
+        T_sh[idx] = (unsigned)((GLOCAL && is_pad ? 0 : mat[cell]) - open) & 0xFFFFu;      // glocal: PAD scores 0 (see above)
+    }
     __syncthreads();
 
     const int lane = threadIdx.x & 31;
@@ -52,7 +67,7 @@ k1_global_kernel(const uint8_t *__restrict__ a_pk, const uint8_t *__restrict__ b
     const unsigned long long pol = keep_policy();
     const int sent = 10 * open + 10 * ext;           // the "not reachable" states of a boundary cell sit this far below it
     // Ho of boundary cell (0, j) or (j, 0), j >= 1:  H + open = 2 open + (j-1) ext;  (0,0): open
-    auto ho_bnd = [=](int j) { return j == 0 ? open : 2 * open + (j - 1) * ext; };
+    auto ho_bnd = [=](int j) { return (GLOCAL || j == 0) ? open : 2 * open + (j - 1) * ext; };     // glocal: H = 0 on the whole boundary
 
     for (;;) {
         int g = 0;
@@ -64,6 +79,8 @@ k1_global_kernel(const uint8_t *__restrict__ a_pk, const uint8_t *__restrict__ b
         const bool valid = lane < G_.n_pairs;
         const int la = valid ? la_arr[p] : 0, lb = valid ? lb_arr[p] : 0;
         int score = 0;
+        int best_row = open;                            // glocal: maximum of Ho over row la
+        unsigned cm = open2;                            // glocal: running maximum of the last column (high half of word 15, last pass)
         const unsigned *ap = reinterpret_cast<const unsigned *>(a_pk + G_.a_off) + lane;  // rows 4B+1..4B+4 at ap[B*32]
         const uint4 *bp = reinterpret_cast<const uint4 *>(b_pk + G_.b_off) + lane * 2;    // pass q at bp[q*64]
         const int nblk = (G_.la_max + 1 + 3) >> 2;      // row steps run in blocks of 4
@@ -139,7 +156,17 @@ k1_global_kernel(const uint8_t *__restrict__ a_pk, const uint8_t *__restrict__ b
                     if (t == 0 && !last && blk > 0) st_keep(mybnd + (size_t)(blk - 1) * bstride, make_uint4(c1, c2, c3, wout[0]), pol);
                     lo15_Ho = Ho[15]; lo15_E = E;
                     HoD = HoD_next;
-                    if (i == trow) {
+                    if (GLOCAL) {
+                        if (last && i <= la + 1) cm = __vmaxs2(cm, Ho[15]);       // cell (i-1, lb); row 0 holds the boundary 0
+                        if (i == la || i == la + 1) {                                  // row la: low halves now, high halves one step later
+                            unsigned rm = __vimax3_s16x2(Ho[0], Ho[1], Ho[2]);
+                            rm = __vimax3_s16x2(rm, Ho[3], Ho[4]); rm = __vimax3_s16x2(rm, Ho[5], Ho[6]);
+                            rm = __vimax3_s16x2(rm, Ho[7], Ho[8]); rm = __vimax3_s16x2(rm, Ho[9], Ho[10]);
+                            rm = __vimax3_s16x2(rm, Ho[11], Ho[12]); rm = __vimax3_s16x2(rm, Ho[13], Ho[14]);
+                            rm = __vmaxs2(rm, Ho[15]);
+                            best_row = max(best_row, i == la ? lo16(rm) : hi16(rm));
+                        }
+                    } else if (i == trow) {
                         int v = 0;
 #pragma unroll
                         for (int k = 0; k < K1_HALF; ++k) {
@@ -153,6 +180,7 @@ k1_global_kernel(const uint8_t *__restrict__ a_pk, const uint8_t *__restrict__ b
             }
             if (!last) st_keep(mybnd + (size_t)(nblk - 1) * bstride, make_uint4(c1, c2, c3, open2), pol);   // rows 4(nblk-1)+1..+3
         }
+        if (GLOCAL) score = max(max(best_row, hi16(cm)), open) - open;      // max(0, last row, last column)
         if (valid) {
             K1Result r;
             r.score = score; r.end_i = la; r.end_j = lb; r.flags = 0;       // SA.rs:296-309: the walk starts at (la, lb)
@@ -165,12 +193,19 @@ cudaError_t k1_global_launch(const swb_engine *e, const swb_batch *b, int n_bloc
 {
     const int nl = e->n + 1;
     const size_t smem = (size_t)nl * nl * 32 * sizeof(unsigned);
-    cudaError_t err = cudaFuncSetAttribute(k1_global_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    const bool glocal = e->mode == SWB_GLOCAL;
+    cudaError_t err = glocal ? cudaFuncSetAttribute(k1_global_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)
+                             : cudaFuncSetAttribute(k1_global_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (err != cudaSuccess) return err;
     err = cudaMemsetAsync(b->d_counter, 0, sizeof(int32_t), st);
     if (err != cudaSuccess) return err;
-    k1_global_kernel<<<n_blocks, K1_THREADS * 2, smem, st>>>(
-        b->d_a, b->d_b, b->d_groups, b->n_groups, b->d_la, b->d_lb, e->d_mat, nl, e->o, e->e,
-        reinterpret_cast<uint4 *>(d_bnd), b->d_counter, b->d_order, b->d_res);
+    if (glocal)
+        k1_global_kernel<true><<<n_blocks, K1_THREADS * 2, smem, st>>>(
+            b->d_a, b->d_b, b->d_groups, b->n_groups, b->d_la, b->d_lb, e->d_mat, nl, e->o, e->e,
+            reinterpret_cast<uint4 *>(d_bnd), b->d_counter, b->d_order, b->d_res);
+    else
+        k1_global_kernel<false><<<n_blocks, K1_THREADS * 2, smem, st>>>(
+            b->d_a, b->d_b, b->d_groups, b->n_groups, b->d_la, b->d_lb, e->d_mat, nl, e->o, e->e,
+            reinterpret_cast<uint4 *>(d_bnd), b->d_counter, b->d_order, b->d_res);
     return cudaGetLastError();
 }

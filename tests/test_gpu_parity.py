@@ -695,14 +695,16 @@ def test_cpp_mirror_runs_the_reference_kats(rust_kats, tmp_path):
     assert "kats: %d cases, 0 failures" % len(rows) in r.stdout
 
 
+@pytest.mark.parametrize("mode", [swb.ALIGN_GLOBAL, swb.ALIGN_GLOCAL])
 @pytest.mark.parametrize("go,ge", [(10.0, 0.5), (0.5, 0.5), (3.0, 1.0)])
-def test_global_score_batch_packed_kernel(go, ge):
-    """Global mode through the packed s16x2 kernel (csrc/k1_global.cu): multi-pass, multi-block shapes, pairs near the
-    s16 routing bound on both sides (longer ones go to the int32 wavefront kernel in the same call), self alignments
-    (largest positive scores) and unrelated pairs of very different lengths (most negative scores)."""
+def test_global_score_batch_packed_kernel(go, ge, mode):
+    """Global and glocal mode through the packed s16x2 kernel (csrc/k1_global.cu): multi-pass, multi-block shapes, pairs
+    near the s16 routing bound on both sides (longer ones go to the int32 wavefront kernel in the same call), self
+    alignments (largest positive scores) and unrelated pairs of very different lengths (most negative scores).  Glocal:
+    free last row / last column (SA.rs:166-170) as two tracked maxima over a right-aligned b."""
     rng = np.random.default_rng(int(go * 10 + ge * 100))
     m = swb.SubstitutionMatrix.get_blosum62_matrix()
-    eng = swb.SequenceAlignment(m, go, ge, swb.ALIGN_GLOBAL)
+    eng = swb.SequenceAlignment(m, go, ge, mode)
     sa = _rand_seqs(rng, 2500, 1, 700); sb = _rand_seqs(rng, 2500, 1, 700)
     for la, lb in [(1, 700), (700, 1), (1400, 1400), (1450, 1460), (1500, 30), (30, 1500), (2500, 2500), (3000, 40), (8192, 5), (5, 8192),
                    (9000, 3), (31, 31), (32, 64), (96, 96), (97, 95)]:
@@ -713,8 +715,12 @@ def test_global_score_batch_packed_kernel(go, ge):
     for k in range(300):                                            # related pairs
         base = _rand_seqs(rng, 1, 50, 900)[0]
         sa.append(base); sb.append(_mutate(rng, base, 0.2, 0.05, 0.05, alphabet=AA.encode()))
+    for k in range(200):                                            # glocal shapes: one sequence inside the other, overlaps
+        base = _rand_seqs(rng, 1, 100, 900)[0]
+        lo = int(rng.integers(0, len(base) // 2)); hi = int(rng.integers(lo + 20, len(base) + 1))
+        sa.append(base); sb.append(_mutate(rng, base[lo:hi], 0.1, 0.02, 0.02, alphabet=AA.encode()) + (_rand_seqs(rng, 1, 0, 60)[0] if k % 2 else b""))
     sc, ea, eb = eng.score_batch(sa, sb)
-    osc, oi, oj = _oracle_scores(m, sa, sb, go, ge, swb.ALIGN_GLOBAL)
+    osc, oi, oj = _oracle_scores(m, sa, sb, go, ge, mode)
     assert np.array_equal(np.rint(sc.astype(np.float64) * 2).astype(np.int64), osc)
     assert np.array_equal(ea, oi) and np.array_equal(eb, oj)
     # one shared `a` (the database-search call) takes the same kernel
@@ -722,7 +728,7 @@ def test_global_score_batch_packed_kernel(go, ge):
     q = _rand_seqs(rng, 1, 350, 350)[0]
     db = S.Database.from_sequences(sb[:800])
     s2, _, _ = S.search_scores(eng, q, db)
-    o2, _, _ = _oracle_scores(m, [q] * 800, sb[:800], go, ge, swb.ALIGN_GLOBAL)
+    o2, _, _ = _oracle_scores(m, [q] * 800, sb[:800], go, ge, mode)
     assert np.array_equal(np.rint(s2.astype(np.float64) * 2).astype(np.int64), o2)
     eng.close()
 
