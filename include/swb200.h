@@ -94,6 +94,7 @@ typedef struct swb_stats {
     int32_t scale;           /* integer rescaling factor in use (10/0.5 -> 2) */
     int32_t exact_scale;     /* 1 = every input was exactly representable on the integer grid */
     int64_t ckpt_pairs;      /* pairs traced back through checkpointed recompute (direction bytes over the budget) */
+    int64_t k3_pairs;        /* pairs traced back on the packed path (s16x2 fill with tile borders + tile-recompute walk) */
 } swb_stats;
 
 /* Built-in matrices (SA.rs:697-733 BLOSUM62, 24 letters; SA.rs:681-695 match/mismatch, A-Z).

@@ -54,6 +54,7 @@ pub struct swb_stats {
     pub scale: i32,
     pub exact_scale: i32,
     pub ckpt_pairs: i64,
+    pub k3_pairs: i64,
 }
 
 #[repr(C)]

@@ -81,7 +81,7 @@ HIT_DTYPE = [("score", "<f4"), ("shard", "<i4"), ("index", "<i8"), ("end_q", "<i
 class Stats(ctypes.Structure):
     _fields_ = [("cells", ctypes.c_double), ("kernel_ms", ctypes.c_double), ("h2d_bytes", ctypes.c_double),
                 ("d2h_bytes", ctypes.c_double), ("launches", ctypes.c_int64), ("i32_reruns", ctypes.c_int64),
-                ("scale", ctypes.c_int32), ("exact_scale", ctypes.c_int32), ("ckpt_pairs", ctypes.c_int64)]
+                ("scale", ctypes.c_int32), ("exact_scale", ctypes.c_int32), ("ckpt_pairs", ctypes.c_int64), ("k3_pairs", ctypes.c_int64)]
 
 
 _lib = None

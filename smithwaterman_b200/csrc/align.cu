@@ -211,6 +211,91 @@ static int align_ckpt_pair(swb_engine *e, const uint8_t *d_a, const uint8_t *d_b
 // strings are spelled from the letters as given with the FULL lengths.  Local mode: a hit of a database search is traced
 // inside the prefix box that ends at its end cell -- every cell of the box has the value it has in the full matrix and
 // precedes the end cell in the reference's scan order (SA.rs:286-294), so the walk is the same.
+// The packed traceback path (k3_tile.cu) for the jobs `sel`: K3 fill with tile borders + KT3 tile walk, chunked by the
+// border-store budget; the strings are inflated on host threads as on the direction-byte path.
+static int align_jobs_k3(swb_engine *e, const uint8_t *d_a, const uint8_t *d_b, const std::vector<AlnJob> &jobs, std::vector<size_t> sel,
+                         bool retain_all, swb_alignment *outs)
+{
+    const float inv = 1.0f / (float)e->scale;
+    const bool dyadic = (e->scale & (e->scale - 1)) == 0;
+    auto to_f = [&](int64_t s) { return dyadic ? (float)s * inv : (float)((double)s / e->scale); };
+    const int64_t budget = dir_budget();
+    // longest first: a warp takes one pair at a time from a counter
+    std::sort(sel.begin(), sel.end(), [&](size_t x, size_t y) { return (int64_t)jobs[x].la * jobs[x].lb > (int64_t)jobs[y].la * jobs[y].lb; });
+    size_t pos = 0;
+    while (pos < sel.size()) {
+        std::vector<K3Pair> hp;
+        int64_t colb = 0, rowb = 0, out_total = 0;
+        size_t end = pos;
+        while (end < sel.size()) {
+            const AlnJob &J = jobs[sel[end]];
+            int64_t c4, rw; k3_sizes(J.la, J.lb, &c4, &rw);
+            rw = (rw + 3) / 4 * 4;
+            if (!hp.empty() && (colb + c4) * 16 + (rowb + rw) * 4 > budget) break;
+            K3Pair P; P.a_off = J.a_off; P.b_off = J.b_off; P.la = J.la; P.lb = J.lb; P.colb_off = colb; P.rowb_off = rowb; P.out_off = out_total;
+            P.start_state = 0; P.score = J.known_score == INT32_MIN ? 0 : J.known_score;
+            hp.push_back(P);
+            colb += c4; rowb += rw; out_total += (int64_t)J.la + J.lb + 1;
+            ++end;
+        }
+        const int np = (int)hp.size();
+        DevBuf d_pairs, d_res, d_colb, d_rowb, d_cnt, d_xa, d_xb, d_nc;
+        CUDA_TRY(e, d_pairs.alloc(np * sizeof(K3Pair), e->stream)); CUDA_TRY(e, d_res.alloc(np * sizeof(KWResult), e->stream));
+        CUDA_TRY(e, d_colb.alloc((size_t)colb * 16 + 64, e->stream)); CUDA_TRY(e, d_rowb.alloc((size_t)rowb * 4 + 64, e->stream));
+        CUDA_TRY(e, d_cnt.alloc(sizeof(int), e->stream));
+        CUDA_TRY(e, d_xa.alloc(out_total * sizeof(int32_t), e->stream)); CUDA_TRY(e, d_xb.alloc(out_total * sizeof(int32_t), e->stream));
+        CUDA_TRY(e, d_nc.alloc(np * sizeof(int32_t), e->stream));
+        CUDA_TRY(e, cudaMemcpyAsync(d_pairs.p, hp.data(), np * sizeof(K3Pair), cudaMemcpyHostToDevice, e->stream));
+        CUDA_TRY(e, cudaEventRecord(e->ev0, e->stream));
+        CUDA_TRY(e, k3_launch(e, d_a, d_b, d_pairs.as<K3Pair>(), np, d_colb.as<uint4>(), d_rowb.as<unsigned>(), d_cnt.as<int>(),
+                              d_xa.as<int32_t>(), d_xb.as<int32_t>(), d_nc.as<int32_t>(), d_res.as<KWResult>(), e->stream));
+        CUDA_TRY(e, cudaEventRecord(e->ev1, e->stream));
+        const size_t tb_need = (size_t)np * (sizeof(KWResult) + sizeof(int32_t)) + 2 * (size_t)out_total * sizeof(int32_t) + 64;
+        if (tb_need > e->tb_bytes) {
+            if (e->h_tb) cudaFreeHost(e->h_tb);
+            e->h_tb = nullptr; e->tb_bytes = 0;
+            CUDA_TRY(e, cudaMallocHost(&e->h_tb, tb_need));
+            e->tb_bytes = tb_need;
+        }
+        KWResult *hr = (KWResult *)e->h_tb;
+        int32_t *hnc = (int32_t *)(hr + np), *hxa = hnc + np, *hxb = hxa + out_total;
+        CUDA_TRY(e, cudaMemcpyAsync(hr, d_res.p, np * sizeof(KWResult), cudaMemcpyDeviceToHost, e->stream));
+        CUDA_TRY(e, cudaMemcpyAsync(hnc, d_nc.p, np * sizeof(int32_t), cudaMemcpyDeviceToHost, e->stream));
+        CUDA_TRY(e, cudaMemcpyAsync(hxa, d_xa.p, out_total * sizeof(int32_t), cudaMemcpyDeviceToHost, e->stream));
+        CUDA_TRY(e, cudaMemcpyAsync(hxb, d_xb.p, out_total * sizeof(int32_t), cudaMemcpyDeviceToHost, e->stream));
+        CUDA_TRY(e, cudaStreamSynchronize(e->stream));
+        float ms = 0; cudaEventElapsedTime(&ms, e->ev0, e->ev1);
+        e->stats.kernel_ms += ms; e->stats.launches += 2; e->stats.k3_pairs += np;
+        e->stats.h2d_bytes += (double)np * sizeof(K3Pair);
+        e->stats.d2h_bytes += (double)np * (sizeof(KWResult) + 4) + 8.0 * out_total;
+        std::atomic<int> next(0), fail(SWB_OK);
+        auto worker = [&]() {
+            for (;;) {
+                const int t = next.fetch_add(1);
+                if (t >= np || fail.load() != SWB_OK) return;
+                const AlnJob &J = jobs[sel[pos + t]];
+                if (hnc[t] < 0) { fail.store(SWB_ERR_EMPTY); return; }
+                const int64_t nc = hnc[t];
+                std::vector<int64_t> xa(nc), xb(nc);
+                for (int64_t c = 0; c < nc; ++c) { xa[c] = hxa[hp[t].out_off + nc - 1 - c]; xb[c] = hxb[hp[t].out_off + nc - 1 - c]; }   // reverse (SA.rs:384-385)
+                std::string ra, rb;
+                inflate(J.ra, J.la_full, J.rb, J.lb_full, xa.data(), xb.data(), nc, e->mode, retain_all, ra, rb);
+                if (fill_out(&outs[J.out], to_f(hr[t].score), hr[t].end_i, hr[t].end_j, xa, xb, ra, rb) != SWB_OK) { fail.store(SWB_ERR_NOMEM); return; }
+            }
+        };
+        const int n_thr = (np >= 8) ? (int)std::min<unsigned>(std::max(1u, std::thread::hardware_concurrency()), 16u) : 1;
+        if (n_thr > 1) {
+            std::vector<std::thread> pool;
+            for (int w = 0; w < n_thr; ++w) pool.emplace_back(worker);
+            for (auto &th : pool) th.join();
+        } else worker();
+        if (fail.load() == SWB_ERR_EMPTY) { e->err = "traceback left the matrix (the reference panics here, SA.rs:360-371)"; return SWB_ERR_EMPTY; }
+        if (fail.load() != SWB_OK) { e->err = "out of memory"; return fail.load(); }
+        pos = end;
+    }
+    return SWB_OK;
+}
+
 // Device core of the traceback path: KW with direction bytes + KT for the jobs whose bytes fit the budget (chunked),
 // checkpointed recompute for the others.  outs: full alignments; souts: the counting form.  Exactly one is non-null.
 int align_jobs_device(swb_engine *e, const uint8_t *d_a, const uint8_t *d_b, const std::vector<AlnJob> &jobs, bool retain_all,
@@ -220,9 +305,25 @@ int align_jobs_device(swb_engine *e, const uint8_t *d_a, const uint8_t *d_b, con
     const bool dyadic = (e->scale & (e->scale - 1)) == 0;
     auto to_f = [&](int64_t s) { return dyadic ? (float)s * inv : (float)((double)s / e->scale); };
     const int64_t budget = dir_budget();
-    std::vector<size_t> work;
+    std::vector<size_t> work, packed;
+    // the packed path (K3 + KT3): global-mode pairs inside the static s16 bound; local-mode pairs whose end cell and score
+    // are known from the scan (hits of a database search) and below the s16 limit
+    const int64_t k3_limit = 32767 - 2 * (int64_t)std::max(e->smax, 0) + e->o - 64;
+    for (size_t w = 0; w < jobs.size() && outs && !d_pssm; ++w) {
+        const AlnJob &J = jobs[w];
+        if (!k3_eligible(e, J.la, J.lb)) continue;
+        if (e->mode == SWB_LOCAL && (J.known_score == INT32_MIN || J.known_score <= 0 || J.known_score >= k3_limit)) continue;
+        packed.push_back(w);
+    }
+    if (!packed.empty()) {
+        int rc = align_jobs_k3(e, d_a, d_b, jobs, packed, retain_all, outs);
+        if (rc != SWB_OK) return rc;
+    }
+    std::vector<char> is_packed(jobs.size(), 0);
+    for (size_t w : packed) is_packed[w] = 1;
     for (size_t w = 0; w < jobs.size(); ++w) {
         const AlnJob &J = jobs[w];
+        if (is_packed[w]) continue;
         if (d_pssm || kw_dir_bytes(J.la, J.lb, 8) <= budget) { work.push_back(w); continue; }
         // direction bytes do not fit: checkpointed traceback, one pair at a time
         KWResult R; std::vector<int64_t> xa, xb; std::string ra, rb;

@@ -1,0 +1,424 @@
+// K3 + KT3 -- the packed traceback path: score-speed fill with sparse tile borders, traceback by recomputing only the
+// tiles the path crosses.
+//
+// Replaces fill_matrix + backtrack of the reference (SA.rs:55-387) for pairs whose scores provably fit s16 lanes and
+// whose penalties satisfy |open| >= |extend| (so that the two-value Gotoh form equals the three-state form in VALUE,
+// SURVEY.md 8a note 3).  The direction-byte path (kw_trace.cu) pays ~42 int32 instructions and one byte of HBM per
+// cell; here
+//   * K3 fills the matrix with the packed s16x2 cell of K1/K2 (5.5 DPX-pipe operations per TWO cells) and stores only
+//     the cells on a grid: the last column of every 32-column pass (H, E, M, F: 8 bytes per row) and, every 64 rows,
+//     three snapshots of the pass's H registers and two of F (320 bytes per pass);
+//   * KT3 walks the path tile by tile (32 columns x <= 64 rows): a warp re-computes the part of the tile above-left of
+//     the cursor with the EXACT three-state int32 cell (kw_cell.cuh: the reference's five priority orders, clamp after
+//     the choice) from the stored border values -- M(r,j) = H(r-1,j-1) + s, X(r,j) by the row recurrence from the
+//     stored E of the pass's left border, Y = F -- writes the predecessor codes to shared memory and follows them.
+// Every border cell holds the value it has in the full matrix, so every recomputed cell and every tie decision is the
+// reference's.  Local mode is given the end cell by the scan (K1/K2) and fills only the prefix box that ends there;
+// global mode reads the start state off the recomputed cell (la, lb).  Glocal stays on the direction-byte path.
+#include <algorithm>
+#include <cstdlib>
+
+#include "swb_internal.h"
+#include "k1_common.cuh"
+#include "kw_cell.cuh"
+
+#define K3_R 64                       // rows between row checkpoints (a multiple of 4)
+#define K3_ROWB_WORDS 80              // per (checkpoint, pass): Ho after steps t=1,2,3 (3 x 16 words) + F after t=2,3 (2 x 16)
+#define K3_WARPS 12                   // 384 threads: up to 168 registers per thread, no spills in the global form
+
+template <int MODE>
+struct K3Cell {
+    static __device__ __forceinline__ unsigned g(unsigned hod, unsigned s2, unsigned fk)
+    {
+        return MODE == SWB_LOCAL ? __viaddmax_s16x2_relu(hod, s2, fk) : __viaddmax_s16x2(hod, s2, fk);
+    }
+};
+
+#define K3_CELL(k)                                                                                   \
+    {                                                                                                \
+        unsigned s_lo = lds32(cb_lo[k] + roff_lo);                                                   \
+        unsigned s_hi = lds32(cb_hi[k] + roff_hi);                                                   \
+        unsigned s2 = s_hi * 65536u + s_lo;                                                          \
+        unsigned Fk = __viaddmax_s16x2(F[k], ext2, Ho[k]);                                           \
+        unsigned G = K3Cell<MODE>::g(HoD, s2, Fk);                                                   \
+        if (k == 15) m15 = __vadd2(HoD, s2);                                                         \
+        E = __viaddmax_s16x2(E, ext2, GoP);                                                          \
+        GoP = __vadd2(G, open2);                                                                     \
+        HoD = Ho[k];                                                                                 \
+        Ho[k] = __viaddmax_s16x2(E, open2, GoP);                                                     \
+        F[k] = Fk;                                                                                   \
+    }
+
+// ---- K3: fill ---------------------------------------------------------------------------------------------------------
+// One warp = one pair; lane l of sweep sw owns the 32-column pass q = 32 sw + l and runs l row blocks (of 4 rows) behind
+// lane 0, so the last column of a pass reaches the next lane by shuffles (as in K2); the last lane's column reaches
+// lane 0 of the next sweep through the pair's own border store, which the walker reads anyway.
+template <int MODE>
+__global__ void __launch_bounds__(K3_WARPS * 32, 1)
+k3_fill_kernel(const uint8_t *__restrict__ a_all, const uint8_t *__restrict__ b_all, const K3Pair *__restrict__ pairs, int n_pairs,
+               const int32_t *__restrict__ mat, int nl, int open, int ext, uint4 *colb, unsigned *rowb, int *counter)
+{
+    extern __shared__ __align__(16) unsigned T_sh[];               // [nl*nl][32 lanes]: (s - open) & 0xFFFF
+    for (int idx = threadIdx.x; idx < nl * nl * 32; idx += blockDim.x)
+        T_sh[idx] = (unsigned)(mat[idx >> 5] - open) & 0xFFFFu;
+    __syncthreads();
+
+    const int lane = threadIdx.x & 31;
+    const unsigned tbase = (unsigned)__cvta_generic_to_shared(T_sh) + lane * 4;
+    const unsigned rowstride = (unsigned)nl * 128u;
+    const unsigned open2 = pack2(open, open), ext2 = pack2(ext, ext);
+    const unsigned pad = (unsigned)(nl - 1);
+    const int sent = 10 * open + 10 * ext;
+    // Ho = H + open of boundary cell (0, j) / (j, 0): global 2 open + (j-1) ext (SA.rs:100-118), local 0 + open
+    auto ho_bnd = [=](int j) { return (MODE == SWB_LOCAL || j == 0) ? open : 2 * open + (j - 1) * ext; };
+
+    for (;;) {
+        int g = 0;
+        if (lane == 0) g = atomicAdd(counter, 1);
+        g = __shfl_sync(0xffffffffu, g, 0);
+        if (g >= n_pairs) break;
+        const K3Pair P = pairs[g];
+        const uint8_t *a = a_all + P.a_off, *b = b_all + P.b_off;
+        const int la = P.la, lb = P.lb;
+        const int n_pass = (lb + K1_STRIP - 1) / K1_STRIP;
+        const int nblk = (la + 1 + 3) >> 2;                          // row blocks: steps 1 .. la+1 (the high half trails by one row)
+        const int sweeps = (n_pass + 31) >> 5;
+        const int n_ck = la / K3_R;                                  // checkpoint rows R m - 1, m = 1 .. n_ck
+        uint4 *cb = colb + P.colb_off;                               // [pass][nblk + 1][2]
+        unsigned *rb = rowb + P.rowb_off;                            // [m - 1][pass][80]
+
+        for (int sw = 0; sw < sweeps; ++sw) {
+            const int q = sw * 32 + lane;
+            const bool has_pass = q < n_pass;
+            const int jbase = q * K1_STRIP;
+            const int lanes_here = min(32, n_pass - sw * 32);
+            const int n_gb = nblk + lanes_here - 1;
+            unsigned cb_lo[K1_HALF], cb_hi[K1_HALF], Ho[K1_HALF], F[K1_HALF];
+            const unsigned fdelta = pack2(sent - open, sent - open);
+#pragma unroll
+            for (int k = 0; k < K1_HALF; ++k) {
+                const int j1 = jbase + k, j2 = jbase + K1_HALF + k;
+                const unsigned c1 = (has_pass && j1 < lb) ? (unsigned)b[j1] : pad;
+                const unsigned c2 = (has_pass && j2 < lb) ? (unsigned)b[j2] : pad;
+                cb_lo[k] = tbase + c1 * 128u; cb_hi[k] = tbase + c2 * 128u;
+                if (MODE == SWB_LOCAL) { Ho[k] = open2; F[k] = 0u; }
+                else { Ho[k] = pack2(ho_bnd(j1 + 1), ho_bnd(j2 + 1)); F[k] = __vadd2(Ho[k], fdelta); }
+            }
+            const bool first = (q == 0);                              // left boundary = column 0 of the matrix
+            const bool from_g = (lane == 0 && sw > 0);                // left boundary = the stored last column of pass q - 1
+            unsigned HoD = MODE == SWB_LOCAL ? open2 : pack2(ho_bnd(jbase), open);
+            unsigned r_prev = pad;
+            unsigned lo15_Ho = MODE == SWB_LOCAL ? open2 : pack2(ho_bnd(jbase + K1_HALF), open), lo15_E = open2;
+            unsigned c1 = open2, c2 = open2, c3 = open2;              // this lane's (Ho, E) words of rows 1..3 of its previous block
+            const uint4 *gin = cb + ((size_t)(q > 0 ? q - 1 : 0) * (nblk + 1)) * 2;
+            uint4 g_cur = make_uint4(open2, open2, open2, open2), g_next = g_cur;
+            if (from_g) { g_cur = gin[0]; g_next = gin[2]; }
+            uint4 *gout = cb + ((size_t)q * (nblk + 1)) * 2;
+
+#pragma unroll 1
+            for (int gbk = 0; gbk < n_gb; ++gbk) {
+                const int bl = gbk - lane;                            // this lane's row block
+                const bool active = has_pass && bl >= 0 && bl < nblk;
+                const int i0 = bl * 4;
+                // rows i0+1..i0+3 of the left boundary: the left lane's words 1..3 of ITS previous block (it runs one block ahead)
+                const unsigned s1 = __shfl_up_sync(0xffffffffu, c1, 1), s2_ = __shfl_up_sync(0xffffffffu, c2, 1),
+                               s3 = __shfl_up_sync(0xffffffffu, c3, 1);
+                unsigned bq[4];
+                if (first) {
+#pragma unroll
+                    for (int t = 0; t < 4; ++t) {
+                        const int hb = ho_bnd(i0 + t + 1);
+                        bq[t] = MODE == SWB_LOCAL ? open2 : pack2(hb, hb - open + sent);      // column 0 (SA.rs:109-118)
+                    }
+                } else if (from_g) { bq[0] = g_cur.y; bq[1] = g_cur.z; bq[2] = g_cur.w; bq[3] = g_next.x; }
+                else { bq[0] = s1; bq[1] = s2_; bq[2] = s3; bq[3] = open2; }
+                unsigned word = 0;
+                if (active) {
+#pragma unroll
+                    for (int t = 0; t < 4; ++t) word |= ((i0 + t < la) ? (unsigned)a[i0 + t] : pad) << (8 * t);
+                }
+                const bool snap = active && ((bl + 1) % (K3_R / 4) == 0) && ((bl + 1) / (K3_R / 4) <= n_ck);
+                unsigned *rdst = rb + ((size_t)(snap ? (bl + 1) / (K3_R / 4) - 1 : 0) * n_pass + q) * K3_ROWB_WORDS;
+                unsigned wout[4] = {open2, open2, open2, open2}, mf[4] = {0u, 0u, 0u, 0u};
+#pragma unroll
+                for (int t = 0; t < 4; ++t) {
+                    if (t == 1) {
+                        // row i0+4 of the left boundary is the left lane's first word of THIS block
+                        const unsigned s0 = __shfl_up_sync(0xffffffffu, wout[0], 1);
+                        if (!first && !from_g) bq[3] = s0;
+                    }
+                    if (active) {
+                        const unsigned r = (word >> (t * 8)) & 0xFFu;
+                        const unsigned roff_lo = r * rowstride, roff_hi = r_prev * rowstride;
+                        r_prev = r;
+                        unsigned GoP = __byte_perm(bq[t], lo15_Ho, 0x5410);
+                        unsigned E = __byte_perm(bq[t], lo15_E, 0x5432);
+                        const unsigned HoD_next = GoP;
+                        unsigned m15 = 0;
+                        K3_CELL(0) K3_CELL(1) K3_CELL(2) K3_CELL(3) K3_CELL(4) K3_CELL(5) K3_CELL(6) K3_CELL(7)
+                        K3_CELL(8) K3_CELL(9) K3_CELL(10) K3_CELL(11) K3_CELL(12) K3_CELL(13) K3_CELL(14) K3_CELL(15)
+                        if (MODE != SWB_LOCAL && t == 0 && bl == 0) {
+                            // the high half has just run its "row 0" step on PAD residues: put the boundary row there instead
+#pragma unroll
+                            for (int k = 0; k < K1_HALF; ++k) {
+                                const int hb = ho_bnd(jbase + K1_HALF + k + 1);
+                                Ho[k] = (Ho[k] & 0xFFFFu) | ((unsigned)hb << 16);
+                                F[k] = (F[k] & 0xFFFFu) | ((unsigned)(hb - open + sent) << 16);
+                            }
+                            E = (E & 0xFFFFu) | ((unsigned)(ho_bnd(jbase + K1_STRIP) - open) << 16);   // X(0, jbase+32) = H(0, .)
+                            m15 = (m15 & 0xFFFFu) | ((unsigned)(ho_bnd(jbase + K1_STRIP) - open + sent) << 16);
+                        }
+                        wout[t] = __byte_perm(Ho[15], E, 0x7632);        // (Ho, E) of column 32q+32 at row i0 + t
+                        mf[t] = __byte_perm(m15, F[15], 0x7632);         // (M, F) of the same cell
+                        lo15_Ho = Ho[15]; lo15_E = E;
+                        HoD = HoD_next;
+                        if (snap && t >= 1) {                            // row checkpoint: see the header comment / KT3
+                            uint4 *d4 = reinterpret_cast<uint4 *>(rdst + (t - 1) * 16);
+                            d4[0] = make_uint4(Ho[0], Ho[1], Ho[2], Ho[3]); d4[1] = make_uint4(Ho[4], Ho[5], Ho[6], Ho[7]);
+                            d4[2] = make_uint4(Ho[8], Ho[9], Ho[10], Ho[11]); d4[3] = make_uint4(Ho[12], Ho[13], Ho[14], Ho[15]);
+                            if (t >= 2) {
+                                uint4 *f4 = reinterpret_cast<uint4 *>(rdst + 48 + (t - 2) * 16);
+                                f4[0] = make_uint4(F[0], F[1], F[2], F[3]); f4[1] = make_uint4(F[4], F[5], F[6], F[7]);
+                                f4[2] = make_uint4(F[8], F[9], F[10], F[11]); f4[3] = make_uint4(F[12], F[13], F[14], F[15]);
+                            }
+                        }
+                    }
+                }
+                if (active) {
+                    gout[(size_t)bl * 2] = make_uint4(wout[0], wout[1], wout[2], wout[3]);         // rows i0 .. i0+3 of column 32q+32
+                    gout[(size_t)bl * 2 + 1] = make_uint4(mf[0], mf[1], mf[2], mf[3]);
+                    c1 = wout[1]; c2 = wout[2]; c3 = wout[3];
+                    if (from_g) { g_cur = g_next; if (bl + 2 <= nblk) g_next = gin[(size_t)(bl + 2) * 2]; }
+                }
+            }
+            __syncwarp();                                             // the last lane's column is read by lane 0 in the next sweep
+        }
+    }
+}
+
+// ---- KT3: the walk ------------------------------------------------------------------------------------------------------
+#define KT3_WARPS 8
+
+struct KT3Smem {
+    uint8_t dir[K3_R][32];          // predecessor codes of the recomputed part of the tile
+    int4 left[K3_R + 2];            // (M, X, Y, raw E) of column c0, rows rtop .. cx; local mode: M, X, Y clamped as the reference's states
+    int hm1[33], h0[33];            // H(rtop - 1, c0 + k), H(rtop, c0 + k), k = 0 .. 32
+};
+
+// (M, X, Y, raw E, H) of a stored border cell (row, column 32 q + 32) -- or of a matrix boundary cell.
+template <int MODE>
+__device__ __forceinline__ void kt3_border_cell(const uint4 *cb, int nblk, int q_left, int row, int col0, int open, int o, int e, int &M, int &X, int &Y, int &Eraw, int &H)
+{
+    const int so = (MODE == SWB_GLOBAL) ? o : 0, se = (MODE == SWB_GLOBAL) ? e : 0, sent = 10 * o + 10 * e;
+    if (q_left < 0) {                                   // column 0 (SA.rs:88-93, 109-118)
+        if (row == 0) { M = 0; X = -1; Y = -1; Eraw = -1; H = 0; return; }
+        const int ls = row * se + (so - se);
+        M = ls + sent; X = ls + sent; Y = ls; Eraw = X; H = ls; return;
+    }
+    if (row == 0) {                                     // row 0 (SA.rs:100-108)
+        const int ls = col0 * se + (so - se);
+        M = ls + sent; X = ls; Y = ls + sent; Eraw = X; H = ls; return;
+    }
+    const uint4 *ent = cb + ((size_t)q_left * (nblk + 1) + (row >> 2)) * 2;
+    const uint4 w0 = ent[0], w1 = ent[1];
+    const int t = row & 3;
+    const unsigned a = t == 0 ? w0.x : (t == 1 ? w0.y : (t == 2 ? w0.z : w0.w));
+    const unsigned b = t == 0 ? w1.x : (t == 1 ? w1.y : (t == 2 ? w1.z : w1.w));
+    H = lo16(a) - open; Eraw = hi16(a); M = lo16(b); Y = hi16(b); X = Eraw;
+    if (MODE == SWB_LOCAL) { M = max(M, 0); X = max(X, 0); Y = max(Y, 0); }
+}
+
+template <int MODE>
+__global__ void __launch_bounds__(KT3_WARPS * 32)
+kt3_walk_kernel(const uint8_t *__restrict__ a_all, const uint8_t *__restrict__ b_all, const K3Pair *__restrict__ pairs, int n_pairs,
+                const int32_t *__restrict__ mat, int nl, int o, int e, const uint4 *__restrict__ colb, const unsigned *__restrict__ rowb,
+                int32_t *__restrict__ idx_a, int32_t *__restrict__ idx_b, int32_t *__restrict__ ncols_out, KWResult *__restrict__ res)
+{
+    extern __shared__ int mat_sh[];
+    __shared__ KT3Smem sm_all[KT3_WARPS];
+    for (int k = threadIdx.x; k < nl * nl; k += blockDim.x) mat_sh[k] = mat[k];
+    __syncthreads();
+    const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
+    const int p = blockIdx.x * KT3_WARPS + wib;
+    if (p >= n_pairs) return;
+    KT3Smem &S = sm_all[wib];
+    const K3Pair P = pairs[p];
+    const uint8_t *a = a_all + P.a_off, *b = b_all + P.b_off;
+    const int la = P.la, lb = P.lb;
+    const int nblk = (la + 1 + 3) >> 2, n_pass = (lb + K1_STRIP - 1) / K1_STRIP;
+    const uint4 *cb = colb + P.colb_off;
+    const unsigned *rb = rowb + P.rowb_off;
+    const int open = o, sent = 10 * o + 10 * e;
+    const int so = (MODE == SWB_GLOBAL) ? o : 0, se = (MODE == SWB_GLOBAL) ? e : 0;
+    int32_t *xa = idx_a + P.out_off, *xb = idx_b + P.out_off;
+
+    int cx = la, cy = lb, st = P.start_state, n = 0, score = P.score;
+    int rtop = 0, c0 = 0, tcx = -1, tcy = -1;           // the tile in shared memory: rows (rtop, tcx], columns (c0, tcy]
+    bool need_start = (MODE != SWB_LOCAL);
+
+    for (;;) {
+        if (cx >= 1 && cy >= 1 && !(tcx >= 0 && cx > rtop && cx <= tcx && cy > c0 && cy <= tcy)) {
+            // ---- recompute the part of the tile of (cx, cy) that lies above-left of the cursor
+            const int q = (cy - 1) >> 5;
+            c0 = q << 5;
+            const int m = cx / K3_R;
+            rtop = m ? K3_R * m - 1 : 0;
+            const int nrows = cx - rtop, ncols = cy - c0;
+            tcx = cx; tcy = cy;
+            __syncwarp();
+            for (int r = lane; r <= nrows; r += 32) {
+                int M, X, Y, Er, H;
+                kt3_border_cell<MODE>(cb, nblk, q - 1, rtop + r, c0, open, o, e, M, X, Y, Er, H);
+                S.left[r] = make_int4(M, X, Y, Er);
+                if (r == 0) S.h0[0] = H;
+            }
+            if (lane == 0) {
+                int M, X, Y, Er, H = 0;
+                if (rtop > 0) kt3_border_cell<MODE>(cb, nblk, q - 1, rtop - 1, c0, open, o, e, M, X, Y, Er, H);
+                S.hm1[0] = H;
+            }
+            // top border row rtop of this lane's column j = c0 + 1 + lane
+            const int j = c0 + 1 + lane;
+            int Mu, Xu, Yu;
+            if (rtop == 0) {
+                const int ls = j * se + (so - se);
+                Mu = ls + sent; Xu = ls; Yu = ls + sent;
+                S.h0[lane + 1] = ls; S.hm1[lane + 1] = 0;
+            } else {
+                const unsigned *w = rb + ((size_t)(m - 1) * n_pass + q) * K3_ROWB_WORDS;
+                const int k = lane & 15;
+                int hm1, h0, f0;
+                if (lane < 16) { hm1 = lo16(w[k]) - open; h0 = lo16(w[16 + k]) - open; f0 = lo16(w[48 + k]); }
+                else { hm1 = hi16(w[16 + k]) - open; h0 = hi16(w[32 + k]) - open; f0 = hi16(w[64 + k]); }
+                S.hm1[lane + 1] = hm1; S.h0[lane + 1] = h0;
+                Yu = f0; Mu = 0; Xu = 0;
+            }
+            __syncwarp();
+            if (rtop > 0) {
+                const int sc = (j <= lb) ? mat_sh[(int)a[rtop - 1] * nl + (int)b[j - 1]] : 0;
+                Mu = S.hm1[lane] + sc;                               // M(rtop, j) = H(rtop-1, j-1) + s
+                int ev = S.left[0].w + (lane + 1) * e;               // X(rtop, j): the row recurrence from the stored E of column c0
+                for (int k = 0; k <= lane; ++k) ev = max(ev, S.h0[k] + o + (lane - k) * e);
+                Xu = ev;
+                if (MODE == SWB_LOCAL) { Mu = max(Mu, 0); Xu = max(Xu, 0); Yu = max(Yu, 0); }
+            }
+            // diagonal of this lane's first cell: cell (rtop, j - 1)
+            int dM = __shfl_up_sync(0xffffffffu, Mu, 1), dX = __shfl_up_sync(0xffffffffu, Xu, 1), dY = __shfl_up_sync(0xffffffffu, Yu, 1);
+            if (lane == 0) { const int4 v = S.left[0]; dM = v.x; dX = v.y; dY = v.z; }
+            int hd0 = __vimax3_s32(dM, dX, dY); unsigned ad0 = kw_am(dM, dX, dY);
+            int lastM = 0, lastX = 0, lastY = 0;
+            const int bcode = (j <= lb) ? (int)b[j - 1] : 0;
+            const int n_steps = nrows + ncols - 1;
+            for (int t = 0; t < n_steps; ++t) {
+                const int r = t - lane + 1;                          // row of this lane in this step, 1 .. nrows
+                int tM = __shfl_up_sync(0xffffffffu, lastM, 1), tX = __shfl_up_sync(0xffffffffu, lastX, 1), tY = __shfl_up_sync(0xffffffffu, lastY, 1);
+                if (lane < ncols && r >= 1 && r <= nrows) {
+                    if (lane == 0) { const int4 v = S.left[r]; tM = v.x; tX = v.y; tY = v.z; }
+                    const int i = rtop + r;
+                    const int s = mat_sh[(int)a[i - 1] * nl + bcode];
+                    const int hd = hd0; const unsigned ad = ad0;
+                    hd0 = __vimax3_s32(tM, tX, tY); ad0 = kw_am(tM, tX, tY);
+                    int mm, xx, yy; unsigned code;
+                    kw_cell<MODE>(hd, ad, tM, tX, tY, Mu, Xu, Yu, s, o, e, o, e, mm, xx, yy, code);
+                    Mu = mm; Xu = xx; Yu = yy;
+                    lastM = mm; lastX = xx; lastY = yy;
+                    S.dir[r - 1][lane] = (uint8_t)code;
+                }
+            }
+            __syncwarp();
+            if (need_start) {                                        // cell (la, lb): first strict maximum in the order M, X, Y (SA.rs:302-308)
+                const int src = ncols - 1;
+                const int fm = __shfl_sync(0xffffffffu, Mu, src), fx = __shfl_sync(0xffffffffu, Xu, src), fy = __shfl_sync(0xffffffffu, Yu, src);
+                score = fm; st = 0;
+                if (fx > score) { score = fx; st = 1; }
+                if (fy > score) { score = fy; st = 2; }
+                need_start = false;
+            }
+        }
+        // ---- one step of the walk (backtrack, SA.rs:346-383), the same on every lane; lane 0 writes
+        unsigned prev;
+        if (cx >= 1 && cy >= 1) prev = ((unsigned)S.dir[cx - rtop - 1][cy - c0 - 1] >> (2 * st)) & 3u;
+        else if (cx == 0 && cy == 0) prev = 0;
+        else if (cx == 0) {                                          // row 0: prev = GAPINX for all states (SA.rs:105-107)
+            prev = 1;
+            if (MODE == SWB_LOCAL && (st == 1 || sent == 0)) prev = 3;
+        } else {                                                     // column 0: prev = GAPINY (SA.rs:114-116)
+            prev = 2;
+            if (MODE == SWB_LOCAL && (st == 2 || sent == 0)) prev = 3;
+        }
+        if (MODE == SWB_LOCAL && prev == 3) break;
+        if (st == 0) {
+            if (cx == 0 || cy == 0) { n = -2; break; }
+            if (lane == 0) { xa[n] = cx - 1; xb[n] = cy - 1; }
+            ++n; --cx; --cy;
+        } else if (st == 1) {
+            if (cy == 0) { n = -2; break; }
+            if (lane == 0) { xa[n] = -1; xb[n] = cy - 1; }
+            ++n; --cy;
+        } else {
+            if (cx == 0) { n = -2; break; }
+            if (lane == 0) { xa[n] = cx - 1; xb[n] = -1; }
+            ++n; --cx;
+        }
+        if (cx == 0 && cy == 0) break;
+        st = (int)prev;
+    }
+    if (lane == 0) {
+        ncols_out[p] = n;
+        KWResult R; R.score = score; R.end_i = la; R.end_j = lb; R.state = P.start_state;
+        res[p] = R;
+    }
+}
+
+// ---- host side ----------------------------------------------------------------------------------------------------------
+// Which pairs may take the packed path.  |open| >= |extend| makes the Gotoh values equal the three-state values.  Local
+// mode: the caller knows the pair's score from the scan and has checked it against the s16 limit (every H is <= it).
+// Global mode has no clamp: the lengths must bound every value.  Upwards min(la,lb) best substitutions; downwards a cell
+// (i, j) is at least the path "min(i,j) worst substitutions, then one gap of |i-j|", whose minimum over the matrix sits in
+// a corner, and the states / temporaries of a cell lie at most 3 openings + one substitution + the sentinel below that.
+bool k3_eligible(const swb_engine *e, int64_t la, int64_t lb)
+{
+    if (e->o > e->e || la < 1 || lb < 1 || la > 0x3FFFFFF0 || lb > 0x3FFFFFF0) return false;
+    if (getenv("SWB_NO_K3")) return false;
+    if (e->mode == SWB_LOCAL) return true;
+    if (e->mode != SWB_GLOBAL) return false;
+    const int64_t mn = std::min(la, lb), mx = std::max(la, lb);
+    const int64_t ao = -(int64_t)e->o, ae = -(int64_t)e->e, sp = std::max(e->smax, 0), sn = std::max(-e->smin, 0);
+    const int64_t up = mn * sp + ao + sp + 64;
+    const int64_t corner = std::max(sn * mn + ae * (mx - mn), ae * mx) + ao;
+    const int64_t down = corner + 3 * ao + sn + (10 * ao + 10 * ae) + 64;
+    return up <= 32000 && down <= 32000;
+}
+
+void k3_sizes(int32_t la, int32_t lb, int64_t *colb_uint4, int64_t *rowb_words)
+{
+    const int64_t n_pass = (lb + K1_STRIP - 1) / K1_STRIP, nblk = (la + 1 + 3) >> 2, n_ck = la / K3_R;
+    *colb_uint4 = n_pass * (nblk + 1) * 2;
+    *rowb_words = n_ck * n_pass * K3_ROWB_WORDS;
+}
+
+cudaError_t k3_launch(const swb_engine *e, const uint8_t *d_a, const uint8_t *d_b, const K3Pair *d_pairs, int n_pairs,
+                      uint4 *d_colb, unsigned *d_rowb, int *d_counter, int32_t *d_idx_a, int32_t *d_idx_b, int32_t *d_ncols,
+                      KWResult *d_res, cudaStream_t st)
+{
+    if (n_pairs <= 0) return cudaSuccess;
+    const int nl = e->n + 1;
+    const size_t smem = (size_t)nl * nl * 32 * sizeof(unsigned);
+    cudaError_t err = cudaMemsetAsync(d_counter, 0, sizeof(int), st);
+    if (err != cudaSuccess) return err;
+    const int fill_blocks = std::min(e->sm_count, (n_pairs + K3_WARPS - 1) / K3_WARPS);
+    const int walk_blocks = (n_pairs + KT3_WARPS - 1) / KT3_WARPS;
+    const size_t wsmem = (size_t)nl * nl * sizeof(int);
+    if (e->mode == SWB_LOCAL) {
+        if ((err = cudaFuncSetAttribute(k3_fill_kernel<SWB_LOCAL>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)) != cudaSuccess) return err;
+        k3_fill_kernel<SWB_LOCAL><<<fill_blocks, K3_WARPS * 32, smem, st>>>(d_a, d_b, d_pairs, n_pairs, e->d_mat, nl, e->o, e->e, d_colb, d_rowb, d_counter);
+        kt3_walk_kernel<SWB_LOCAL><<<walk_blocks, KT3_WARPS * 32, wsmem, st>>>(d_a, d_b, d_pairs, n_pairs, e->d_mat, nl, e->o, e->e, d_colb, d_rowb,
+                                                                              d_idx_a, d_idx_b, d_ncols, d_res);
+    } else {
+        if ((err = cudaFuncSetAttribute(k3_fill_kernel<SWB_GLOBAL>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)) != cudaSuccess) return err;
+        k3_fill_kernel<SWB_GLOBAL><<<fill_blocks, K3_WARPS * 32, smem, st>>>(d_a, d_b, d_pairs, n_pairs, e->d_mat, nl, e->o, e->e, d_colb, d_rowb, d_counter);
+        kt3_walk_kernel<SWB_GLOBAL><<<walk_blocks, KT3_WARPS * 32, wsmem, st>>>(d_a, d_b, d_pairs, n_pairs, e->d_mat, nl, e->o, e->e, d_colb, d_rowb,
+                                                                               d_idx_a, d_idx_b, d_ncols, d_res);
+    }
+    return cudaGetLastError();
+}

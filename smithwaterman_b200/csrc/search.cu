@@ -12,6 +12,7 @@
 // shards.  Each hit is traced back by the shard that owns it (swb_search_align), so the traceback work divides by the
 // number of GPUs as well.
 #include <algorithm>
+#include <cmath>
 #include <cstring>
 #include <numeric>
 #include <thread>
@@ -424,6 +425,7 @@ extern "C" int swb_search_align(swb_engine *e, const char *query, int64_t lq, sw
         J.ra = query; J.rb = db->h_letters.data() + db->h_off[loc]; J.la_full = lq; J.lb_full = lb; J.out = k;
         if (e->mode == SWB_LOCAL && hits[k].end_q >= 1 && hits[k].end_t >= 1 && hits[k].end_q <= lq && hits[k].end_t <= lb) {
             J.la = (int32_t)hits[k].end_q; J.lb = (int32_t)hits[k].end_t;
+            J.known_score = (int32_t)std::llround((double)hits[k].score * e->scale);      // the scan's score: the hit may take the packed path
         }
         if (lq == 0 || lb == 0 || (e->mode == SWB_LOCAL && hits[k].end_q < 1)) {     // nothing to trace on the device: closed forms
             const int64_t oa[2] = {0, lq}, ob[2] = {0, lb};

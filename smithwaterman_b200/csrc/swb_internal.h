@@ -2,6 +2,7 @@
 #pragma once
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include <climits>
 #include <string>
 #include <vector>
 
@@ -215,10 +216,27 @@ struct AlnJob {
     const char *ra, *rb;            // letters as given
     int64_t la_full, lb_full;       // lengths of the whole sequences (retain_all padding, SA.rs:512-549)
     int64_t out;                    // index into outs / souts
+    int32_t known_score = INT32_MIN;// local mode: the scan's scaled score of the pair whose end cell is (la, lb) -- allows the packed path
 };
 int align_jobs_device(swb_engine *e, const uint8_t *d_a, const uint8_t *d_b, const std::vector<AlnJob> &jobs, bool retain_all,
                       swb_alignment *outs, swb_aln_stats *souts, const int32_t *d_pssm, const uint8_t *d_ra, const uint8_t *d_rb);
 bool swb_range_ok(const swb_engine *e, int64_t la, int64_t lb, int64_t smax_abs = -1);   // do the scores of a pair fit the int32 lanes of KW?
+
+// ---- K3 / KT3: packed fill with tile borders + tile-recompute traceback (k3_tile.cu) ------------------------------------
+struct K3Pair {
+    int64_t a_off, b_off;           // offsets into the device code arrays
+    int32_t la, lb;                 // DP extents (local mode: the prefix box that ends at the end cell)
+    int64_t colb_off;               // uint4 units: last column of every pass, [pass][row block + 1 slack][2]
+    int64_t rowb_off;               // 32-bit words: row checkpoints, [checkpoint][pass][80]
+    int64_t out_off;                // offset of the pair's reversed column lists
+    int32_t start_state;            // local: 0 (MATCH); global: taken from the recomputed cell (la, lb)
+    int32_t score;                  // local: the scan's score (scaled); global: filled in by the walker
+};
+bool k3_eligible(const swb_engine *e, int64_t la, int64_t lb);       // mode, |open| >= |extend| and the static s16 bound (global)
+void k3_sizes(int32_t la, int32_t lb, int64_t *colb_uint4, int64_t *rowb_words);
+cudaError_t k3_launch(const swb_engine *e, const uint8_t *d_a, const uint8_t *d_b, const K3Pair *d_pairs, int n_pairs,
+                      uint4 *d_colb, unsigned *d_rowb, int *d_counter, int32_t *d_idx_a, int32_t *d_idx_b, int32_t *d_ncols,
+                      KWResult *d_res, cudaStream_t st);
 
 // K0
 cudaError_t k0_run(int which, int sm_count, double *thread_instr_per_s);

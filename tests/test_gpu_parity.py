@@ -936,3 +936,69 @@ def test_perl_harness_over_the_cli(tmp_path):
     r = subprocess.run(["perl", os.path.join(ROOT, "test", "check_results.pl")], cwd=tmp_path, capture_output=True, text=True)
     assert r.returncode == 0, r.stderr + r.stdout
     assert r.stdout.splitlines()[-2:] == ["OK", "Checked 300 results"]
+
+
+@pytest.mark.parametrize("go,ge,protein", [(5.0, 2.0, False), (10.0, 0.5, True), (2.0, 2.0, False)])
+def test_packed_traceback_path_global(go, ge, protein, monkeypatch):
+    """The packed traceback path (csrc/k3_tile.cu: s16x2 fill with tile borders + tile-recompute walk) in global mode:
+    strings, index lists and scores equal the dense oracle's on pairs of every shape -- single pass, several sweeps of
+    1024 columns, fewer rows than one checkpoint, one-letter sequences, unrelated pairs -- and equal the direction-byte
+    path on 6 kb pairs."""
+    rng = np.random.default_rng(int(go * 7 + ge * 3))
+    m = swb.SubstitutionMatrix.get_blosum62_matrix() if protein else swb.SubstitutionMatrix.get_mat_matrix(2.0, -3.0)
+    al = AA if protein else "ACGT"
+    eng = swb.SequenceAlignment(m, go, ge, swb.ALIGN_GLOBAL)
+    oeng = O.Engine(_omatrix(m), go, ge, swb.ALIGN_GLOBAL)
+    sa, sb = [], []
+    for la, lb in [(1, 1), (1, 40), (40, 1), (5, 70), (63, 33), (64, 32), (65, 31), (130, 1100), (1100, 130), (300, 2100), (700, 700), (257, 96)]:
+        if protein and max(la, lb) > 1400:
+            la, lb = min(la, 1300), min(lb, 1300)
+        sa.append(_rand_seqs(rng, 1, la, la, al)[0]); sb.append(_rand_seqs(rng, 1, lb, lb, al)[0])
+    for k in range(25):
+        base = _rand_seqs(rng, 1, 30, 1300, al)[0]
+        sa.append(base); sb.append(_mutate(rng, base, 0.1, 0.04, 0.04, alphabet=al.encode()))
+    res = eng.align_list(sa, sb, True)
+    assert eng.stats()["k3_pairs"] == len(sa)
+    for k, r in enumerate(res):
+        r1, r2, s = oeng.align(sa[k].decode(), sb[k].decode(), True)
+        assert (r["aln_a"], r["aln_b"], r["score"]) == ("".join(r1), "".join(r2), s), k
+        xa, xb, _, ei, ej = oeng.raw(_omatrix(m).seq_to_index(sa[k].decode()), _omatrix(m).seq_to_index(sb[k].decode()))
+        assert np.array_equal(r["idx_a"], xa) and np.array_equal(r["idx_b"], xb) and (r["end_a"], r["end_b"]) == (ei, ej)
+    if not protein:                                               # 6 kb pairs: packed path == direction-byte path
+        big_a = _rand_seqs(rng, 3, 6000, 6000, al)
+        big_b = [_mutate(rng, x, 0.05, 0.05, 0.05) for x in big_a]
+        r3 = eng.align_list(big_a, big_b, True)
+        assert eng.stats()["k3_pairs"] == 3
+        monkeypatch.setenv("SWB_NO_K3", "1")
+        rw = eng.align_list(big_a, big_b, True)
+        assert eng.stats()["k3_pairs"] == 0
+        for x, y in zip(r3, rw):
+            assert (x["aln_a"], x["aln_b"], x["score"]) == (y["aln_a"], y["aln_b"], y["score"])
+    eng.close()
+
+
+def test_packed_traceback_path_local_hits():
+    """Local mode on the packed path: hits of a database search are traced inside the prefix box of their end cell with
+    the scan's score as the s16 guarantee; strings equal the oracle's, with and without retain_all, for subjects of one
+    pass up to several sweeps, and the direction-byte path gives the same."""
+    from smithwaterman_b200 import search as S
+    rng = np.random.default_rng(99)
+    m = swb.SubstitutionMatrix.get_blosum62_matrix()
+    eng = swb.SequenceAlignment(m, 10.0, 0.5, swb.ALIGN_LOCAL)
+    oeng = O.Engine(_omatrix(m), 10.0, 0.5, swb.ALIGN_LOCAL)
+    query = _rand_seqs(rng, 1, 1300, 1300)[0]
+    seqs = _rand_seqs(rng, 200, 20, 400)
+    for k in range(0, 200, 10):
+        lo = int(rng.integers(0, 900)); w = query[lo:lo + int(rng.integers(40, 400))]
+        seqs[k] = _rand_seqs(rng, 1, 0, 50)[0] + _mutate(rng, w, 0.2, 0.03, 0.03, alphabet=AA.encode()) + _rand_seqs(rng, 1, 0, 50)[0]
+    seqs[5] = _rand_seqs(rng, 1, 1500, 1500)[0] + query[100:1200] + _rand_seqs(rng, 1, 300, 300)[0]     # hit far right in a long subject: 3 sweeps
+    db = S.Database.from_sequences(seqs)
+    ddb = S.DeviceDatabase(eng, db)
+    hits = ddb.search(query, 30)
+    for ra in (False, True):
+        alns = ddb.align(query, hits, ra)
+        assert eng.stats()["k3_pairs"] >= 20
+        for k, h in enumerate(hits):
+            r1, r2, s = oeng.align(query.decode(), seqs[int(h["index"])].decode(), ra)
+            assert (alns[k]["aln_a"], alns[k]["aln_b"], alns[k]["score"]) == ("".join(r1), "".join(r2), s), (k, ra)
+    ddb.free(); eng.close()
