@@ -78,9 +78,10 @@ class ClockSampler(threading.Thread):
                 "reasons": sorted(self.reasons), "samples": len(self.samples)}
 
 
-def cpu_reference_gcups(a, oa, b, ob, target_s, threads):
+def cpu_reference_gcups(a, oa, b, ob, target_s, threads, layout="flat"):
     """The reference's CPU path (dense f32 fill + score scan, SA.rs:55-272, 438-467) as restated in oracle/,
-    OpenMP over pairs on `threads` host threads, on the first pairs of the same workload."""
+    OpenMP over pairs on `threads` host threads, on the first pairs of the same workload.  layout: "flat" arrays or
+    "faithful" = the reference's own cell structure."""
     from oracle import oracle as O
     m = O.Matrix.blosum62()
 
@@ -88,7 +89,7 @@ def cpu_reference_gcups(a, oa, b, ob, target_s, threads):
         ia = m.seq_to_index_bytes(a[:oa[k]]) if hasattr(m, "seq_to_index_bytes") else _idx(m, a[:oa[k]])
         ib = _idx(m, b[:ob[k]])
         t0 = time.perf_counter()
-        O.score_batch_f32(ia, oa[:k + 1].copy(), ib, ob[:k + 1].copy(), m.scores, 10.0, 0.5, O.ALIGN_LOCAL, threads)
+        O.score_batch_f32(ia, oa[:k + 1].copy(), ib, ob[:k + 1].copy(), m.scores, 10.0, 0.5, O.ALIGN_LOCAL, threads, layout)
         dt = time.perf_counter() - t0
         cells = float(np.sum((oa[1:k + 1] - oa[:k]) * (ob[1:k + 1] - ob[:k])))
         return cells, dt
@@ -423,6 +424,12 @@ def main():
         g, k, ccells, dt = cpu_reference_gcups(a, oa, b, ob, args.cpu_seconds, threads)
         cpu = {"value": g, "unit": "GCUPS", "cores": threads, "kind": "port",
                "sample": "first %d pairs of the workload (%.3g cells, %.1f s): dense f32 fill + score scan of the reference, OpenMP over pairs" % (k, ccells, dt)}
+        # the other flavours, short samples (the reference CLI itself is serial, SA-main.rs:35-45)
+        fl = {}
+        for tag, thr, lay in (("flat_1_thread", 1, "flat"), ("faithful_1_thread", 1, "faithful"), ("faithful_%d_threads" % threads, threads, "faithful")):
+            g2, k2, c2, d2 = cpu_reference_gcups(a, oa, b, ob, 2.0, thr, lay)
+            fl[tag] = {"gcups": g2, "pairs": k2, "seconds": d2}
+        cpu["flavours"] = fl
     # ---- the other BASELINE configs, bounded sizes, N = 1 only: reported beside the headline, not part of it
     extras = None
     if world == 1 and not args.no_extras:

@@ -29,7 +29,7 @@ MODE_NAMES = {ALIGN_GLOBAL: "Global alignment", ALIGN_GLOCAL: "Glocal alignment"
 
 def build(force=False):
     so = os.path.join(_HERE, "liboracle.so")
-    srcs = [os.path.join(_HERE, f) for f in ("sw_oracle.c", "sw_oracle_int.c")]
+    srcs = [os.path.join(_HERE, f) for f in ("sw_oracle.c", "sw_oracle_int.c", "sw_oracle_faithful.c", "sw_oracle_fill.inc")]
     if force or not os.path.exists(so) or any(os.path.getmtime(s) > os.path.getmtime(so) for s in srcs):
         subprocess.check_call(["make", "-s", "-C", _HERE, "liboracle.so"])
     return so
@@ -50,6 +50,8 @@ def lib():
         L.swo_score_batch.restype = c.c_int
         L.swo_score_batch.argtypes = [p, p, p, p, c.c_int64, p, c.c_int64, c.c_float, c.c_float, c.c_int,
                                       p, p, p, c.c_int]
+        L.swf_score_batch.restype = c.c_int
+        L.swf_score_batch.argtypes = L.swo_score_batch.argtypes
         L.swo_int_score.restype = c.c_int
         L.swo_int_score.argtypes = [p, c.c_int64, p, c.c_int64, p, c.c_int64, c.c_int32, c.c_int32, c.c_int32,
                                     c.c_int, p, p, p]
@@ -337,14 +339,17 @@ def pack(seqs_idx):
     return np.ascontiguousarray(allv), off
 
 
-def score_batch_f32(a_all, off_a, b_all, off_b, matrix_f32, go, ge, mode, nthreads=1):
-    """Dense f32 fill + score_only scan per pair (the reference's CPU path), OpenMP over pairs."""
+def score_batch_f32(a_all, off_a, b_all, off_b, matrix_f32, go, ge, mode, nthreads=1, layout="flat"):
+    """Dense f32 fill + score_only scan per pair (the reference's CPU path), OpenMP over pairs.
+    layout "flat": contiguous arrays; "faithful": the reference's own data structure, one heap-owning cell per DP cell
+    and an indirect call per score lookup (sw_oracle_faithful.c, SA.rs:556-572)."""
     n = len(off_a) - 1
     sc = np.empty(n, np.float32)
     ei = np.empty(n, np.int64)
     ej = np.empty(n, np.int64)
     m = np.ascontiguousarray(matrix_f32, np.float32)
-    rc = lib().swo_score_batch(_ptr(a_all), _ptr(off_a), _ptr(b_all), _ptr(off_b), n, _ptr(m), m.shape[0],
+    fn = lib().swf_score_batch if layout == "faithful" else lib().swo_score_batch
+    rc = fn(_ptr(a_all), _ptr(off_a), _ptr(b_all), _ptr(off_b), n, _ptr(m), m.shape[0],
                                float(go), float(ge), int(mode), _ptr(sc), _ptr(ei), _ptr(ej), int(nthreads))
     if rc:
         raise MemoryError

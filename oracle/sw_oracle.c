@@ -51,109 +51,19 @@ static void swo_penalties(float go, float ge, float *o, float *e)
     if (*e > 0.0f) *e *= -1.0f;
 }
 
-/*
- * fill_matrix, SA.rs:55-272.
- * a,b: residue indices; score(ai,bj) = mat[ai*n+bj] when pssm==0 (SA.rs:646-648),
- * = mat[i + j*la_full] when pssm!=0 (PositionSpecificMatrix, SA.rs:593-595;
- * then a[i]==i, b[j]==j, SA.rs:596-601, and n holds a_length).
- */
-static void swo_fill(swo_buf *B, const int32_t *a, size_t la, const int32_t *b, size_t lb,
-                     const float *mat, size_t n, int pssm, float o_pen, float e_pen, int mode)
-{
-    const size_t W = lb + 1;
-    float start_e, start_o;                       /* SA.rs:74-82 */
-    if (mode == ALIGN_GLOBAL) { start_e = e_pen; start_o = o_pen; }
-    else { start_e = 0.0f; start_o = 0.0f; }
-    const float sentinel_o = 10.0f * o_pen, sentinel_e = 10.0f * e_pen;
-
-    for (size_t ii = 0; ii <= la; ii++) {
-        for (size_t jj = 0; jj <= lb; jj++) {
-            float *c = B->sc + (ii * W + jj) * 3;
-            uint8_t *p = B->pv + (ii * W + jj) * 3;
-            float openal = o_pen, epenal = e_pen;
-            if (ii == 0 && jj == 0) {             /* SA.rs:88-93 */
-                c[CELL_MATCH] = 0.0f;  p[CELL_MATCH] = CELL_MATCH;
-                c[CELL_GAPINX] = -1.0f; p[CELL_GAPINX] = CELL_MATCH;
-                c[CELL_GAPINY] = -1.0f; p[CELL_GAPINY] = CELL_MATCH;
-                continue;
-            }
-            if (ii * jj == 0) { openal = start_o; epenal = start_e; }   /* SA.rs:96-99 */
-            if (ii == 0) {                        /* SA.rs:100-108 */
-                float ls = (float)jj * epenal + (openal - epenal);
-                c[CELL_MATCH] = ls + sentinel_o + sentinel_e;
-                c[CELL_GAPINX] = ls;
-                c[CELL_GAPINY] = ls + sentinel_o + sentinel_e;
-                p[0] = p[1] = p[2] = CELL_GAPINX;
-                continue;
-            } else if (jj == 0) {                 /* SA.rs:109-118 */
-                float ls = (float)ii * epenal + (openal - epenal);
-                c[CELL_MATCH] = ls + sentinel_o + sentinel_e;
-                c[CELL_GAPINX] = ls + sentinel_o + sentinel_e;
-                c[CELL_GAPINY] = ls;
-                p[0] = p[1] = p[2] = CELL_GAPINY;
-                continue;
-            }
-            const float *lt = B->sc + ((ii - 1) * W + (jj - 1)) * 3;   /* SA.rs:121 */
-            const float *l = B->sc + ((ii - 1) * W + jj) * 3;          /* SA.rs:122 */
-            const float *t = B->sc + (ii * W + (jj - 1)) * 3;          /* SA.rs:123 */
-            float mm = pssm ? mat[(size_t)a[ii - 1] + (size_t)b[jj - 1] * n]
-                            : mat[(size_t)a[ii - 1] * n + (size_t)b[jj - 1]];   /* SA.rs:127 */
-            float ms, gx, gy; uint8_t mi, gxi, gyi;
-
-            /* MATCH, SA.rs:139-158 */
-            if (lt[CELL_MATCH] + mm >= lt[CELL_GAPINX] + mm) {
-                if (lt[CELL_MATCH] + mm >= lt[CELL_GAPINY] + mm) { ms = lt[CELL_MATCH] + mm; mi = CELL_MATCH; }
-                else { ms = lt[CELL_GAPINY] + mm; mi = CELL_GAPINY; }
-            } else {
-                if (lt[CELL_GAPINX] + mm >= lt[CELL_GAPINY] + mm) { ms = lt[CELL_GAPINX] + mm; mi = CELL_GAPINX; }
-                else { ms = lt[CELL_GAPINY] + mm; mi = CELL_GAPINY; }
-            }
-
-            if (mode != ALIGN_LOCAL) {            /* SA.rs:164-212 */
-                float po = (la - ii == 0) ? start_o : openal;
-                float pe = (la - ii == 0) ? start_e : epenal;
-                float qo = (lb - jj == 0) ? start_o : openal;
-                float qe = (lb - jj == 0) ? start_e : epenal;
-                if (t[CELL_MATCH] + po > t[CELL_GAPINX] + pe) {
-                    if (t[CELL_MATCH] + po >= t[CELL_GAPINY] + po) { gx = t[CELL_MATCH] + po; gxi = CELL_MATCH; }
-                    else { gx = t[CELL_GAPINY] + po; gxi = CELL_GAPINY; }
-                } else {
-                    if (t[CELL_GAPINX] + pe >= t[CELL_GAPINY] + po) { gx = t[CELL_GAPINX] + pe; gxi = CELL_GAPINX; }
-                    else { gx = t[CELL_GAPINY] + po; gxi = CELL_GAPINY; }
-                }
-                if (l[CELL_MATCH] + qo > l[CELL_GAPINY] + qe) {
-                    if (l[CELL_MATCH] + qo >= l[CELL_GAPINX] + qo) { gy = l[CELL_MATCH] + qo; gyi = CELL_MATCH; }
-                    else { gy = l[CELL_GAPINX] + qo; gyi = CELL_GAPINX; }
-                } else {
-                    if (l[CELL_GAPINY] + qe >= l[CELL_GAPINX] + qo) { gy = l[CELL_GAPINY] + qe; gyi = CELL_GAPINY; }
-                    else { gy = l[CELL_GAPINX] + qo; gyi = CELL_GAPINX; }
-                }
-            } else {                              /* SA.rs:213-253 */
-                if (t[CELL_MATCH] + openal >= t[CELL_GAPINX] + epenal) {
-                    if (t[CELL_MATCH] + openal > t[CELL_GAPINY] + openal) { gx = t[CELL_MATCH] + openal; gxi = CELL_MATCH; }
-                    else { gx = t[CELL_GAPINY] + openal; gxi = CELL_GAPINY; }
-                } else {
-                    if (t[CELL_GAPINX] + epenal > t[CELL_GAPINY] + openal) { gx = t[CELL_GAPINX] + epenal; gxi = CELL_GAPINX; }
-                    else { gx = t[CELL_GAPINY] + openal; gxi = CELL_GAPINY; }
-                }
-                if (l[CELL_MATCH] + openal >= l[CELL_GAPINY] + epenal) {
-                    if (l[CELL_MATCH] + openal > l[CELL_GAPINX] + openal) { gy = l[CELL_MATCH] + openal; gyi = CELL_MATCH; }
-                    else { gy = l[CELL_GAPINX] + openal; gyi = CELL_GAPINX; }
-                } else {
-                    if (l[CELL_GAPINY] + epenal > l[CELL_GAPINX] + openal) { gy = l[CELL_GAPINY] + epenal; gyi = CELL_GAPINY; }
-                    else { gy = l[CELL_GAPINX] + openal; gyi = CELL_GAPINX; }
-                }
-            }
-            if (mode == ALIGN_LOCAL) {            /* SA.rs:256-260 */
-                if (!(ms > 0.0f)) ms = 0.0f;      /* f32::max(0.0): values are never NaN here */
-                if (!(gx > 0.0f)) gx = 0.0f;
-                if (!(gy > 0.0f)) gy = 0.0f;
-            }
-            c[CELL_MATCH] = ms; c[CELL_GAPINX] = gx; c[CELL_GAPINY] = gy;   /* SA.rs:262-268 */
-            p[CELL_MATCH] = mi; p[CELL_GAPINX] = gxi; p[CELL_GAPINY] = gyi;
-        }
-    }
-}
+#define SWO_FILL_NAME swo_fill
+#define SWO_STORE swo_buf
+#define SWO_PV_T uint8_t
+#define SWO_SC(B, i, j) ((B)->sc + ((i) * W + (j)) * 3)
+#define SWO_PV(B, i, j) ((B)->pv + ((i) * W + (j)) * 3)
+#define SWO_SCORE(mat, n, pssm, ai, bj) ((pssm) ? (mat)[(size_t)(ai) + (size_t)(bj) * (n)] : (mat)[(size_t)(ai) * (n) + (size_t)(bj)])
+#include "sw_oracle_fill.inc"
+#undef SWO_FILL_NAME
+#undef SWO_STORE
+#undef SWO_PV_T
+#undef SWO_SC
+#undef SWO_PV
+#undef SWO_SCORE
 
 /*
  * backtrack, SA.rs:273-387.  Writes reversed-then-reversed (i.e. forward) index

@@ -109,3 +109,19 @@ def test_rust_display():
     assert O.rust_f32_display(54.5) == "54.5"
     assert O.rust_f32_display(-1770.5) == "-1770.5"
     assert O.rust_f32_display(0.0) == "0"
+
+
+def test_faithful_layout_equals_flat(emboss):
+    """oracle/sw_oracle_faithful.c (the reference's own data structure: one heap-owning cell per DP cell, an indirect
+    call per score lookup -- the `ref-faithful` CPU flavour of BASELINE.md section 3) shares the fill body with the flat
+    port and gives the same scores and end cells on the golden pairs, all modes."""
+    m = O.Matrix.blosum62()
+    sa = [m.seq_to_index(r["seq1"]) for r in emboss[:40]]
+    sb = [m.seq_to_index(r["seq2"]) for r in emboss[:40]]
+    a, oa = O.pack(sa)
+    b, ob = O.pack(sb)
+    for mode in (O.ALIGN_GLOBAL, O.ALIGN_GLOCAL, O.ALIGN_LOCAL):
+        flat = O.score_batch_f32(a, oa, b, ob, m.scores, 10.0, 0.5, mode, 4)
+        faith = O.score_batch_f32(a, oa, b, ob, m.scores, 10.0, 0.5, mode, 4, layout="faithful")
+        for x, y in zip(flat, faith):
+            assert np.array_equal(x, y)
