@@ -1,7 +1,7 @@
 #!/usr/bin/env python3
 """Small pass through every kernel of the library (K1, K2, KW with and without directions for both strip widths, the
 team-scheduled long-pair path, KT, the PSSM fill, the staged batch API) in a few seconds: the run to put under a
-profiler or a debugger (`python tools/exercise_kernels.py [k1 k2 kw team pssm staged]`).  No oracle here -- the parity
+profiler or a debugger (`python tools/exercise_kernels.py [k1 k2 kw team search k3 glocal pssm staged]`).  No oracle here -- the parity
 tests check the values.
 """
 import os
@@ -63,6 +63,30 @@ def main():
             r = eng.align_raw(a, b, False)
             print("team", mode, r["score"])
             eng.close()
+    if want("search"):                                             # resident database: K2 scan, device top-K, packed traceback of the hits (K3 + KT3)
+        eng = swb.SequenceAlignment(m, 10.0, 0.5, swb.ALIGN_LOCAL)
+        q = rand(rng, 1, 1100, 1100)[0]
+        seqs = rand(rng, 300, 1, 300) + [q[100:900], b"", q[:500] + rand(rng, 1, 1200, 1200)[0]]
+        ddb = S.DeviceDatabase(eng, S.Database.from_sequences(seqs))
+        hits = ddb.search(q, 10)
+        al = ddb.align(q, hits)
+        print("search", float(hits["score"].sum()), len(al), eng.stats()["k3_pairs"])
+        for w in range(2):                                         # two shards of the same database
+            sh = S.DeviceDatabase(eng, S.Database.from_sequences(seqs), w, 2)
+            print("shard", w, float(sh.search(q, 5)["score"].sum()))
+            sh.free()
+        ddb.free(); eng.close()
+    if want("k3"):                                                 # packed traceback path, global mode: several sweeps and checkpoints
+        eng = swb.SequenceAlignment(m, 10.0, 0.5, swb.ALIGN_GLOBAL)
+        a, b = rand(rng, 12, 1, 1300), rand(rng, 12, 1, 1300)
+        res = eng.align_list(a, b, True)
+        print("k3 global", sum(r["score"] for r in res), eng.stats()["k3_pairs"])
+        eng.close()
+    if want("glocal"):                                             # packed glocal score kernel (right-aligned b)
+        eng = swb.SequenceAlignment(m, 10.0, 0.5, swb.ALIGN_GLOCAL)
+        sc, _, _ = eng.score_batch(rand(rng, 500, 1, 200), rand(rng, 500, 1, 200))
+        print("glocal", float(sc.sum()))
+        eng.close()
     if want("pssm"):
         pm = swb.PositionSpecificMatrix()
         eng = swb.SequenceAlignment(pm, 10.0, 0.5, swb.ALIGN_GLOBAL)
