@@ -9,7 +9,7 @@
 //   * the result is the maximum of the three states at (la, lb) (SA.rs:296-309), i.e. H(la, lb); no running maximum.
 // The Gotoh form used here equals the reference's 3-state form in value when |open| >= |ext| (SURVEY.md 8a note 3);
 // global mode charges the same penalties on the last row and column as elsewhere (so = open, se = ext, SA.rs:166-170),
-// which is why only this mode (not glocal, whose last row / column are free) fits the uniform packed cell.
+// so the uniform packed cell applies as it is (glocal, whose last row / column are free, needs the GLOCAL form below).
 // The s16 range is guaranteed by the host's routing (batch.cu k1_take: |scores| bounded from the lengths), not by flags.
 // Cells beyond (la, lb) are computed on PAD residues; they may wrap, but nothing flows from them to a real cell.
 //
