@@ -477,7 +477,22 @@ static int align_batch_core(swb_engine *e, const char *a_all, const int64_t *off
     const float inv = 1.0f / (float)e->scale;
     const bool dyadic = (e->scale & (e->scale - 1)) == 0;
     auto to_f = [&](int64_t s) { return dyadic ? (float)s * inv : (float)((double)s / e->scale); };
+    // Local mode, pairs the score kernels take (both lengths <= 8192): scan first (K1, ~4 TCUPS).  The end cell bounds the
+    // part of the matrix the traceback can touch (the prefix box, see AlnJob) and the score proves the s16 range, so the
+    // pair can take the packed traceback path; pairs that score 0 need no device work at all.
+    std::vector<float> pre_sc; std::vector<int64_t> pre_ea, pre_eb;
+    double pre_ms = 0; int64_t pre_launches = 0;
+    bool prescan = outs && !pssm && !part_a && !part_b && e->mode == SWB_LOCAL && e->o <= e->e && n > 0 && !getenv("SWB_NO_K3");
+    for (int64_t k = 0; k < n && prescan; ++k)
+        if (off_a[k + 1] - off_a[k] > 8192 || off_b[k + 1] - off_b[k] > 8192) prescan = false;
+    if (prescan) {
+        pre_sc.resize(n); pre_ea.resize(n); pre_eb.resize(n);
+        const int rc = swb_score_batch(e, a_all, off_a, b_all, off_b, n, pre_sc.data(), pre_ea.data(), pre_eb.data());
+        if (rc != SWB_OK) return rc;
+        pre_ms = e->stats.kernel_ms; pre_launches = e->stats.launches;
+    }
     e->stats = swb_stats{}; e->stats.scale = e->scale; e->stats.exact_scale = e->exact_scale;
+    e->stats.kernel_ms = pre_ms; e->stats.launches = pre_launches;
 
     // encode on the host (small inputs on this path); unknown letters as SA.rs:669-679
     const int64_t na = n ? off_a[n] : 0, nb = n ? off_b[n] : 0;
@@ -495,9 +510,20 @@ static int align_batch_core(swb_engine *e, const char *a_all, const int64_t *off
         const int64_t lb = part_b ? std::min(std::max<int64_t>(part_b[k], 0), lb_full) : lb_full;
         if (!swb_range_ok(e, la, lb, pssm ? 8000 : -1)) { e->err = "scores of a pair this long do not fit the int32 lanes"; return SWB_ERR_RANGE; }
         e->stats.cells += (double)la * (double)lb;
+        if (la > 0 && lb > 0 && prescan && pre_ea[k] < 1) {          // local score 0: no alignment (SA.rs:346-348)
+            std::vector<int64_t> xa, xb; std::string ra, rb;
+            inflate(a_all + off_a[k], la_full, b_all + off_b[k], lb_full, nullptr, nullptr, 0, e->mode, retain_all, ra, rb);
+            int rc = fill_out(&outs[k], 0.0f, -1, -1, xa, xb, ra, rb);
+            if (rc != SWB_OK) { e->err = "out of memory"; return rc; }
+            continue;
+        }
         if (la > 0 && lb > 0) {
             AlnJob J; J.a_off = off_a[k]; J.b_off = off_b[k]; J.la = (int32_t)la; J.lb = (int32_t)lb;
             J.ra = a_all + off_a[k]; J.rb = b_all + off_b[k]; J.la_full = la_full; J.lb_full = lb_full; J.out = k;
+            if (prescan) {                                             // trace inside the prefix box that ends at the end cell
+                J.la = (int32_t)pre_ea[k]; J.lb = (int32_t)pre_eb[k];
+                J.known_score = (int32_t)std::llround((double)pre_sc[k] * e->scale);
+            }
             jobs.push_back(J);
             continue;
         }

@@ -510,6 +510,75 @@ __global__ void kt_kernel(const KWPair *__restrict__ pairs, const KWResult *__re
     else ncols[p] = n;
 }
 
+// KT, warp form (a few long pairs): the walk is a chain of dependent byte loads, ~0.2 us each from L2.  Here a warp
+// fetches the 32 x 32 block of direction bytes that ends at the cursor in one round trip (lane l loads row cx - l),
+// parks it in shared memory and walks inside it -- at least 32 columns of the alignment per round trip.  The walk itself
+// is the same code on every lane (uniform); lane 0 writes the lists.
+#define KTW_WARPS 4
+template <int MODE, int COLS>
+__global__ void __launch_bounds__(KTW_WARPS * 32)
+kt_warp_kernel(const KWPair *__restrict__ pairs, const KWResult *__restrict__ res, int n_pairs, const uint8_t *__restrict__ dir,
+               const int64_t *__restrict__ out_off, int32_t *__restrict__ idx_a, int32_t *__restrict__ idx_b,
+               int32_t *__restrict__ ncols, int sent)
+{
+    __shared__ uint8_t tile_all[KTW_WARPS][32][33];
+    const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
+    const int p = blockIdx.x * KTW_WARPS + wib;
+    if (p >= n_pairs) return;
+    uint8_t (*tile)[33] = tile_all[wib];
+    const KWPair P = pairs[p];
+    const KWResult R = res[p];
+    int32_t *xa = idx_a + out_off[p], *xb = idx_b + out_off[p];
+    int n = 0;
+    if (R.end_i < 0) { if (lane == 0) ncols[p] = 0; return; }      // SA.rs:346-348
+    int cx = R.end_i, cy = R.end_j, st = R.state;
+    int tx = -1, ty = -1;                                          // the block in shared memory ends at (tx, ty): rows tx-31..tx, columns ty-31..ty
+    for (;;) {
+        unsigned prev;
+        if (cx >= 1 && cy >= 1) {
+            if (tx < 0 || cx <= tx - 32 || cy <= ty - 32) {
+                tx = cx; ty = cy;
+                __syncwarp();
+                const int i = tx - lane;
+                if (i >= 1) {
+#pragma unroll 8
+                    for (int c = 0; c < 32; ++c) {
+                        const int j = ty - c;
+                        if (j >= 1) tile[lane][c] = dir[kt_addr<COLS>(P.dir_off, P.la, i, j)];
+                    }
+                }
+                __syncwarp();
+            }
+            prev = ((unsigned)tile[tx - cx][ty - cy] >> (2 * st)) & 3u;
+        }
+        else if (cx == 0 && cy == 0) prev = 0;                     // only reachable when la == lb == 0
+        else if (cx == 0) {                                        // row 0: prev = GAPINX for all states (SA.rs:105-107)
+            prev = 1;
+            if (MODE == SWB_LOCAL && (st == 1 || sent == 0)) prev = 3;
+        } else {                                                   // column 0: prev = GAPINY (SA.rs:114-116)
+            prev = 2;
+            if (MODE == SWB_LOCAL && (st == 2 || sent == 0)) prev = 3;
+        }
+        if (MODE == SWB_LOCAL && prev == 3) break;
+        if (st == 0) {
+            if (cx == 0 || cy == 0) { n = -2; break; }             // reference underflows / panics
+            if (lane == 0) { xa[n] = cx - 1; xb[n] = cy - 1; }
+            ++n; --cx; --cy;
+        } else if (st == 1) {
+            if (cy == 0) { n = -2; break; }
+            if (lane == 0) { xa[n] = -1; xb[n] = cy - 1; }
+            ++n; --cy;
+        } else {
+            if (cx == 0) { n = -2; break; }                        // SA.rs:369-371
+            if (lane == 0) { xa[n] = cx - 1; xb[n] = -1; }
+            ++n; --cx;
+        }
+        if (cx == 0 && cy == 0) break;
+        st = (int)prev;
+    }
+    if (lane == 0) ncols[p] = n;
+}
+
 cudaError_t kt_launch(const swb_engine *e, const KWPair *d_pairs, const KWResult *d_res, int n_pairs,
                       const uint8_t *d_dir, int cols, const int64_t *d_out_off, int32_t *d_idx_a, int32_t *d_idx_b,
                       int32_t *d_ncols, cudaStream_t st)
@@ -517,7 +586,11 @@ cudaError_t kt_launch(const swb_engine *e, const KWPair *d_pairs, const KWResult
     if (n_pairs <= 0) return cudaSuccess;
     const int threads = 32, blocks = (n_pairs + threads - 1) / threads;
     const int sent = 10 * e->o + 10 * e->e;
-#define KT_GO(M) do { if (cols == 2) kt_kernel<M, 2, false><<<blocks, threads, 0, st>>>(d_pairs, d_res, n_pairs, d_dir, d_out_off, d_idx_a, d_idx_b, d_ncols, sent, nullptr, nullptr, nullptr); \
+    const bool warp_form = n_pairs <= 2048 && !getenv("SWB_KT_THREAD");     // a few pairs: one warp each, block-cached walk
+    const int wblocks = (n_pairs + KTW_WARPS - 1) / KTW_WARPS;
+#define KT_GO(M) do { if (warp_form) { if (cols == 2) kt_warp_kernel<M, 2><<<wblocks, KTW_WARPS * 32, 0, st>>>(d_pairs, d_res, n_pairs, d_dir, d_out_off, d_idx_a, d_idx_b, d_ncols, sent); \
+                                       else kt_warp_kernel<M, 8><<<wblocks, KTW_WARPS * 32, 0, st>>>(d_pairs, d_res, n_pairs, d_dir, d_out_off, d_idx_a, d_idx_b, d_ncols, sent); } \
+                      else if (cols == 2) kt_kernel<M, 2, false><<<blocks, threads, 0, st>>>(d_pairs, d_res, n_pairs, d_dir, d_out_off, d_idx_a, d_idx_b, d_ncols, sent, nullptr, nullptr, nullptr); \
                       else kt_kernel<M, 8, false><<<blocks, threads, 0, st>>>(d_pairs, d_res, n_pairs, d_dir, d_out_off, d_idx_a, d_idx_b, d_ncols, sent, nullptr, nullptr, nullptr); } while (0)
     switch (e->mode) {
     case SWB_GLOBAL: KT_GO(SWB_GLOBAL); break;
@@ -553,16 +626,31 @@ template <int MODE, int COLS>
 __global__ void kt_band_kernel(const uint8_t *__restrict__ dir, int la_band, int row0, KTCursor *__restrict__ cur,
                                int32_t *__restrict__ xa, int32_t *__restrict__ xb, int sent)
 {
-    if (blockIdx.x != 0 || threadIdx.x != 0) return;
+    // one warp, block-cached like kt_warp_kernel: the 32 x 32 direction bytes that end at the cursor per round trip
+    __shared__ uint8_t tile[32][33];
+    if (blockIdx.x != 0 || threadIdx.x >= 32) return;
+    const int lane = threadIdx.x;
     KTCursor K = *cur;
     int cx = K.cx, cy = K.cy, st = K.st, n = K.n, status = 0;
+    int tx = -1, ty = -1;
     for (;;) {
         if (row0 > 0 && cx == row0) { status = 1; break; }         // the predecessor codes of this row belong to the band above
         unsigned prev;
         if (cx >= 1 && cy >= 1) {
-            if (cx - row0 > KT_AHEAD && cy > KT_AHEAD)
-                asm volatile("prefetch.global.L1 [%0];" ::"l"(dir + kt_addr<COLS>(0, la_band, cx - row0 - KT_AHEAD, cy - KT_AHEAD)));
-            prev = ((unsigned)dir[kt_addr<COLS>(0, la_band, cx - row0, cy)] >> (2 * st)) & 3u;
+            if (tx < 0 || cx <= tx - 32 || cy <= ty - 32) {
+                tx = cx; ty = cy;
+                __syncwarp();
+                const int i = tx - lane;
+                if (i > row0) {
+#pragma unroll 8
+                    for (int c = 0; c < 32; ++c) {
+                        const int j = ty - c;
+                        if (j >= 1) tile[lane][c] = dir[kt_addr<COLS>(0, la_band, i - row0, j)];
+                    }
+                }
+                __syncwarp();
+            }
+            prev = ((unsigned)tile[tx - cx][ty - cy] >> (2 * st)) & 3u;
         }
         else if (cx == 0 && cy == 0) prev = 0;
         else if (cx == 0) {                                        // row 0: prev = GAPINX for all states (SA.rs:105-107)
@@ -575,22 +663,21 @@ __global__ void kt_band_kernel(const uint8_t *__restrict__ dir, int la_band, int
         if (MODE == SWB_LOCAL && prev == 3) break;
         if (st == 0) {
             if (cx == 0 || cy == 0) { status = -2; break; }
-            xa[n] = cx - 1; xb[n] = cy - 1;
+            if (lane == 0) { xa[n] = cx - 1; xb[n] = cy - 1; }
             ++n; --cx; --cy;
         } else if (st == 1) {
             if (cy == 0) { status = -2; break; }
-            xa[n] = -1; xb[n] = cy - 1;
+            if (lane == 0) { xa[n] = -1; xb[n] = cy - 1; }
             ++n; --cy;
         } else {
             if (cx == 0) { status = -2; break; }
-            xa[n] = cx - 1; xb[n] = -1;
+            if (lane == 0) { xa[n] = cx - 1; xb[n] = -1; }
             ++n; --cx;
         }
         if (cx == 0 && cy == 0) break;
         st = (int)prev;
     }
-    K.cx = cx; K.cy = cy; K.st = st; K.n = n; K.status = status;
-    *cur = K;
+    if (lane == 0) { K.cx = cx; K.cy = cy; K.st = st; K.n = n; K.status = status; *cur = K; }
 }
 
 cudaError_t kt_band_launch(const swb_engine *e, const uint8_t *d_dir, int cols, int32_t la_band, int32_t row0,
