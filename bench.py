@@ -259,6 +259,7 @@ def main():
     ap.add_argument("--cpu-seconds", type=float, default=10.0)
     ap.add_argument("--no-extras", action="store_true", help="skip the side measurements of configs[3..4]")
     ap.add_argument("--no-search", action="store_true", help="skip the configs[2] search block")
+    ap.add_argument("--search-timeout", type=int, default=420, help="seconds the search block may take before the line is printed without it")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
@@ -358,22 +359,32 @@ def main():
     else:
         ms_step, e2e_ms, tot_cells = t[0].item(), t[1].item(), cells
         e2e_ranks = [round(e2e_ms, 2)]
-    # ---- configs[2] at every N (all ranks take part; strong scaling)
+    # ---- configs[2] at every N (all ranks take part; strong scaling).  Runs on a watchdog thread: whatever happens in
+    #      there (an exception on one rank would leave the others inside a collective), the headline line is printed.
     search = None
+    hung = False
     if not args.no_search:
-        try:
-            dpx_rate_s = swb.dpx_peak(0, local_rank)
-            peaks_s = {}
+        box = {}
+
+        def _run():
             try:
-                peaks_s = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
-            except Exception:
-                pass
-            search = search_block(swb, local_rank, rank, world, dpx_rate_s / 2.0 / 1e9, peaks_s.get("hbm_gbs", 6650.0))
-        except Exception as ex:                                   # never lose the bench line over it
-            if world > 1:
-                raise
-            search = {"error": repr(ex)}
+                torch.cuda.set_device(local_rank)
+                pk = {}
+                try:
+                    pk = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+                except Exception:
+                    pass
+                box["r"] = search_block(swb, local_rank, rank, world, swb.dpx_peak(0, local_rank) / 2.0 / 1e9, pk.get("hbm_gbs", 6650.0))
+            except Exception as ex:
+                box["r"] = {"error": repr(ex)}
+        th = threading.Thread(target=_run, daemon=True)
+        th.start()
+        th.join(args.search_timeout)
+        hung = th.is_alive()
+        search = {"error": "no result after %d s" % args.search_timeout} if hung else box.get("r")
     if rank != 0:
+        if hung:
+            os._exit(0)
         if world > 1:
             dist.destroy_process_group()
         return
@@ -445,7 +456,9 @@ def main():
             "gpu_launches": int(launches), "roofline": roofline, "cpu_baseline": cpu,
             "i32_reruns": int(reruns), "cells_per_step": tot_cells,
             "oracle_checked_pairs": int(len(pick)), "mismatches": mism, "other_configs": extras, "search": search}
-    print(json.dumps(line))
+    print(json.dumps(line), flush=True)
+    if hung:
+        os._exit(0)
     if world > 1:
         dist.destroy_process_group()
 
