@@ -741,6 +741,7 @@ def test_checkpointed_traceback_equals_direct(mode, cols, monkeypatch):
     Pairs include related DNA (long diagonal path through every band), unrelated sequences (local: short path; global:
     path along the edges), very unequal lengths and |open| < |extend|."""
     monkeypatch.setenv("SWB_KW_COLS", cols)
+    monkeypatch.setenv("SWB_NO_K3", "1")                           # this test is about the direction-byte path and its checkpointed form
     rng = np.random.default_rng(20250 + int(cols))
     m = swb.SubstitutionMatrix.get_mat_matrix(2.0, -3.0)
     for go, ge in ((5.0, 2.0), (2.0, 3.0)):
