@@ -226,6 +226,7 @@ static int align_jobs_k3(swb_engine *e, const uint8_t *d_a, const uint8_t *d_b, 
     while (pos < sel.size()) {
         std::vector<K3Pair> hp;
         int64_t colb = 0, rowb = 0, out_total = 0;
+        int max_sweeps = 1;
         size_t end = pos;
         while (end < sel.size()) {
             const AlnJob &J = jobs[sel[end]];
@@ -235,6 +236,7 @@ static int align_jobs_k3(swb_engine *e, const uint8_t *d_a, const uint8_t *d_b, 
             K3Pair P; P.a_off = J.a_off; P.b_off = J.b_off; P.la = J.la; P.lb = J.lb; P.colb_off = colb; P.rowb_off = rowb; P.out_off = out_total;
             P.start_state = 0; P.score = J.known_score == INT32_MIN ? 0 : J.known_score;
             hp.push_back(P);
+            max_sweeps = std::max(max_sweeps, (J.lb + 1023) / 1024);
             colb += c4; rowb += rw; out_total += (int64_t)J.la + J.lb + 1;
             ++end;
         }
@@ -248,7 +250,7 @@ static int align_jobs_k3(swb_engine *e, const uint8_t *d_a, const uint8_t *d_b, 
         CUDA_TRY(e, cudaMemcpyAsync(d_pairs.p, hp.data(), np * sizeof(K3Pair), cudaMemcpyHostToDevice, e->stream));
         CUDA_TRY(e, cudaEventRecord(e->ev0, e->stream));
         CUDA_TRY(e, k3_launch(e, d_a, d_b, d_pairs.as<K3Pair>(), np, d_colb.as<uint4>(), d_rowb.as<unsigned>(), d_cnt.as<int>(),
-                              d_xa.as<int32_t>(), d_xb.as<int32_t>(), d_nc.as<int32_t>(), d_res.as<KWResult>(), e->stream));
+                              d_xa.as<int32_t>(), d_xb.as<int32_t>(), d_nc.as<int32_t>(), d_res.as<KWResult>(), e->stream, max_sweeps));
         CUDA_TRY(e, cudaEventRecord(e->ev1, e->stream));
         const size_t tb_need = (size_t)np * (sizeof(KWResult) + sizeof(int32_t)) + 2 * (size_t)out_total * sizeof(int32_t) + 64;
         if (tb_need > e->tb_bytes) {

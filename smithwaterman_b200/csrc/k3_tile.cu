@@ -50,20 +50,35 @@ struct K3Cell {
     }
 
 // ---- K3: fill ---------------------------------------------------------------------------------------------------------
-// One warp = one pair; lane l of sweep sw owns the 32-column pass q = 32 sw + l and runs l row blocks (of 4 rows) behind
-// lane 0, so the last column of a pass reaches the next lane by shuffles (as in K2); the last lane's column reaches
-// lane 0 of the next sweep through the pair's own border store, which the walker reads anyway.
+// A TEAM of `team` warps of one block = one pair; warp w takes the sweeps w, w + team, ... (a sweep = 32 passes = 1024
+// columns); lane l of a sweep owns the 32-column pass q = 32 sw + l and runs l row blocks (of 4 rows) behind lane 0, so the
+// last column of a pass reaches the next lane by shuffles (as in K2); the last lane's column reaches lane 0 of the next
+// sweep -- another warp of the team, about 33 row blocks behind -- through the pair's own border store, which the walker
+// reads anyway, guarded by a progress word in shared memory (published row blocks, monotone over the sweeps).  The warps
+// of a team sit in one block, so they are resident together by construction: no inter-block waiting anywhere.
+// (A lone warp runs this cell at an IPC of ~0.25 -- 119 registers leave no room to software-pipeline the table loads --
+// so a pair needs several warps as soon as there are fewer pairs than warp slots.)
+__device__ __forceinline__ void k3_team_bar(int slot, int team)
+{
+    if (team == 1) __syncwarp();
+    else asm volatile("bar.sync %0, %1;" ::"r"(slot + 1), "r"(team * 32) : "memory");
+}
+
 template <int MODE>
 __global__ void __launch_bounds__(K3_WARPS * 32, 1)
 k3_fill_kernel(const uint8_t *__restrict__ a_all, const uint8_t *__restrict__ b_all, const K3Pair *__restrict__ pairs, int n_pairs,
-               const int32_t *__restrict__ mat, int nl, int open, int ext, uint4 *colb, unsigned *rowb, int *counter)
+               const int32_t *__restrict__ mat, int nl, int open, int ext, uint4 *colb, unsigned *rowb, int *counter, int team)
 {
     extern __shared__ __align__(16) unsigned T_sh[];               // [nl*nl][32 lanes]: (s - open) & 0xFFFF
+    __shared__ volatile int prog_sh[K3_WARPS];                     // per warp: sweep * (nblk + 2) + row blocks of its last pass published
+    __shared__ int pair_sh[K3_WARPS];
     for (int idx = threadIdx.x; idx < nl * nl * 32; idx += blockDim.x)
         T_sh[idx] = (unsigned)(mat[idx >> 5] - open) & 0xFFFFu;
     __syncthreads();
 
-    const int lane = threadIdx.x & 31;
+    const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
+    const int slot = wib / team, w = wib - slot * team;             // team slot of the block, warp within the team
+    const int pw = slot * team + (w + team - 1) % team;             // the warp that owns the sweep before this warp's
     const unsigned tbase = (unsigned)__cvta_generic_to_shared(T_sh) + lane * 4;
     const unsigned rowstride = (unsigned)nl * 128u;
     const unsigned open2 = pack2(open, open), ext2 = pack2(ext, ext);
@@ -73,9 +88,11 @@ k3_fill_kernel(const uint8_t *__restrict__ a_all, const uint8_t *__restrict__ b_
     auto ho_bnd = [=](int j) { return (MODE == SWB_LOCAL || j == 0) ? open : 2 * open + (j - 1) * ext; };
 
     for (;;) {
-        int g = 0;
-        if (lane == 0) g = atomicAdd(counter, 1);
-        g = __shfl_sync(0xffffffffu, g, 0);
+        k3_team_bar(slot, team);                                   // every warp of the team is done with the previous pair
+        if (lane == 0) prog_sh[wib] = -1;
+        if (w == 0 && lane == 0) pair_sh[slot] = atomicAdd(counter, 1);
+        k3_team_bar(slot, team);
+        const int g = pair_sh[slot];
         if (g >= n_pairs) break;
         const K3Pair P = pairs[g];
         const uint8_t *a = a_all + P.a_off, *b = b_all + P.b_off;
@@ -87,7 +104,8 @@ k3_fill_kernel(const uint8_t *__restrict__ a_all, const uint8_t *__restrict__ b_
         uint4 *cb = colb + P.colb_off;                               // [pass][nblk + 1][2]
         unsigned *rb = rowb + P.rowb_off;                            // [m - 1][pass][80]
 
-        for (int sw = 0; sw < sweeps; ++sw) {
+        const int pbase = nblk + 2;
+        for (int sw = w; sw < sweeps; sw += team) {
             const int q = sw * 32 + lane;
             const bool has_pass = q < n_pass;
             const int jbase = q * K1_STRIP;
@@ -112,7 +130,15 @@ k3_fill_kernel(const uint8_t *__restrict__ a_all, const uint8_t *__restrict__ b_
             unsigned c1 = open2, c2 = open2, c3 = open2;              // this lane's (Ho, E) words of rows 1..3 of its previous block
             const uint4 *gin = cb + ((size_t)(q > 0 ? q - 1 : 0) * (nblk + 1)) * 2;
             uint4 g_cur = make_uint4(open2, open2, open2, open2), g_next = g_cur;
-            if (from_g) { g_cur = gin[0]; g_next = gin[2]; }
+            // lane 0 of a later sweep: wait until the row blocks it is about to read have been published by the sweep before
+            auto wait_pub = [&](int need) {
+                if (team > 1) {
+                    const int tgt = (sw - 1) * pbase + min(need, nblk);
+                    while (prog_sh[pw] < tgt) __nanosleep(20);
+                    __threadfence_block();
+                }
+            };
+            if (from_g) { wait_pub(2); g_cur = __ldcg(gin); g_next = __ldcg(gin + 2); }
             uint4 *gout = cb + ((size_t)q * (nblk + 1)) * 2;
 
 #pragma unroll 1
@@ -188,7 +214,8 @@ k3_fill_kernel(const uint8_t *__restrict__ a_all, const uint8_t *__restrict__ b_
                     gout[(size_t)bl * 2] = make_uint4(wout[0], wout[1], wout[2], wout[3]);         // rows i0 .. i0+3 of column 32q+32
                     gout[(size_t)bl * 2 + 1] = make_uint4(mf[0], mf[1], mf[2], mf[3]);
                     c1 = wout[1]; c2 = wout[2]; c3 = wout[3];
-                    if (from_g) { g_cur = g_next; if (bl + 2 <= nblk) g_next = gin[(size_t)(bl + 2) * 2]; }
+                    if (from_g) { g_cur = g_next; if (bl + 2 < nblk) { wait_pub(bl + 3); g_next = __ldcg(gin + (size_t)(bl + 2) * 2); } }
+                    if (team > 1 && lane == lanes_here - 1) { __threadfence_block(); prog_sh[wib] = sw * pbase + bl + 1; }
                 }
             }
             __syncwarp();                                             // the last lane's column is read by lane 0 in the next sweep
@@ -399,24 +426,34 @@ void k3_sizes(int32_t la, int32_t lb, int64_t *colb_uint4, int64_t *rowb_words)
 
 cudaError_t k3_launch(const swb_engine *e, const uint8_t *d_a, const uint8_t *d_b, const K3Pair *d_pairs, int n_pairs,
                       uint4 *d_colb, unsigned *d_rowb, int *d_counter, int32_t *d_idx_a, int32_t *d_idx_b, int32_t *d_ncols,
-                      KWResult *d_res, cudaStream_t st)
+                      KWResult *d_res, cudaStream_t st, int max_sweeps)
 {
     if (n_pairs <= 0) return cudaSuccess;
     const int nl = e->n + 1;
     const size_t smem = (size_t)nl * nl * 32 * sizeof(unsigned);
     cudaError_t err = cudaMemsetAsync(d_counter, 0, sizeof(int), st);
     if (err != cudaSuccess) return err;
-    const int fill_blocks = std::min(e->sm_count, (n_pairs + K3_WARPS - 1) / K3_WARPS);
+    // team size: a divisor of the block's warps, enough to fill the warp slots of the GPU when pairs are few, no more
+    // than the sweeps of the widest pair (`max_sweeps`, from the caller)
+    int team = 1;
+    {
+        const int want = (e->sm_count * K3_WARPS + n_pairs - 1) / n_pairs;
+        const int divs[] = {1, 2, 3, 4, 6, 12};
+        for (int d : divs) if (d <= std::max(1, max_sweeps) && (team < want)) team = d;
+        if (const char *f = getenv("SWB_K3_TEAM")) { const int v = atoi(f); for (int d : divs) if (d == v) team = v; }
+    }
+    const int slots = K3_WARPS / team;
+    const int fill_blocks = std::min(e->sm_count, (n_pairs + slots - 1) / slots);
     const int walk_blocks = (n_pairs + KT3_WARPS - 1) / KT3_WARPS;
     const size_t wsmem = (size_t)nl * nl * sizeof(int);
     if (e->mode == SWB_LOCAL) {
         if ((err = cudaFuncSetAttribute(k3_fill_kernel<SWB_LOCAL>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)) != cudaSuccess) return err;
-        k3_fill_kernel<SWB_LOCAL><<<fill_blocks, K3_WARPS * 32, smem, st>>>(d_a, d_b, d_pairs, n_pairs, e->d_mat, nl, e->o, e->e, d_colb, d_rowb, d_counter);
+        k3_fill_kernel<SWB_LOCAL><<<fill_blocks, K3_WARPS * 32, smem, st>>>(d_a, d_b, d_pairs, n_pairs, e->d_mat, nl, e->o, e->e, d_colb, d_rowb, d_counter, team);
         kt3_walk_kernel<SWB_LOCAL><<<walk_blocks, KT3_WARPS * 32, wsmem, st>>>(d_a, d_b, d_pairs, n_pairs, e->d_mat, nl, e->o, e->e, d_colb, d_rowb,
                                                                               d_idx_a, d_idx_b, d_ncols, d_res);
     } else {
         if ((err = cudaFuncSetAttribute(k3_fill_kernel<SWB_GLOBAL>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)) != cudaSuccess) return err;
-        k3_fill_kernel<SWB_GLOBAL><<<fill_blocks, K3_WARPS * 32, smem, st>>>(d_a, d_b, d_pairs, n_pairs, e->d_mat, nl, e->o, e->e, d_colb, d_rowb, d_counter);
+        k3_fill_kernel<SWB_GLOBAL><<<fill_blocks, K3_WARPS * 32, smem, st>>>(d_a, d_b, d_pairs, n_pairs, e->d_mat, nl, e->o, e->e, d_colb, d_rowb, d_counter, team);
         kt3_walk_kernel<SWB_GLOBAL><<<walk_blocks, KT3_WARPS * 32, wsmem, st>>>(d_a, d_b, d_pairs, n_pairs, e->d_mat, nl, e->o, e->e, d_colb, d_rowb,
                                                                                d_idx_a, d_idx_b, d_ncols, d_res);
     }

@@ -540,13 +540,14 @@ kt_warp_kernel(const KWPair *__restrict__ pairs, const KWResult *__restrict__ re
                 tx = cx; ty = cy;
                 __syncwarp();
                 const int i = tx - lane;
-                if (i >= 1) {
-#pragma unroll 8
-                    for (int c = 0; c < 32; ++c) {
-                        const int j = ty - c;
-                        if (j >= 1) tile[lane][c] = dir[kt_addr<COLS>(P.dir_off, P.la, i, j)];
-                    }
+                uint8_t v[32];                                     // all 32 loads in flight before the first use: one round trip
+#pragma unroll
+                for (int c = 0; c < 32; ++c) {
+                    const int j = ty - c;
+                    v[c] = (i >= 1 && j >= 1) ? dir[kt_addr<COLS>(P.dir_off, P.la, i, j)] : (uint8_t)0;
                 }
+#pragma unroll
+                for (int c = 0; c < 32; ++c) tile[lane][c] = v[c];
                 __syncwarp();
             }
             prev = ((unsigned)tile[tx - cx][ty - cy] >> (2 * st)) & 3u;
@@ -641,13 +642,14 @@ __global__ void kt_band_kernel(const uint8_t *__restrict__ dir, int la_band, int
                 tx = cx; ty = cy;
                 __syncwarp();
                 const int i = tx - lane;
-                if (i > row0) {
-#pragma unroll 8
-                    for (int c = 0; c < 32; ++c) {
-                        const int j = ty - c;
-                        if (j >= 1) tile[lane][c] = dir[kt_addr<COLS>(0, la_band, i - row0, j)];
-                    }
+                uint8_t v[32];
+#pragma unroll
+                for (int c = 0; c < 32; ++c) {
+                    const int j = ty - c;
+                    v[c] = (i > row0 && j >= 1) ? dir[kt_addr<COLS>(0, la_band, i - row0, j)] : (uint8_t)0;
                 }
+#pragma unroll
+                for (int c = 0; c < 32; ++c) tile[lane][c] = v[c];
                 __syncwarp();
             }
             prev = ((unsigned)tile[tx - cx][ty - cy] >> (2 * st)) & 3u;

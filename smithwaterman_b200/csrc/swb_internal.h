@@ -236,7 +236,7 @@ bool k3_eligible(const swb_engine *e, int64_t la, int64_t lb);       // mode, |o
 void k3_sizes(int32_t la, int32_t lb, int64_t *colb_uint4, int64_t *rowb_words);
 cudaError_t k3_launch(const swb_engine *e, const uint8_t *d_a, const uint8_t *d_b, const K3Pair *d_pairs, int n_pairs,
                       uint4 *d_colb, unsigned *d_rowb, int *d_counter, int32_t *d_idx_a, int32_t *d_idx_b, int32_t *d_ncols,
-                      KWResult *d_res, cudaStream_t st);
+                      KWResult *d_res, cudaStream_t st, int max_sweeps = 1);
 
 // K0
 cudaError_t k0_run(int which, int sm_count, double *thread_instr_per_s);
