@@ -138,8 +138,23 @@ k3_fill_kernel(const uint8_t *__restrict__ a_all, const uint8_t *__restrict__ b_
                     __threadfence_block();
                 }
             };
-            if (from_g) { wait_pub(2); g_cur = __ldcg(gin); g_next = __ldcg(gin + 2); }
+            // (the wait is executed by the WHOLE warp -- its condition is warp-uniform -- and only the two loads are lane 0's:
+            //  a spin inside lane-0-only control flow left the warp split into {lane 0} and {lanes 1..31} for the whole
+            //  sweep, each half issuing every instruction of the loop: measured, 2 x the warp instructions)
+            if (sw > 0) {
+                wait_pub(2);
+                if (lane == 0) { g_cur = __ldcg(gin); g_next = __ldcg(gin + 2); }
+            }
             uint4 *gout = cb + ((size_t)q * (nblk + 1)) * 2;
+            auto load_rows = [&](int blk) -> unsigned {                 // residues of rows 4 blk + 1 .. 4 blk + 4, PAD beyond la
+                unsigned wd = 0;
+                if (has_pass && blk >= 0 && blk < nblk) {
+#pragma unroll
+                    for (int t = 0; t < 4; ++t) wd |= ((4 * blk + t < la) ? (unsigned)a[4 * blk + t] : pad) << (8 * t);
+                }
+                return wd;
+            };
+            unsigned word_next = load_rows(-lane);
 
 #pragma unroll 1
             for (int gbk = 0; gbk < n_gb; ++gbk) {
@@ -158,11 +173,8 @@ k3_fill_kernel(const uint8_t *__restrict__ a_all, const uint8_t *__restrict__ b_
                     }
                 } else if (from_g) { bq[0] = g_cur.y; bq[1] = g_cur.z; bq[2] = g_cur.w; bq[3] = g_next.x; }
                 else { bq[0] = s1; bq[1] = s2_; bq[2] = s3; bq[3] = open2; }
-                unsigned word = 0;
-                if (active) {
-#pragma unroll
-                    for (int t = 0; t < 4; ++t) word |= ((i0 + t < la) ? (unsigned)a[i0 + t] : pad) << (8 * t);
-                }
+                const unsigned word = word_next;                       // fetched one block ahead: no load latency on the block's critical path
+                word_next = load_rows(bl + 1);
                 const bool snap = active && ((bl + 1) % (K3_R / 4) == 0) && ((bl + 1) / (K3_R / 4) <= n_ck);
                 unsigned *rdst = rb + ((size_t)(snap ? (bl + 1) / (K3_R / 4) - 1 : 0) * n_pass + q) * K3_ROWB_WORDS;
                 unsigned wout[4] = {open2, open2, open2, open2}, mf[4] = {0u, 0u, 0u, 0u};
@@ -214,8 +226,12 @@ k3_fill_kernel(const uint8_t *__restrict__ a_all, const uint8_t *__restrict__ b_
                     gout[(size_t)bl * 2] = make_uint4(wout[0], wout[1], wout[2], wout[3]);         // rows i0 .. i0+3 of column 32q+32
                     gout[(size_t)bl * 2 + 1] = make_uint4(mf[0], mf[1], mf[2], mf[3]);
                     c1 = wout[1]; c2 = wout[2]; c3 = wout[3];
-                    if (from_g) { g_cur = g_next; if (bl + 2 < nblk) { wait_pub(bl + 3); g_next = __ldcg(gin + (size_t)(bl + 2) * 2); } }
                     if (team > 1 && lane == lanes_here - 1) { __threadfence_block(); prog_sh[wib] = sw * pbase + bl + 1; }
+                }
+                if (sw > 0 && gbk < nblk) {                             // lane 0 has finished its block gbk: its next two border entries
+                    const bool more = gbk + 2 < nblk;
+                    if (more) wait_pub(gbk + 3);
+                    if (lane == 0) { g_cur = g_next; if (more) g_next = __ldcg(gin + (size_t)(gbk + 2) * 2); }
                 }
             }
             __syncwarp();                                             // the last lane's column is read by lane 0 in the next sweep
@@ -230,6 +246,7 @@ struct KT3Smem {
     uint8_t dir[K3_R][32];          // predecessor codes of the recomputed part of the tile
     int4 left[K3_R + 2];            // (M, X, Y, raw E) of column c0, rows rtop .. cx; local mode: M, X, Y clamped as the reference's states
     int hm1[33], h0[33];            // H(rtop - 1, c0 + k), H(rtop, c0 + k), k = 0 .. 32
+    int arow[K3_R + 2];             // score-table row offset of the residue of row rtop + r (no global load inside the wavefront)
 };
 
 // (M, X, Y, raw E, H) of a stored border cell (row, column 32 q + 32) -- or of a matrix boundary cell.
@@ -298,6 +315,7 @@ kt3_walk_kernel(const uint8_t *__restrict__ a_all, const uint8_t *__restrict__ b
                 kt3_border_cell<MODE>(cb, nblk, q - 1, rtop + r, c0, open, o, e, M, X, Y, Er, H);
                 S.left[r] = make_int4(M, X, Y, Er);
                 if (r == 0) S.h0[0] = H;
+                S.arow[r] = (rtop + r >= 1) ? (int)a[rtop + r - 1] * nl : 0;
             }
             if (lane == 0) {
                 int M, X, Y, Er, H = 0;
@@ -336,13 +354,15 @@ kt3_walk_kernel(const uint8_t *__restrict__ a_all, const uint8_t *__restrict__ b
             int lastM = 0, lastX = 0, lastY = 0;
             const int bcode = (j <= lb) ? (int)b[j - 1] : 0;
             const int n_steps = nrows + ncols - 1;
+            auto score_of = [&](int r) { return (lane < ncols && r >= 1 && r <= nrows) ? mat_sh[S.arow[r] + bcode] : 0; };
+            int s_nxt = score_of(1 - lane);
             for (int t = 0; t < n_steps; ++t) {
                 const int r = t - lane + 1;                          // row of this lane in this step, 1 .. nrows
                 int tM = __shfl_up_sync(0xffffffffu, lastM, 1), tX = __shfl_up_sync(0xffffffffu, lastX, 1), tY = __shfl_up_sync(0xffffffffu, lastY, 1);
+                const int s = s_nxt;
+                s_nxt = score_of(r + 1);                             // the next step's score: two shared-memory loads off the critical path
                 if (lane < ncols && r >= 1 && r <= nrows) {
                     if (lane == 0) { const int4 v = S.left[r]; tM = v.x; tX = v.y; tY = v.z; }
-                    const int i = rtop + r;
-                    const int s = mat_sh[(int)a[i - 1] * nl + bcode];
                     const int hd = hd0; const unsigned ad = ad0;
                     hd0 = __vimax3_s32(tM, tX, tY); ad0 = kw_am(tM, tX, tY);
                     int mm, xx, yy; unsigned code;
