@@ -161,6 +161,29 @@ int swb_cluster(swb_engine *e, const char *seq_all, const int64_t *off, int64_t 
 int swb_score_batch(swb_engine *e, const char *a_all, const int64_t *off_a, const char *b_all,
                     const int64_t *off_b, int64_t n, float *scores, int64_t *end_a, int64_t *end_b);
 
+/* Score + end cell of n pairs WITHOUT any device allocation: DEVICE buffers in and out, the kernel's scratch in a
+ * file-scope __device__ array of the library (csrc/static_scratch.cu).
+ * NO COUNTERPART IN THE REFERENCE: added for callers that cannot call cudaMalloc
+ * (CUDA graph capture, tight serving loops, harnesses that forbid it).  Results are those of swb_score_batch.
+ *   d_a_all / d_b_all    letters on the device, total_a / total_b bytes;   d_off_a / d_off_b: n + 1 offsets, on the device
+ *   d_scores[n], d_end_a[n], d_end_b[n] (the end arrays may be NULL), d_status[1] (may be NULL): on the device
+ *   stream               a cudaStream_t (NULL = the default stream); the work is enqueued there and the call returns
+ *                        without synchronising; *d_status = 0, SWB_ERR_LETTER (unknown letter, no X) or SWB_ERR_ARG (an
+ *                        offset out of order / out of range or a sequence longer than SWB_STATIC_MAX_LEN: such a pair is
+ *                        scored as two empty sequences).
+ * Limits (SWB_ERR_ARG beyond them, nothing is enqueued): n <= SWB_STATIC_MAX_PAIRS, every sequence <=
+ * SWB_STATIC_MAX_LEN letters, total_a (rounded up to 256) + total_b <= SWB_STATIC_MAX_RESIDUES.
+ * Every GPU that loads the library holds SWB_STATIC_SCRATCH_BYTES until exit.  All calls share that array: calls that
+ * overlap on the GPU (different streams without a dependency) race; calls on one stream are safe.  The first call on a
+ * device resolves the array's address (cudaGetSymbolAddress); no call allocates or frees device memory. */
+#define SWB_STATIC_MAX_PAIRS 4096
+#define SWB_STATIC_MAX_LEN 1024
+#define SWB_STATIC_MAX_RESIDUES 1048576
+#define SWB_STATIC_SCRATCH_BYTES 9945600
+int swb_score_batch_static(swb_engine *e, const char *d_a_all, const int64_t *d_off_a, int64_t total_a,
+                           const char *d_b_all, const int64_t *d_off_b, int64_t total_b, int64_t n, float *d_scores,
+                           int64_t *d_end_a, int64_t *d_end_b, int32_t *d_status, void *stream);
+
 /* Database search, scoring stage: one query (the `a` sequence) against n database sequences (`b`); results as
  * swb_score_batch.  The caller selects its top-K from `scores` (ties: lower index first keeps multi-GPU runs
  * deterministic) and obtains the alignments of those hits with swb_align_batch. */

@@ -1,7 +1,7 @@
 //! Declarations of every entry point of `include/swb200.h` (same order as the header).
 //! Not compiled in this repository's build image (no Rust toolchain); a test keeps the symbol list equal to the header's.
 #![allow(non_camel_case_types)]
-use std::os::raw::{c_char, c_int, c_uint};
+use std::os::raw::{c_char, c_int, c_uint, c_void};
 
 pub const SWB_GLOBAL: c_int = 0; // alignment_type, SA.rs:11-13
 pub const SWB_GLOCAL: c_int = 1;
@@ -17,6 +17,9 @@ pub const SWB_ERR_NOMEM: c_int = 6;
 pub const SWB_ERR_RANGE: c_int = 7;
 pub const SWB_RETAIN_ALL: c_uint = 1;
 pub const SWB_MAX_TOPK: c_int = 4096;
+pub const SWB_STATIC_MAX_PAIRS: i64 = 4096;
+pub const SWB_STATIC_MAX_LEN: i64 = 1024;
+pub const SWB_STATIC_MAX_RESIDUES: i64 = 1048576;
 
 pub enum swb_engine {}
 pub enum swb_batch {}
@@ -96,6 +99,9 @@ extern "C" {
     pub fn swb_align_stats_batch(e: *mut swb_engine, a_all: *const c_char, off_a: *const i64, b_all: *const c_char, off_b: *const i64, n: i64, flags: c_uint, outs: *mut swb_aln_stats) -> c_int;
     pub fn swb_cluster(e: *mut swb_engine, seq_all: *const c_char, off: *const i64, n: i64, identity: f64, coverage_short: f64, coverage_long: f64, order: *mut i64, cluster_of: *mut i64, identical: *mut i64, n_alignments: *mut i64) -> c_int;
     pub fn swb_score_batch(e: *mut swb_engine, a_all: *const c_char, off_a: *const i64, b_all: *const c_char, off_b: *const i64, n: i64, scores: *mut f32, end_a: *mut i64, end_b: *mut i64) -> c_int;
+    /// No counterpart in the reference: swb_score_batch on DEVICE buffers with
+    /// the kernel's scratch in a static __device__ array; allocates nothing.  Limits: SWB_STATIC_MAX_PAIRS / _LEN / _RESIDUES.
+    pub fn swb_score_batch_static(e: *mut swb_engine, d_a_all: *const c_char, d_off_a: *const i64, total_a: i64, d_b_all: *const c_char, d_off_b: *const i64, total_b: i64, n: i64, d_scores: *mut f32, d_end_a: *mut i64, d_end_b: *mut i64, d_status: *mut i32, stream: *mut c_void) -> c_int;
     pub fn swb_search_scores(e: *mut swb_engine, query: *const c_char, lq: i64, db_all: *const c_char, off_db: *const i64, n: i64, scores: *mut f32, end_q: *mut i64, end_t: *mut i64) -> c_int;
     pub fn swb_db_shard(off: *const i64, n: i64, rank: c_int, world: c_int, idx: *mut i64, n_idx: *mut i64) -> c_int;
     pub fn swb_db_upload(e: *mut swb_engine, letters: *const c_char, off: *const i64, n: i64, global_index: *const i64, out: *mut *mut swb_db) -> c_int;

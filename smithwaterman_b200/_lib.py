@@ -116,6 +116,7 @@ def lib():
         "swb_cluster": (c.c_int, [vp, vp, vp, i64, c.c_double, c.c_double, c.c_double, vp, vp, vp, vp]),
         "swb_score_batch": (c.c_int, [vp, vp, vp, vp, vp, i64, vp, vp, vp]),
         "swb_search_scores": (c.c_int, [vp, vp, i64, vp, vp, i64, vp, vp, vp]),
+        "swb_score_batch_static": (c.c_int, [vp, vp, vp, i64, vp, vp, i64, i64, vp, vp, vp, vp, vp]),
         "swb_batch_upload": (c.c_int, [vp, vp, vp, vp, vp, i64, c.POINTER(vp)]),
         "swb_batch_run": (c.c_int, [vp, vp]),
         "swb_batch_fetch": (c.c_int, [vp, vp, vp, vp, vp]),
