@@ -1,7 +1,7 @@
 #!/usr/bin/env python3
 """Small pass through every kernel of the library (K1, K2, KW with and without directions for both strip widths, the
 team-scheduled long-pair path, KT, the PSSM fill, the staged batch API) in a few seconds: the run to put under a
-profiler or a debugger (`python tools/exercise_kernels.py [k1 k2 kw team search k3 glocal pssm staged]`).  No oracle here -- the parity
+profiler or a debugger (`python tools/exercise_kernels.py [k1 k2 kw team search k3 glocal pssm staged static]`).  No oracle here -- the parity
 tests check the values.
 """
 import os
@@ -106,6 +106,22 @@ def main():
         sc = bt.fetch()[0]
         print("staged", float(np.asarray(sc).sum()))
         bt.free()
+        eng.close()
+    if want("static"):                                             # allocation-free scorer: scratch in a static __device__ array
+        import ctypes
+        import torch
+        eng = swb.SequenceAlignment(m, 10.0, 0.5, swb.ALIGN_LOCAL)
+        a, b = rand(rng, 300, 0, 600), rand(rng, 300, 0, 600)
+        pa, oa = pack_sequences(a)
+        pb, ob = pack_sequences(b)
+        ta, tb = torch.from_numpy(pa).cuda(), torch.from_numpy(pb).cuda()
+        toa, tob = torch.from_numpy(oa).cuda(), torch.from_numpy(ob).cuda()
+        tsc = torch.zeros(300, dtype=torch.float32, device="cuda"); tst = torch.zeros(1, dtype=torch.int32, device="cuda")
+        for _ in range(2):
+            eng._check(eng.L.swb_score_batch_static(eng._h, ta.data_ptr(), toa.data_ptr(), len(pa), tb.data_ptr(), tob.data_ptr(), len(pb),
+                                                    300, tsc.data_ptr(), None, None, tst.data_ptr(), ctypes.c_void_p(0)))
+        torch.cuda.synchronize()
+        print("static", float(tsc.sum().item()), int(tst.item()))
         eng.close()
     print("exercise_kernels: done")
 
