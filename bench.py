@@ -133,12 +133,14 @@ def search_block(swb, local_rank, rank, world, roof_gcups, hbm_peak, steps=3):
             dist.barrier()
         torch.cuda.synchronize()
 
+    stage = {}
+
     def one(tb):
-        return S.search(eng, q, db, topk=100, traceback=tb, rank=rank, world_size=world, device=dev, ddb=ddb)
+        return S.search(eng, q, db, topk=100, traceback=tb, rank=rank, world_size=world, device=dev, ddb=ddb, timings=stage)
 
     hits = one(True)                                          # warm-up: scratch growth, NCCL channels
     one(False)
-    t_score, t_full, dev_ms, tb_ms = [], [], [], []
+    t_score, t_full, dev_ms, tb_ms, stages = [], [], [], [], []
     for _ in range(steps):
         barrier(); a0 = time.perf_counter()
         ddb.search(q, 100)
@@ -148,6 +150,7 @@ def search_block(swb, local_rank, rank, world, roof_gcups, hbm_peak, steps=3):
         barrier(); a2 = time.perf_counter()
         hits = one(True)
         tb_ms.append(eng.stats()["kernel_ms"])
+        stages.append([stage.get(k, 0.0) for k in ("scan", "gather_hits", "align", "gather_alignments")])
         barrier(); a3 = time.perf_counter()
         t_score.append(a2 - a1); t_full.append(a3 - a2)
     idx = S.native_shard_indices(db.offsets, rank, world)
@@ -160,7 +163,9 @@ def search_block(swb, local_rank, rank, world, roof_gcups, hbm_peak, steps=3):
     sc_host, _, _ = S.search_scores(eng, q, sub)
     barrier(); b1 = time.perf_counter()
     same = bool(np.array_equal(sc_host, ddb.scores()[0])) if world == 1 else None
-    t = torch.tensor([min(t_score), min(t_full), min(dev_ms), b1 - b0, min(tb_ms), float(ddb.residues), float(owned)], dtype=torch.float64, device=dev)
+    best_step = int(np.argmin(t_full))
+    t = torch.tensor([min(t_score), min(t_full), min(dev_ms), b1 - b0, min(tb_ms), float(ddb.residues), float(owned)] + stages[best_step],
+                     dtype=torch.float64, device=dev)
     if world > 1:
         tm = t.clone(); dist.all_reduce(tm, op=dist.ReduceOp.MAX)
         ts = t.clone(); dist.all_reduce(ts, op=dist.ReduceOp.SUM)
@@ -177,6 +182,8 @@ def search_block(swb, local_rank, rank, world, roof_gcups, hbm_peak, steps=3):
             "score_stage_s": tm[0].item(), "gcups_score_stage": cells / tm[0].item() / 1e9,
             "score_plus_traceback_s": tm[1].item(), "gcups_with_traceback": cells / tm[1].item() / 1e9,
             "traceback_device_ms_max_rank": tm[4].item(), "hits_traced_by_this_rank": int(owned), "hits_traced_total": int(ts[6].item()),
+            "stage_wall_ms_max_rank": {"scan": tm[7].item() * 1e3, "gather_hits": tm[8].item() * 1e3, "align_own_hits": tm[9].item() * 1e3,
+                                       "gather_alignments": tm[10].item() * 1e3},
             "per_gpu": {"gcups_scan": per_gpu_scan, "frac_of_dpx_roof": per_gpu_scan / roof_gcups,
                         "hbm_gbs_streamed_shard": tm[5].item() / (tm[2].item() * 1e-3) / 1e9, "hbm_peak_gbs": hbm_peak,
                         "hbm_frac": tm[5].item() / (tm[2].item() * 1e-3) / 1e9 / hbm_peak},
@@ -210,7 +217,7 @@ def other_configs(swb, dev):
                                              ("configs[4] 256 x 10 kb DNA pairs, global, strings", swb.ALIGN_GLOBAL, 256, 10000, 0.05, 0.05)):
         sa, sb = noisy(n, length, sub, indel)
         eng = swb.SequenceAlignment(dna, 5.0, 2.0, mode, device=dev)
-        eng.align_list(sa[:1], sb[:1], True)
+        eng.align_list(sa, sb, True)                           # warm-up at the full size: the engine's scratch grows once
         t0 = time.perf_counter(); r = eng.align_list(sa, sb, True); dt = time.perf_counter() - t0
         cells = float(sum(len(x) * len(y) for x, y in zip(sa, sb)))
         out[tag] = {"gcups": cells / dt / 1e9, "seconds": dt, "device_ms": eng.stats()["kernel_ms"],

@@ -275,7 +275,7 @@ def search_scores(engine, query, db):
 
 
 def search(engine, query, db, topk=100, traceback=True, retain_all=False, rank=0, world_size=1, shard=None, device=None,
-           score_fn=None, ddb=None, gather_alignments=True):
+           score_fn=None, ddb=None, gather_alignments=True, timings=None):
     """Top-k hits of `query` in `db`.
 
     ddb: the rank's resident shard (DeviceDatabase(engine, db, rank, world_size)); built here when absent -- callers that
@@ -283,8 +283,15 @@ def search(engine, query, db, topk=100, traceback=True, retain_all=False, rank=0
     merges the per-rank lists (swb_search_merge), every rank traces the hits it owns and the alignments are gathered.
     score_fn: replaces the device path by a host scoring function over (engine, query, shard Database) -- the CPU
     multi-process tests of the rank logic.
+    timings: a dict that receives the wall seconds of the stages (scan, gather_hits, align, gather_alignments).
     Returns a list of dicts: idx, score, end_q, end_t (+ aln_q, aln_t, idx_q, idx_t when traceback).
     """
+    import time
+    tick = [time.perf_counter()]
+
+    def lap(name):
+        if timings is not None:
+            now = time.perf_counter(); timings[name] = now - tick[0]; tick[0] = now
     own_ddb = False
     if score_fn is not None:                                  # host restatement (tests): shard, score, select with numpy
         if world_size > 1:
@@ -301,18 +308,22 @@ def search(engine, query, db, topk=100, traceback=True, retain_all=False, rank=0
         if own_ddb:
             ddb = DeviceDatabase(engine, db, rank, world_size)
         local = ddb.search(query, topk)
+    lap("scan")
     best = merge_hits(allgather_hits(local, topk, device), topk) if world_size > 1 else local
+    lap("gather_hits")
     hits = [{"idx": int(r["index"]), "score": float(r["score"]), "end_q": int(r["end_q"]), "end_t": int(r["end_t"])} for r in best]
     if traceback and hits and engine is not None:
         if score_fn is not None:
             mine = {k: a for k, a in enumerate(engine.align_list([query] * len(hits), [db.sequence(h["idx"]) for h in hits], retain_all=retain_all))}
         else:
             mine = ddb.align(query, best, retain_all)         # only the hits whose subject lives in this shard
+        lap("align")
         if world_size > 1 and score_fn is None and gather_alignments:
             import torch.distributed as dist
             parts = [None] * world_size
             dist.all_gather_object(parts, {k: (a["aln_a"], a["aln_b"], a["idx_a"], a["idx_b"], a["score"]) for k, a in mine.items()})
             mine = {k: {"aln_a": v[0], "aln_b": v[1], "idx_a": v[2], "idx_b": v[3], "score": v[4]} for p in parts for k, v in p.items()}
+        lap("gather_alignments")
         for k, h in enumerate(hits):
             a = mine.get(k)
             if a is None:

@@ -392,6 +392,63 @@ def test_config4_dna_pair_100kb_properties(monkeypatch):
     assert scores[swb.ALIGN_GLOBAL] <= scores[swb.ALIGN_LOCAL]
 
 
+@pytest.mark.timeout(1500)
+def test_config4_100kb_score_and_end_cell_vs_integer_oracle_all_modes():
+    """BASELINE configs[3] at FULL size (100 kb x ~100 kb, 10^10 cells) in all three modes: score and end cell of the
+    score-only path against the linear-memory integer oracle (SA.rs:438-467 score_only scan); the three oracle runs
+    (about a minute each on one host core) go in parallel threads."""
+    import threading
+    rng = np.random.default_rng(20244)
+    a = _rand_seqs(rng, 1, 100000, 100000, "ACGT")[0]
+    b = _mutate(rng, a, 0.08, 0.02, 0.02)
+    m = swb.SubstitutionMatrix.get_mat_matrix(2.0, -3.0)
+    om = _omatrix(m)
+    ia, oa = O.pack([om.seq_to_index(a.decode())]); ib, ob = O.pack([om.seq_to_index(b.decode())])
+    mi = np.rint(m.scores).astype(np.int32)
+    modes = (swb.ALIGN_LOCAL, swb.ALIGN_GLOBAL, swb.ALIGN_GLOCAL)
+    want = {}
+
+    def run(mode):
+        osc, oi, oj = O.score_batch_int(ia, oa, ib, ob, mi, -5, -2, 1, mode, 1)
+        want[mode] = (float(osc[0]), int(oi[0]), int(oj[0]))
+    th = [threading.Thread(target=run, args=(mode,)) for mode in modes]
+    for t in th:
+        t.start()
+    got = {}
+    for mode in modes:
+        eng = swb.SequenceAlignment(m, 5.0, 2.0, mode)
+        sc, ea, eb = eng.score_batch([a], [b])
+        got[mode] = (float(sc[0]), int(ea[0]), int(eb[0]))
+        eng.close()
+    for t in th:
+        t.join()
+    assert got == want
+    assert got[swb.ALIGN_GLOBAL][0] <= got[swb.ALIGN_GLOCAL][0] <= got[swb.ALIGN_LOCAL][0]
+
+
+def test_glocal_batch_10kb_with_strings():
+    """Glocal at the configs[4] size (10 kb noisy DNA pairs, one sequence a fragment of the other in half of them): scores
+    against the integer oracle on all pairs, strings against the dense oracle on two, re-scoring of the core on all."""
+    rng = np.random.default_rng(20246)
+    n = 12
+    sa = _rand_seqs(rng, n, 10000, 10000, "ACGT")
+    sb = [_mutate(rng, s if k % 2 else s[1500:8200], 0.05, 0.04, 0.04) for k, s in enumerate(sa)]
+    m = swb.SubstitutionMatrix.get_mat_matrix(2.0, -3.0)
+    om = _omatrix(m)
+    eng = swb.SequenceAlignment(m, 5.0, 2.0, swb.ALIGN_GLOCAL)
+    res = eng.align_list(sa, sb, False)
+    sc, ea, eb = eng.score_batch(sa, sb)
+    ia, oa = O.pack([om.seq_to_index(s.decode()) for s in sa]); ib, ob = O.pack([om.seq_to_index(s.decode()) for s in sb])
+    osc, oi, oj = O.score_batch_int(ia, oa, ib, ob, np.rint(m.scores).astype(np.int32), -5, -2, 1, swb.ALIGN_GLOCAL, 8)
+    assert [r["score"] for r in res] == [float(x) for x in osc] == [float(x) for x in sc]
+    assert np.array_equal(ea, oi) and np.array_equal(eb, oj)
+    oeng = O.Engine(om, 5.0, 2.0, swb.ALIGN_GLOCAL)
+    for k in (0, 1):
+        r1, r2, osc1 = oeng.align(sa[k].decode(), sb[k].decode(), False)
+        assert (res[k]["aln_a"], res[k]["aln_b"], res[k]["score"]) == ("".join(r1), "".join(r2), osc1)
+    eng.close()
+
+
 def test_config5_nw_batch_10kb():
     """BASELINE configs[4]: Needleman-Wunsch (global) on a batch of 10 kb noisy-read-like DNA pairs with traceback
     strings: dense oracle on two pairs (strings), linear integer oracle on all (scores), re-scoring on all."""
