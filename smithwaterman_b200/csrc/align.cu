@@ -220,6 +220,11 @@ static int align_jobs_k3(swb_engine *e, const uint8_t *d_a, const uint8_t *d_b, 
     const bool dyadic = (e->scale & (e->scale - 1)) == 0;
     auto to_f = [&](int64_t s) { return dyadic ? (float)s * inv : (float)((double)s / e->scale); };
     const int64_t budget = dir_budget();
+    // transposition needs a symmetric score table (the kernels look up table[row residue][column residue])
+    bool swap_ok = true, swap_all = false;
+    for (int r = 0; r < e->n && swap_ok; ++r)
+        for (int c = 0; c < r; ++c) if (e->mat[(size_t)r * e->n + c] != e->mat[(size_t)c * e->n + r]) { swap_ok = false; break; }
+    if (const char *f = getenv("SWB_K3_SWAP")) { if (atoi(f) == 0) swap_ok = false; else swap_all = true; }   // tests force both forms
     // longest first: a warp takes one pair at a time from a counter
     std::sort(sel.begin(), sel.end(), [&](size_t x, size_t y) { return (int64_t)jobs[x].la * jobs[x].lb > (int64_t)jobs[y].la * jobs[y].lb; });
     size_t pos = 0;
@@ -230,13 +235,17 @@ static int align_jobs_k3(swb_engine *e, const uint8_t *d_a, const uint8_t *d_b, 
         size_t end = pos;
         while (end < sel.size()) {
             const AlnJob &J = jobs[sel[end]];
-            int64_t c4, rw; k3_sizes(J.la, J.lb, &c4, &rw);
+            // a tall box (many rows, few columns) is one long sweep of a single warp; transposed it is several short sweeps
+            // that a team of warps pipelines (the hits of a search: 5000 query rows x a few hundred subject columns)
+            const bool swp = swap_ok && (swap_all || J.la > 2 * (int64_t)J.lb);
+            const int32_t la_k = swp ? J.lb : J.la, lb_k = swp ? J.la : J.lb;
+            int64_t c4, rw; k3_sizes(la_k, lb_k, &c4, &rw);
             rw = (rw + 3) / 4 * 4;
             if (!hp.empty() && (colb + c4) * 16 + (rowb + rw) * 4 > budget) break;
-            K3Pair P; P.a_off = J.a_off; P.b_off = J.b_off; P.la = J.la; P.lb = J.lb; P.colb_off = colb; P.rowb_off = rowb; P.out_off = out_total;
-            P.start_state = 0; P.score = J.known_score == INT32_MIN ? 0 : J.known_score;
+            K3Pair P; P.a_off = J.a_off; P.b_off = J.b_off; P.la = la_k; P.lb = lb_k; P.colb_off = colb; P.rowb_off = rowb; P.out_off = out_total;
+            P.start_state = 0; P.score = J.known_score == INT32_MIN ? 0 : J.known_score; P.swap = swp ? 1 : 0; P.pad_ = 0;
             hp.push_back(P);
-            max_sweeps = std::max(max_sweeps, (J.lb + 1023) / 1024);
+            max_sweeps = std::max(max_sweeps, (lb_k + 1023) / 1024);
             colb += c4; rowb += rw; out_total += (int64_t)J.la + J.lb + 1;
             ++end;
         }
@@ -279,10 +288,12 @@ static int align_jobs_k3(swb_engine *e, const uint8_t *d_a, const uint8_t *d_b, 
                 if (hnc[t] < 0) { fail.store(SWB_ERR_EMPTY); return; }
                 const int64_t nc = hnc[t];
                 std::vector<int64_t> xa(nc), xb(nc);
-                for (int64_t c = 0; c < nc; ++c) { xa[c] = hxa[hp[t].out_off + nc - 1 - c]; xb[c] = hxb[hp[t].out_off + nc - 1 - c]; }   // reverse (SA.rs:384-385)
+                const int32_t *la_list = hp[t].swap ? hxb : hxa, *lb_list = hp[t].swap ? hxa : hxb;     // transposed pairs: rows were b
+                for (int64_t c = 0; c < nc; ++c) { xa[c] = la_list[hp[t].out_off + nc - 1 - c]; xb[c] = lb_list[hp[t].out_off + nc - 1 - c]; }   // reverse (SA.rs:384-385)
                 std::string ra, rb;
                 inflate(J.ra, J.la_full, J.rb, J.lb_full, xa.data(), xb.data(), nc, e->mode, retain_all, ra, rb);
-                if (fill_out(&outs[J.out], to_f(hr[t].score), hr[t].end_i, hr[t].end_j, xa, xb, ra, rb) != SWB_OK) { fail.store(SWB_ERR_NOMEM); return; }
+                const int64_t ei = hp[t].swap ? hr[t].end_j : hr[t].end_i, ej = hp[t].swap ? hr[t].end_i : hr[t].end_j;
+                if (fill_out(&outs[J.out], to_f(hr[t].score), ei, ej, xa, xb, ra, rb) != SWB_OK) { fail.store(SWB_ERR_NOMEM); return; }
             }
         };
         const int n_thr = (np >= 8) ? (int)std::min<unsigned>(std::max(1u, std::thread::hardware_concurrency()), 16u) : 1;

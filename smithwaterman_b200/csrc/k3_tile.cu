@@ -95,7 +95,7 @@ k3_fill_kernel(const uint8_t *__restrict__ a_all, const uint8_t *__restrict__ b_
         const int g = pair_sh[slot];
         if (g >= n_pairs) break;
         const K3Pair P = pairs[g];
-        const uint8_t *a = a_all + P.a_off, *b = b_all + P.b_off;
+        const uint8_t *a = P.swap ? b_all + P.b_off : a_all + P.a_off, *b = P.swap ? a_all + P.a_off : b_all + P.b_off;
         const int la = P.la, lb = P.lb;
         const int n_pass = (lb + K1_STRIP - 1) / K1_STRIP;
         const int nblk = (la + 1 + 3) >> 2;                          // row blocks: steps 1 .. la+1 (the high half trails by one row)
@@ -287,7 +287,14 @@ kt3_walk_kernel(const uint8_t *__restrict__ a_all, const uint8_t *__restrict__ b
     if (p >= n_pairs) return;
     KT3Smem &S = sm_all[wib];
     const K3Pair P = pairs[p];
-    const uint8_t *a = a_all + P.a_off, *b = b_all + P.b_off;
+    // Transposed pairs (P.swap): rows = b, columns = a.  The gap-state rules of the reference mirror each other (GAPINX prefers
+    // X > M > Y where GAPINY prefers Y > M > X, SA.rs:172-211; local Y > M > X / X > M > Y, SA.rs:214-252) and so do the
+    // boundaries (SA.rs:100-118), so the cell is the same with the state names X and Y exchanged; what is NOT symmetric is
+    // the MATCH predecessor priority M > X > Y (SA.rs:139-158) and the start-state order M, X, Y (SA.rs:302-308): in the
+    // transposed names they read M > Y > X.  The host exchanges the two column lists and the end cell back.
+    const bool swp = P.swap != 0;
+    const uint8_t *a = swp ? b_all + P.b_off : a_all + P.a_off, *b = swp ? a_all + P.a_off : b_all + P.b_off;
+    auto am = [swp](int m, int x, int y) -> unsigned { return (m >= x && m >= y) ? 0u : (swp ? ((y >= x) ? 2u : 1u) : ((x >= y) ? 1u : 2u)); };
     const int la = P.la, lb = P.lb;
     const int nblk = (la + 1 + 3) >> 2, n_pass = (lb + K1_STRIP - 1) / K1_STRIP;
     const uint4 *cb = colb + P.colb_off;
@@ -350,7 +357,7 @@ kt3_walk_kernel(const uint8_t *__restrict__ a_all, const uint8_t *__restrict__ b
             // diagonal of this lane's first cell: cell (rtop, j - 1)
             int dM = __shfl_up_sync(0xffffffffu, Mu, 1), dX = __shfl_up_sync(0xffffffffu, Xu, 1), dY = __shfl_up_sync(0xffffffffu, Yu, 1);
             if (lane == 0) { const int4 v = S.left[0]; dM = v.x; dX = v.y; dY = v.z; }
-            int hd0 = __vimax3_s32(dM, dX, dY); unsigned ad0 = kw_am(dM, dX, dY);
+            int hd0 = __vimax3_s32(dM, dX, dY); unsigned ad0 = am(dM, dX, dY);
             int lastM = 0, lastX = 0, lastY = 0;
             const int bcode = (j <= lb) ? (int)b[j - 1] : 0;
             const int n_steps = nrows + ncols - 1;
@@ -364,7 +371,7 @@ kt3_walk_kernel(const uint8_t *__restrict__ a_all, const uint8_t *__restrict__ b
                 if (lane < ncols && r >= 1 && r <= nrows) {
                     if (lane == 0) { const int4 v = S.left[r]; tM = v.x; tX = v.y; tY = v.z; }
                     const int hd = hd0; const unsigned ad = ad0;
-                    hd0 = __vimax3_s32(tM, tX, tY); ad0 = kw_am(tM, tX, tY);
+                    hd0 = __vimax3_s32(tM, tX, tY); ad0 = am(tM, tX, tY);
                     int mm, xx, yy; unsigned code;
                     kw_cell<MODE>(hd, ad, tM, tX, tY, Mu, Xu, Yu, s, o, e, o, e, mm, xx, yy, code);
                     Mu = mm; Xu = xx; Yu = yy;
@@ -377,8 +384,8 @@ kt3_walk_kernel(const uint8_t *__restrict__ a_all, const uint8_t *__restrict__ b
                 const int src = ncols - 1;
                 const int fm = __shfl_sync(0xffffffffu, Mu, src), fx = __shfl_sync(0xffffffffu, Xu, src), fy = __shfl_sync(0xffffffffu, Yu, src);
                 score = fm; st = 0;
-                if (fx > score) { score = fx; st = 1; }
-                if (fy > score) { score = fy; st = 2; }
+                if (!swp) { if (fx > score) { score = fx; st = 1; } if (fy > score) { score = fy; st = 2; } }
+                else { if (fy > score) { score = fy; st = 2; } if (fx > score) { score = fx; st = 1; } }
                 need_start = false;
             }
         }

@@ -231,6 +231,8 @@ struct K3Pair {
     int64_t out_off;                // offset of the pair's reversed column lists
     int32_t start_state;            // local: 0 (MATCH); global: taken from the recomputed cell (la, lb)
     int32_t score;                  // local: the scan's score (scaled); global: filled in by the walker
+    int32_t swap;                   // 1: the kernels run the TRANSPOSED problem (rows = b, columns = a; la / lb above are the transposed
+    int32_t pad_;                   //    extents): a tall box becomes a wide one, whose sweeps pipeline over a team of warps
 };
 bool k3_eligible(const swb_engine *e, int64_t la, int64_t lb);       // mode, |open| >= |extend| and the static s16 bound (global)
 void k3_sizes(int32_t la, int32_t lb, int64_t *colb_uint4, int64_t *rowb_words);

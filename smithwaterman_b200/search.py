@@ -241,24 +241,76 @@ def topk_records(scores, idx, end_q, end_t, k):
     return rec[order[:k]]
 
 
-def allgather_hits(local, k, device=None):
-    """THE collective of the search: all-gather of the fixed-size per-rank hit blocks (k x 32 bytes, padded)."""
+def _allgather_blocks(block, device):
+    """All-gather of one equally sized uint8 block per rank -> (world, len(block)) numpy array: one collective into one
+    device tensor, one copy back."""
     import torch
     import torch.distributed as dist
     world = dist.get_world_size()
+    t = torch.from_numpy(block)
+    if device is not None:
+        t = t.to(device, non_blocking=True)
+    out = torch.empty(world * t.numel(), dtype=torch.uint8, device=t.device)
+    dist.all_gather_into_tensor(out, t)
+    return out.cpu().numpy().reshape(world, -1)
+
+
+def allgather_hits(local, k, device=None):
+    """THE collective of the search: all-gather of the fixed-size per-rank hit blocks (k x 32 bytes, padded)."""
     buf = np.zeros(k, HIT_DTYPE)
     buf["index"] = -1
     buf[:len(local)] = local
-    t = torch.from_numpy(buf.view(np.uint8).copy())
-    if device is not None:
-        t = t.to(device)
-    outs = [torch.empty_like(t) for _ in range(world)]
-    dist.all_gather(outs, t)
     parts = []
-    for o in outs:
-        a = o.cpu().numpy().view(HIT_DTYPE)
+    for row in _allgather_blocks(buf.view(np.uint8).copy(), device):
+        a = row.view(HIT_DTYPE)
         parts.append(a[a["index"] >= 0])
     return parts
+
+
+_ALN_HDR = np.dtype([("k", "<i8"), ("n", "<i8"), ("score", "<f8"), ("start_a", "<i8"), ("start_b", "<i8")])
+
+
+def pack_alignments(mine):
+    """{position: alignment dict} of core alignments (retain_all = False) -> one uint8 array: per hit a 40-byte header and
+    the two strings.  The column index lists are not sent: they follow from the strings and the first residue index."""
+    chunks = []
+    for k, a in mine.items():
+        h = np.zeros(1, _ALN_HDR)
+        xa, xb = np.asarray(a["idx_a"]), np.asarray(a["idx_b"])
+        fa, fb = xa[xa >= 0], xb[xb >= 0]
+        h["k"], h["n"], h["score"] = k, len(a["aln_a"]), a["score"]
+        h["start_a"], h["start_b"] = (fa[0] if len(fa) else 0), (fb[0] if len(fb) else 0)
+        chunks += [h.view(np.uint8), np.frombuffer(a["aln_a"].encode("latin-1"), np.uint8), np.frombuffer(a["aln_b"].encode("latin-1"), np.uint8)]
+    return np.concatenate(chunks) if chunks else np.zeros(0, np.uint8)
+
+
+def unpack_alignments(buf):
+    out = {}
+    p = 0
+    while p < len(buf):
+        h = buf[p:p + _ALN_HDR.itemsize].view(_ALN_HDR)[0]; p += _ALN_HDR.itemsize
+        n = int(h["n"])
+        sa, sb = buf[p:p + n], buf[p + n:p + 2 * n]; p += 2 * n
+        ga, gb = sa != ord("-"), sb != ord("-")
+        out[int(h["k"])] = {"aln_a": sa.tobytes().decode("latin-1"), "aln_b": sb.tobytes().decode("latin-1"), "score": float(h["score"]),
+                            "idx_a": np.where(ga, int(h["start_a"]) + np.cumsum(ga) - 1, -1).astype(np.int64),
+                            "idx_b": np.where(gb, int(h["start_b"]) + np.cumsum(gb) - 1, -1).astype(np.int64)}
+    return out
+
+
+def allgather_alignments(mine, device=None):
+    """Every rank's traced hits on every rank: the sizes (8 bytes per rank), then the packed strings padded to the largest."""
+    payload = pack_alignments(mine)
+    sizes = _allgather_blocks(np.array([len(payload)], np.int64).view(np.uint8), device).view(np.int64).ravel()
+    width = int(sizes.max())
+    if width == 0:
+        return {}
+    block = np.zeros(width, np.uint8); block[:len(payload)] = payload
+    rows = _allgather_blocks(block, device)
+    out = {}
+    for r, sz in zip(rows, sizes):
+        out.update(unpack_alignments(r[:int(sz)]))
+    return out
 
 
 def search_scores(engine, query, db):
@@ -319,10 +371,13 @@ def search(engine, query, db, topk=100, traceback=True, retain_all=False, rank=0
             mine = ddb.align(query, best, retain_all)         # only the hits whose subject lives in this shard
         lap("align")
         if world_size > 1 and score_fn is None and gather_alignments:
-            import torch.distributed as dist
-            parts = [None] * world_size
-            dist.all_gather_object(parts, {k: (a["aln_a"], a["aln_b"], a["idx_a"], a["idx_b"], a["score"]) for k, a in mine.items()})
-            mine = {k: {"aln_a": v[0], "aln_b": v[1], "idx_a": v[2], "idx_b": v[3], "score": v[4]} for p in parts for k, v in p.items()}
+            if not retain_all:                                # core alignments: strings only, two small collectives
+                mine = allgather_alignments(mine, device)
+            else:
+                import torch.distributed as dist
+                parts = [None] * world_size
+                dist.all_gather_object(parts, {k: (a["aln_a"], a["aln_b"], a["idx_a"], a["idx_b"], a["score"]) for k, a in mine.items()})
+                mine = {k: {"aln_a": v[0], "aln_b": v[1], "idx_a": v[2], "idx_b": v[3], "score": v[4]} for p in parts for k, v in p.items()}
         lap("gather_alignments")
         for k, h in enumerate(hits):
             a = mine.get(k)

@@ -996,12 +996,16 @@ def test_perl_harness_over_the_cli(tmp_path):
     assert r.stdout.splitlines()[-2:] == ["OK", "Checked 300 results"]
 
 
+@pytest.mark.parametrize("swap", [None, "0", "1"])
 @pytest.mark.parametrize("go,ge,protein", [(5.0, 2.0, False), (10.0, 0.5, True), (2.0, 2.0, False)])
-def test_packed_traceback_path_global(go, ge, protein, monkeypatch):
+def test_packed_traceback_path_global(go, ge, protein, swap, monkeypatch):
     """The packed traceback path (csrc/k3_tile.cu: s16x2 fill with tile borders + tile-recompute walk) in global mode:
     strings, index lists and scores equal the dense oracle's on pairs of every shape -- single pass, several sweeps of
     1024 columns, fewer rows than one checkpoint, one-letter sequences, unrelated pairs -- and equal the direction-byte
     path on 6 kb pairs."""
+    # swap: SWB_K3_SWAP forces every pair through the transposed form of the kernels (rows = b) or none; default: tall pairs only
+    if swap is not None:
+        monkeypatch.setenv("SWB_K3_SWAP", swap)
     rng = np.random.default_rng(int(go * 7 + ge * 3))
     m = swb.SubstitutionMatrix.get_blosum62_matrix() if protein else swb.SubstitutionMatrix.get_mat_matrix(2.0, -3.0)
     al = AA if protein else "ACGT"
@@ -1035,11 +1039,14 @@ def test_packed_traceback_path_global(go, ge, protein, monkeypatch):
     eng.close()
 
 
-def test_packed_traceback_path_local_hits():
+@pytest.mark.parametrize("swap", [None, "0", "1"])
+def test_packed_traceback_path_local_hits(swap, monkeypatch):
     """Local mode on the packed path: hits of a database search are traced inside the prefix box of their end cell with
     the scan's score as the s16 guarantee; strings equal the oracle's, with and without retain_all, for subjects of one
     pass up to several sweeps, and the direction-byte path gives the same."""
     from smithwaterman_b200 import search as S
+    if swap is not None:
+        monkeypatch.setenv("SWB_K3_SWAP", swap)
     rng = np.random.default_rng(99)
     m = swb.SubstitutionMatrix.get_blosum62_matrix()
     eng = swb.SequenceAlignment(m, 10.0, 0.5, swb.ALIGN_LOCAL)

@@ -49,6 +49,15 @@ def _worker(rank, world, port, out, db_path=None):
         db = S.Database.load(db_path)
     hits = S.search(None, query, db, topk=25, traceback=False, rank=rank, world_size=world, score_fn=_oracle_score_fn)
     out[rank] = [(h["idx"], h["score"], h["end_q"], h["end_t"]) for h in hits]
+    # the second exchange: every rank's traced alignments on every rank (packed strings, two small collectives)
+    mine = {k: {"aln_a": "AC-GT" * (k + 1), "aln_b": "A-TGT" * (k + 1), "score": float(k),
+                "idx_a": np.where(np.tile([1, 1, 0, 1, 1], k + 1) > 0, 10 * k + np.cumsum(np.tile([1, 1, 0, 1, 1], k + 1)) - 1, -1),
+                "idx_b": np.where(np.tile([1, 0, 1, 1, 1], k + 1) > 0, 3 + np.cumsum(np.tile([1, 0, 1, 1, 1], k + 1)) - 1, -1)}
+            for k in range(rank, 7, world)}
+    if rank == 1:
+        mine[9] = {"aln_a": "", "aln_b": "", "score": 0.0, "idx_a": np.zeros(0, np.int64), "idx_b": np.zeros(0, np.int64)}
+    got = S.allgather_alignments(mine)
+    out["aln%d" % rank] = {k: (v["aln_a"], v["aln_b"], v["score"], v["idx_a"].tolist(), v["idx_b"].tolist()) for k, v in got.items()}
     dist.destroy_process_group()
 
 
@@ -73,6 +82,9 @@ def test_world2_gloo_matches_single_process():
     single = S.search(None, query, db, topk=25, traceback=False, score_fn=_oracle_score_fn)
     ref = [(h["idx"], h["score"], h["end_q"], h["end_t"]) for h in single]
     assert out[0] == ref and out[1] == ref
+    assert out["aln0"] == out["aln1"] and sorted(out["aln0"]) == [0, 1, 2, 3, 4, 5, 6, 9]
+    a3 = out["aln0"][3]
+    assert a3[0] == "AC-GT" * 4 and a3[2] == 3.0 and a3[3][:5] == [30, 31, -1, 32, 33] and a3[4][:5] == [3, -1, 4, 5, 6]
     # ties resolved by the lower database index; planted duplicates guarantee at least one tie
     scores = [r[1] for r in ref]
     assert any(scores[i] == scores[i + 1] and ref[i][0] < ref[i + 1][0] for i in range(len(ref) - 1))
@@ -93,6 +105,9 @@ def test_world2_gloo_from_packed_database_file(tmp_path):
     single = S.search(None, query, db, topk=25, traceback=False, score_fn=_oracle_score_fn)
     ref = [(h["idx"], h["score"], h["end_q"], h["end_t"]) for h in single]
     assert out[0] == ref and out[1] == ref
+    assert out["aln0"] == out["aln1"] and sorted(out["aln0"]) == [0, 1, 2, 3, 4, 5, 6, 9]
+    a3 = out["aln0"][3]
+    assert a3[0] == "AC-GT" * 4 and a3[2] == 3.0 and a3[3][:5] == [30, 31, -1, 32, 33] and a3[4][:5] == [3, -1, 4, 5, 6]
 
 
 def test_packed_database_file_round_trip(tmp_path):
