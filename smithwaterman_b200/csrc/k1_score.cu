@@ -435,6 +435,226 @@ k2_search_kernel(const unsigned *__restrict__ a_words, int la, const uint8_t *__
     }
 }
 
+// ------------------------------------------------------------------------------------------------------------------
+// K2P -- K2 with a QUERY PROFILE.  The query is the same for every subject of a search, so the substitution scores are
+// laid out once per block as bytes  QP[column residue c][row x] = s(query[x], c) - open  (0 <= x < la; 0 in the margins
+// and for the PAD residue, i.e. s = open there: a PAD row keeps the initial state, a PAD column only ever holds
+// (real H) + open < best).  A cell-vector then fetches its two scores with two LDS.U8 whose row offset is an IMMEDIATE
+// (t = 0..3 inside a 4-row block; the per-column pointers advance by 4 once per block) and merges them with one IMAD:
+// no row-residue extraction, no per-cell address arithmetic -- 9 issue slots per cell-vector instead of 14.  The
+// recurrence, the lane skew, the boundary exchange and the end-cell logic are K2's.  Needs every s - open in [0, 127]
+// (|open| >= |smin|: BLOSUM62 with 10/0.5 gives 12..42) and a query whose profile fits shared memory; k2_launch falls
+// back to K2 otherwise.
+template <int IMM>
+__device__ __forceinline__ unsigned ldsu8i(unsigned addr)
+{
+    unsigned v;
+    asm("ld.shared.u8 %0, [%1+%2];" : "=r"(v) : "r"(addr), "n"(IMM));
+    return v;
+}
+
+#define K2P_MARGIN 128                 // profile bytes before row 1: lane l starts l row blocks early (the high half one row earlier still)
+#define K2P_TAIL 144                   // and after row la: 31 blocks of skew + the block that finishes the high half
+
+#define K2P_CELL(k, T)                                                                               \
+    {                                                                                                \
+        unsigned s_lo = ldsu8i<T>(plo[k]);                                                           \
+        unsigned s_hi = ldsu8i<T>(phi[k]);                                                           \
+        unsigned s2 = s_hi * 65536u + s_lo;                                                          \
+        unsigned Fk = __viaddmax_s16x2(F[k], ext2, Ho[k]);                                           \
+        unsigned G = __viaddmax_s16x2_relu(HoD, s2, Fk);                                             \
+        E = __viaddmax_s16x2(E, ext2, GoP);                                                          \
+        GoP = __vadd2(G, open2);                                                                     \
+        HoD = Ho[k];                                                                                 \
+        Ho[k] = __viaddmax_s16x2(E, open2, GoP);                                                     \
+        F[k] = Fk;                                                                                   \
+    }
+
+#define K2P_ROW(T)                                                                                                     \
+    {                                                                                                                  \
+        const int i = i0 + T + 1;                    /* low lane row; high lane row = i-1 */                           \
+        unsigned GoP = __byte_perm(bq[T], lo15_Ho, 0x5410);                                                            \
+        unsigned E = __byte_perm(bq[T], lo15_E, 0x5432);                                                               \
+        const unsigned HoD_next = GoP;                                                                                 \
+        K2P_CELL(0, T) K2P_CELL(1, T) K2P_CELL(2, T) K2P_CELL(3, T) K2P_CELL(4, T) K2P_CELL(5, T) K2P_CELL(6, T) K2P_CELL(7, T) \
+        K2P_CELL(8, T) K2P_CELL(9, T) K2P_CELL(10, T) K2P_CELL(11, T) K2P_CELL(12, T) K2P_CELL(13, T) K2P_CELL(14, T) K2P_CELL(15, T) \
+        wout[T] = __byte_perm(Ho[15], E, 0x7632);    /* column 32q+31 at row i-1 */                                    \
+        if (T == 0) {                                                                                                  \
+            const unsigned s0 = __shfl_up_sync(0xffffffffu, wout[0], 1);                                               \
+            bq[3] = first ? open2 : (from_g ? g4.w : s0);                                                              \
+            if (to_g && bl > 0) mybnd[bl - 1] = make_uint4(c1, c2, c3, wout[0]);                                       \
+        }                                                                                                              \
+        lo15_Ho = Ho[15]; lo15_E = E;                                                                                  \
+        HoD = HoD_next;                                                                                                \
+        unsigned rm = __vimax3_s16x2(thr2, Ho[0], Ho[1]);                                                              \
+        rm = __vimax3_s16x2(rm, Ho[2], Ho[3]);                                                                         \
+        rm = __vimax3_s16x2(rm, Ho[4], Ho[5]);                                                                         \
+        rm = __vimax3_s16x2(rm, Ho[6], Ho[7]);                                                                         \
+        rm = __vimax3_s16x2(rm, Ho[8], Ho[9]);                                                                         \
+        rm = __vimax3_s16x2(rm, Ho[10], Ho[11]);                                                                       \
+        rm = __vimax3_s16x2(rm, Ho[12], Ho[13]);                                                                       \
+        rm = __vimax3_s16x2(rm, Ho[14], Ho[15]);                                                                       \
+        if (rm != thr2) {                            /* rare path as in K2 */                                          \
+            const int rlo = lo16(rm), rhi = hi16(rm);                                                                  \
+            const bool ulo = i >= 1 && i <= la && (rlo > bestHo || (rlo == bestHo && rlo > open && i < bi));           \
+            if (ulo) { bestHo = rlo; bi = i; bj = jbase; }                                                             \
+            const bool uhi = i >= 2 && i - 1 <= la && (rhi > bestHo || (rhi == bestHo && rhi > open && i - 1 < bi));   \
+            if (uhi) { bestHo = rhi; bi = i - 1; bj = jbase + K1_HALF; }                                               \
+            if (ulo || uhi) {                                                                                          \
+                snap[0] = make_uint4(Ho[0], Ho[1], Ho[2], Ho[3]);                                                      \
+                snap[K1_THREADS * 2] = make_uint4(Ho[4], Ho[5], Ho[6], Ho[7]);                                         \
+                snap[K1_THREADS * 4] = make_uint4(Ho[8], Ho[9], Ho[10], Ho[11]);                                       \
+                snap[K1_THREADS * 6] = make_uint4(Ho[12], Ho[13], Ho[14], Ho[15]);                                     \
+            }                                                                                                          \
+            tb = max(tb, bestHo);                                                                                      \
+            thr2 = pack2(tb - 1, tb - 1);                                                                              \
+        }                                                                                                              \
+    }
+
+__global__ void __launch_bounds__(K1_THREADS * 2, 1)
+k2p_search_kernel(const uint8_t *__restrict__ a_codes, int la, const uint8_t *__restrict__ codes_b,
+                  const int64_t *__restrict__ off_b, long long base_b, const int32_t *__restrict__ item_pairs,
+                  const int32_t *__restrict__ item_sweeps, int n_items, const int32_t *__restrict__ mat, int nl, int open,
+                  int ext, int limit_ho, int pitch, uint4 *__restrict__ gbnd, int gb_blocks, int *counter, K1Result *__restrict__ res)
+{
+    extern __shared__ __align__(16) unsigned char QP_sh[];          // [nl][pitch] bytes, then the snapshot slots
+    __shared__ int cand_sh[K1_THREADS * 2 / 32][32][4];
+    for (int idx = threadIdx.x; idx < nl * pitch; idx += blockDim.x) {
+        const int c = idx / pitch, x = idx - c * pitch - K2P_MARGIN;
+        int v = 0;                                                   // margins and the PAD column: s = open
+        if (x >= 0 && x < la && c != nl - 1) v = mat[(int)a_codes[x] * nl + c] - open;
+        QP_sh[idx] = (unsigned char)v;
+    }
+    __syncthreads();
+
+    const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
+    const int wslot = blockIdx.x * (blockDim.x >> 5) + wib;
+    uint4 *mybnd = gbnd + (size_t)wslot * (size_t)gb_blocks;
+    const unsigned qbase = (unsigned)__cvta_generic_to_shared(QP_sh) + K2P_MARGIN;
+    const unsigned open2 = pack2(open, open), ext2 = pack2(ext, ext);
+    const unsigned pad = (unsigned)(nl - 1);
+    uint4 *snap = reinterpret_cast<uint4 *>(QP_sh + (((size_t)nl * pitch + 15) & ~(size_t)15)) + threadIdx.x;   // [4][thread] uint4
+    const int nblk = (la + 1 + 3) >> 2;              // row blocks of a pass (one step past la finishes the high half)
+
+    for (;;) {
+        int g = 0;
+        if (lane == 0) g = atomicAdd(counter, 1);
+        g = __shfl_sync(0xffffffffu, g, 0);
+        if (g >= n_items) break;
+        const int pair = item_pairs[(size_t)g * 32 + lane];           // caller index of this lane's subject, -1 = idle
+        const int sweeps = item_sweeps[g];
+        const int prev_pair = __shfl_up_sync(0xffffffffu, pair, 1);
+        const bool head = (lane == 0) || (pair != prev_pair);
+        const unsigned heads = __ballot_sync(0xffffffffu, head);
+        const int head_lane = 31 - __clz(heads & (0xffffffffu >> (31 - lane)));
+        const int pos = lane - head_lane;                             // pass index of this lane within its subject
+        const unsigned next_heads = heads & ~((2u << lane) - 1u);     // heads above this lane
+        const int seg_end = next_heads ? (__ffs(next_heads) - 1) : 32;
+        long long ob = 0; int lb = 0;
+        if (pair >= 0) { ob = off_b[pair] - base_b; lb = (int)(off_b[pair + 1] - off_b[pair]); }
+        // Lanes are skewed by their LANE index (K2: by the position inside the subject): lane l is at row block g - l, so the 32
+        // profile words of one LDS lie in 32 different banks whatever the residues are (the profile rows of all residues
+        // start in the same bank: pitch is a multiple of 128 bytes).  A subject that starts at lane h idles h blocks first.
+        const int last_lane = 31 - __clz(__ballot_sync(0xffffffffu, pair >= 0) | 1u);
+        const int n_gb = nblk + last_lane;
+        int bestHo = open, bi = -1, bj = -1;
+        int tb = open;
+
+        for (int sw = 0; sw < sweeps; ++sw) {
+            const int jbase = (sw * 32 + pos) * K1_STRIP;
+            unsigned plo[K1_HALF], phi[K1_HALF], Ho[K1_HALF], F[K1_HALF];
+            // profile pointers of this lane's 32 columns at its first row block (block -pos: rows -4 pos + 1 ..); the high
+            // half is one row behind
+            const unsigned rowoff = qbase + (unsigned)(-4 * lane);
+#pragma unroll
+            for (int k = 0; k < K1_HALF; ++k) {
+                const int j1 = jbase + k, j2 = jbase + K1_HALF + k;
+                const unsigned c1 = (j1 < lb) ? (unsigned)codes_b[ob + j1] : pad;
+                const unsigned c2 = (j2 < lb) ? (unsigned)codes_b[ob + j2] : pad;
+                plo[k] = rowoff + c1 * (unsigned)pitch; phi[k] = rowoff + c2 * (unsigned)pitch - 1u;
+                Ho[k] = open2; F[k] = 0u;
+            }
+            const bool first = (pos == 0 && sw == 0);
+            const bool from_g = (pos == 0 && sw > 0);
+            const bool to_g = (lane == 31 && sw + 1 < sweeps);
+            unsigned HoD = open2, lo15_Ho = open2, lo15_E = open2;
+            unsigned thr2 = pack2(tb - 1, tb - 1);
+            unsigned c1 = open2, c2 = open2, c3 = open2;
+            int bl = -lane;
+            uint4 g_next = make_uint4(open2, open2, open2, open2);
+            if (from_g) g_next = mybnd[0];
+
+#pragma unroll 1
+            for (int gbk = 0; gbk < n_gb; ++gbk, ++bl) {
+                const int i0 = bl * 4;
+                const uint4 g4 = g_next;
+                if (from_g && bl + 1 < nblk) g_next = mybnd[bl + 1];
+                const unsigned s1 = __shfl_up_sync(0xffffffffu, c1, 1), s2_ = __shfl_up_sync(0xffffffffu, c2, 1),
+                               s3 = __shfl_up_sync(0xffffffffu, c3, 1);
+                unsigned bq[4];
+                bq[0] = first ? open2 : (from_g ? g4.x : s1);
+                bq[1] = first ? open2 : (from_g ? g4.y : s2_);
+                bq[2] = first ? open2 : (from_g ? g4.z : s3);
+                bq[3] = open2;
+                unsigned wout[4];
+                K2P_ROW(0) K2P_ROW(1) K2P_ROW(2) K2P_ROW(3)
+#pragma unroll
+                for (int k = 0; k < K1_HALF; ++k) { plo[k] += 4u; phi[k] += 4u; }
+                c1 = wout[1]; c2 = wout[2]; c3 = wout[3];
+                {
+                    const int up = __shfl_up_sync(0xffffffffu, tb, 1), dn = __shfl_down_sync(0xffffffffu, tb, 1);
+                    int nb = tb;
+                    if (!head) nb = max(nb, up);
+                    if (lane + 1 < seg_end) nb = max(nb, dn);
+                    if (nb != tb) { tb = nb; thr2 = pack2(tb - 1, tb - 1); }
+                }
+            }
+            if (to_g) mybnd[nblk - 1] = make_uint4(c1, c2, c3, open2);
+            __syncwarp();
+        }
+
+        if (bestHo > open) {
+            const uint4 s0 = snap[0], s1 = snap[K1_THREADS * 2], s2 = snap[K1_THREADS * 4], s3 = snap[K1_THREADS * 6];
+            const unsigned w[K1_HALF] = {s0.x, s0.y, s0.z, s0.w, s1.x, s1.y, s1.z, s1.w, s2.x, s2.y, s2.z, s2.w, s3.x, s3.y, s3.z, s3.w};
+            const bool hi = (bj & K1_HALF) != 0;
+            int kk = 0;
+#pragma unroll
+            for (int k = K1_HALF - 1; k >= 0; --k)
+                if ((hi ? hi16(w[k]) : lo16(w[k])) == bestHo) kk = k;
+            bj += kk + 1;
+        }
+        cand_sh[wib][lane][0] = bestHo; cand_sh[wib][lane][1] = bi; cand_sh[wib][lane][2] = bj; cand_sh[wib][lane][3] = (bestHo >= limit_ho) ? 1 : 0;
+        __syncwarp();
+        if (head && pair >= 0) {
+            int ovf = (bestHo >= limit_ho) ? 1 : 0;
+            for (int l2 = lane + 1; l2 < seg_end; ++l2) {
+                const int ob_ = cand_sh[wib][l2][0], oi = cand_sh[wib][l2][1], oj = cand_sh[wib][l2][2];
+                ovf |= cand_sh[wib][l2][3];
+                if (ob_ > bestHo || (ob_ == bestHo && ob_ > open && (oi < bi || (oi == bi && oj < bj)))) { bestHo = ob_; bi = oi; bj = oj; }
+            }
+            K1Result r;
+            r.score = bestHo - open;
+            r.end_i = (bestHo > open) ? bi : -1;
+            r.end_j = (bestHo > open) ? bj : -1;
+            r.flags = ovf;
+            res[pair] = r;
+        }
+        __syncwarp();
+    }
+}
+
+// Profile form available?  Every s - open must be a non-negative byte, the profile must fit next to the snapshot slots.
+static int k2p_pitch(const swb_engine *e, int la)
+{
+    if (getenv("SWB_NO_K2P")) return 0;
+    if (e->smin - e->o < 0 || e->smax - e->o > 127) return 0;
+    int pitch = K2P_MARGIN + la + K2P_TAIL;
+    pitch = (pitch + 127) / 128 * 128;                             // every residue's row starts in bank 0 (see the lane skew in the kernel)
+    const int nl = e->n + 1;
+    const size_t smem = (((size_t)nl * pitch + 15) & ~(size_t)15) + (size_t)K1_THREADS * 2 * 4 * sizeof(uint4);
+    return smem <= 220 * 1024 ? pitch : 0;
+}
+
 size_t k2_bnd_bytes(int n_blocks, int la) { return (size_t)n_blocks * (K1_THREADS * 2 / 32) * (size_t)((la + 1 + 3) / 4 + 2) * sizeof(uint4); }
 
 cudaError_t k2_launch(const swb_engine *e, const uint8_t *d_query, int la, const uint8_t *d_codes_b, const int64_t *d_off_b,
@@ -448,6 +668,15 @@ cudaError_t k2_launch(const swb_engine *e, const uint8_t *d_query, int la, const
     err = cudaMemsetAsync(d_counter, 0, sizeof(int32_t), st);
     if (err != cudaSuccess) return err;
     const int limit_ho = 32767 - 2 * e->smax + e->o - 1;
+    if (const int pitch = k2p_pitch(e, la)) {
+        const size_t psmem = (((size_t)nl * pitch + 15) & ~(size_t)15) + (size_t)K1_THREADS * 2 * 4 * sizeof(uint4);
+        err = cudaFuncSetAttribute(k2p_search_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)psmem);
+        if (err != cudaSuccess) return err;
+        k2p_search_kernel<<<n_blocks, K1_THREADS * 2, psmem, st>>>(
+            d_query, la, d_codes_b, d_off_b, (long long)base_b, d_item_pairs, d_item_sweeps, n_items, e->d_mat, nl, e->o, e->e, limit_ho,
+            pitch, reinterpret_cast<uint4 *>(d_gbnd), (la + 1 + 3) / 4 + 2, d_counter, d_res);
+        return cudaGetLastError();
+    }
     k2_search_kernel<<<n_blocks, K1_THREADS * 2, smem, st>>>(
         reinterpret_cast<const unsigned *>(d_query), la, d_codes_b, d_off_b, (long long)base_b, d_item_pairs, d_item_sweeps,
         n_items, e->d_mat, nl, e->o, e->e, limit_ho, reinterpret_cast<uint4 *>(d_gbnd), (la + 1 + 3) / 4 + 2, d_counter, d_res);

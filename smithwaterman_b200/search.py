@@ -17,6 +17,7 @@ merges the per-rank lists and `swb_search_align` traces the hits the shard owns.
 adds the torch.distributed collectives; a C / Rust caller does the same with swb_search_sharded or its own gather.
 """
 import ctypes
+import struct
 import os
 
 import numpy as np
@@ -267,7 +268,17 @@ def allgather_hits(local, k, device=None):
     return parts
 
 
-_ALN_HDR = np.dtype([("k", "<i8"), ("n", "<i8"), ("score", "<f8"), ("start_a", "<i8"), ("start_b", "<i8")])
+_ALN_HDR = struct.Struct("<qqdqq")          # position in the hit list, string length, score, first residue of a / of b
+
+
+def _first_residue(idx):
+    idx = np.asarray(idx)
+    if not len(idx):
+        return 0
+    if idx[0] >= 0:
+        return int(idx[0])
+    nz = np.flatnonzero(idx >= 0)
+    return int(idx[nz[0]]) if len(nz) else 0
 
 
 def pack_alignments(mine):
@@ -275,31 +286,35 @@ def pack_alignments(mine):
     the two strings.  The column index lists are not sent: they follow from the strings and the first residue index."""
     chunks = []
     for k, a in mine.items():
-        h = np.zeros(1, _ALN_HDR)
-        xa, xb = np.asarray(a["idx_a"]), np.asarray(a["idx_b"])
-        fa, fb = xa[xa >= 0], xb[xb >= 0]
-        h["k"], h["n"], h["score"] = k, len(a["aln_a"]), a["score"]
-        h["start_a"], h["start_b"] = (fa[0] if len(fa) else 0), (fb[0] if len(fb) else 0)
-        chunks += [h.view(np.uint8), np.frombuffer(a["aln_a"].encode("latin-1"), np.uint8), np.frombuffer(a["aln_b"].encode("latin-1"), np.uint8)]
-    return np.concatenate(chunks) if chunks else np.zeros(0, np.uint8)
+        chunks.append(_ALN_HDR.pack(k, len(a["aln_a"]), a["score"], _first_residue(a["idx_a"]), _first_residue(a["idx_b"])))
+        chunks.append(a["aln_a"].encode("latin-1")); chunks.append(a["aln_b"].encode("latin-1"))
+    return np.frombuffer(b"".join(chunks), np.uint8)
 
 
-def unpack_alignments(buf):
+def column_indices(aln, start):
+    """Residue index per alignment column (-1 = gap) of a core alignment string that starts at residue `start`."""
+    g = np.frombuffer(aln.encode("latin-1"), np.uint8) != ord("-")
+    return np.where(g, int(start) + np.cumsum(g) - 1, -1).astype(np.int64)
+
+
+def unpack_alignments(buf, index_lists=True):
     out = {}
     p = 0
-    while p < len(buf):
-        h = buf[p:p + _ALN_HDR.itemsize].view(_ALN_HDR)[0]; p += _ALN_HDR.itemsize
-        n = int(h["n"])
-        sa, sb = buf[p:p + n], buf[p + n:p + 2 * n]; p += 2 * n
-        ga, gb = sa != ord("-"), sb != ord("-")
-        out[int(h["k"])] = {"aln_a": sa.tobytes().decode("latin-1"), "aln_b": sb.tobytes().decode("latin-1"), "score": float(h["score"]),
-                            "idx_a": np.where(ga, int(h["start_a"]) + np.cumsum(ga) - 1, -1).astype(np.int64),
-                            "idx_b": np.where(gb, int(h["start_b"]) + np.cumsum(gb) - 1, -1).astype(np.int64)}
+    raw = buf.tobytes()
+    while p < len(raw):
+        k, n, score, start_a, start_b = _ALN_HDR.unpack_from(raw, p); p += _ALN_HDR.size
+        a = {"aln_a": raw[p:p + n].decode("latin-1"), "aln_b": raw[p + n:p + 2 * n].decode("latin-1"), "score": score,
+             "start_a": start_a, "start_b": start_b}
+        p += 2 * n
+        if index_lists:
+            a["idx_a"] = column_indices(a["aln_a"], start_a); a["idx_b"] = column_indices(a["aln_b"], start_b)
+        out[k] = a
     return out
 
 
-def allgather_alignments(mine, device=None):
-    """Every rank's traced hits on every rank: the sizes (8 bytes per rank), then the packed strings padded to the largest."""
+def allgather_alignments(mine, device=None, index_lists=True):
+    """Every rank's traced hits on every rank: the sizes (8 bytes per rank), then the packed strings padded to the largest.
+    index_lists = False leaves out the per-column index arrays of the received hits (column_indices rebuilds them)."""
     payload = pack_alignments(mine)
     sizes = _allgather_blocks(np.array([len(payload)], np.int64).view(np.uint8), device).view(np.int64).ravel()
     width = int(sizes.max())
@@ -309,7 +324,7 @@ def allgather_alignments(mine, device=None):
     rows = _allgather_blocks(block, device)
     out = {}
     for r, sz in zip(rows, sizes):
-        out.update(unpack_alignments(r[:int(sz)]))
+        out.update(unpack_alignments(r[:int(sz)], index_lists))
     return out
 
 
@@ -327,7 +342,7 @@ def search_scores(engine, query, db):
 
 
 def search(engine, query, db, topk=100, traceback=True, retain_all=False, rank=0, world_size=1, shard=None, device=None,
-           score_fn=None, ddb=None, gather_alignments=True, timings=None):
+           score_fn=None, ddb=None, gather_alignments=True, timings=None, index_lists=True):
     """Top-k hits of `query` in `db`.
 
     ddb: the rank's resident shard (DeviceDatabase(engine, db, rank, world_size)); built here when absent -- callers that
@@ -336,6 +351,8 @@ def search(engine, query, db, topk=100, traceback=True, retain_all=False, rank=0
     score_fn: replaces the device path by a host scoring function over (engine, query, shard Database) -- the CPU
     multi-process tests of the rank logic.
     timings: a dict that receives the wall seconds of the stages (scan, gather_hits, align, gather_alignments).
+    index_lists = False: hits traced by OTHER ranks come with aln_q / aln_t / start_q / start_t only (column_indices(aln, start)
+    gives idx_q / idx_t on demand) -- rebuilding 2 x 100 index arrays in Python costs more than the collective.
     Returns a list of dicts: idx, score, end_q, end_t (+ aln_q, aln_t, idx_q, idx_t when traceback).
     """
     import time
@@ -372,7 +389,7 @@ def search(engine, query, db, topk=100, traceback=True, retain_all=False, rank=0
         lap("align")
         if world_size > 1 and score_fn is None and gather_alignments:
             if not retain_all:                                # core alignments: strings only, two small collectives
-                mine = allgather_alignments(mine, device)
+                mine = allgather_alignments(mine, device, index_lists)
             else:
                 import torch.distributed as dist
                 parts = [None] * world_size
@@ -383,7 +400,11 @@ def search(engine, query, db, topk=100, traceback=True, retain_all=False, rank=0
             a = mine.get(k)
             if a is None:
                 continue
-            h.update(aln_q=a["aln_a"], aln_t=a["aln_b"], idx_q=a["idx_a"], idx_t=a["idx_b"])
+            h.update(aln_q=a["aln_a"], aln_t=a["aln_b"])
+            if "idx_a" in a:
+                h.update(idx_q=a["idx_a"], idx_t=a["idx_b"])
+            else:
+                h.update(start_q=a["start_a"], start_t=a["start_b"])
             if a["score"] != h["score"]:
                 raise SwbError(4, "scan and traceback disagree on subject %d" % h["idx"])
     if score_fn is None and own_ddb:
