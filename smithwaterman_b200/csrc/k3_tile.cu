@@ -240,6 +240,12 @@ k3_fill_kernel(const uint8_t *__restrict__ a_all, const uint8_t *__restrict__ b_
 }
 
 // ---- KT3: the walk ------------------------------------------------------------------------------------------------------
+// One BLOCK of KT3_WARPS warps per pair.  The walk is serial, but re-computing a tile is not part of the dependency: a tile's
+// codes follow from the stored borders alone.  Each round, warp w re-computes the w-th tile that a straight diagonal from the
+// cursor would visit (warp 0: the cursor's own tile, only the part above-left of the cursor; the others: whole tiles), then
+// warp 0 walks through as many of those tiles as the path really visits and the block starts the next round at the first
+// tile that was not predicted.  A walk alone spends ~85 % of its time re-computing; with 8 warps a round costs one
+// re-compute plus the walk through several tiles.
 #define KT3_WARPS 8
 
 struct KT3Smem {
@@ -247,6 +253,8 @@ struct KT3Smem {
     int4 left[K3_R + 2];            // (M, X, Y, raw E) of column c0, rows rtop .. cx; local mode: M, X, Y clamped as the reference's states
     int hm1[33], h0[33];            // H(rtop - 1, c0 + k), H(rtop, c0 + k), k = 0 .. 32
     int arow[K3_R + 2];             // score-table row offset of the residue of row rtop + r (no global load inside the wavefront)
+    int rtop, c0, tcx, tcy;         // the tile held: rows (rtop, tcx], columns (c0, tcy]; tcx < 0 = none
+    int fin[3];                     // (M, X, Y) of the tile's last cell (tcx, tcy): the start state of a global walk
 };
 
 // (M, X, Y, raw E, H) of a stored border cell (row, column 32 q + 32) -- or of a matrix boundary cell.
@@ -272,6 +280,98 @@ __device__ __forceinline__ void kt3_border_cell(const uint4 *cb, int nblk, int q
     if (MODE == SWB_LOCAL) { M = max(M, 0); X = max(X, 0); Y = max(Y, 0); }
 }
 
+struct KT3Ctx {
+    const uint8_t *a, *b;
+    int la, lb, nblk, n_pass, nl, o, e;
+    const uint4 *cb;
+    const unsigned *rb;
+    const int *mat_sh;
+    bool swp;
+};
+
+// Re-compute rows (rtop, hi_row] x columns (c0, hi_col] of the tile of (hi_row, hi_col) into S (one warp).
+template <int MODE>
+__device__ __forceinline__ void kt3_tile(KT3Smem &S, const KT3Ctx &C, int lane, int hi_row, int hi_col)
+{
+    const int o = C.o, e = C.e, open = C.o, nl = C.nl, lb = C.lb;
+    const int so = (MODE == SWB_GLOBAL) ? o : 0, se = (MODE == SWB_GLOBAL) ? e : 0, sent = 10 * o + 10 * e;
+    const bool swp = C.swp;
+    auto am = [swp](int m, int x, int y) -> unsigned { return (m >= x && m >= y) ? 0u : (swp ? ((y >= x) ? 2u : 1u) : ((x >= y) ? 1u : 2u)); };
+    const int q = (hi_col - 1) >> 5;
+    const int c0 = q << 5;
+    const int m = hi_row / K3_R;
+    const int rtop = m ? K3_R * m - 1 : 0;
+    const int nrows = hi_row - rtop, ncols = hi_col - c0;
+    __syncwarp();
+    if (lane == 0) { S.rtop = rtop; S.c0 = c0; S.tcx = hi_row; S.tcy = hi_col; }
+    for (int r = lane; r <= nrows; r += 32) {
+        int M, X, Y, Er, H;
+        kt3_border_cell<MODE>(C.cb, C.nblk, q - 1, rtop + r, c0, open, o, e, M, X, Y, Er, H);
+        S.left[r] = make_int4(M, X, Y, Er);
+        if (r == 0) S.h0[0] = H;
+        S.arow[r] = (rtop + r >= 1) ? (int)C.a[rtop + r - 1] * nl : 0;
+    }
+    if (lane == 0) {
+        int M, X, Y, Er, H = 0;
+        if (rtop > 0) kt3_border_cell<MODE>(C.cb, C.nblk, q - 1, rtop - 1, c0, open, o, e, M, X, Y, Er, H);
+        S.hm1[0] = H;
+    }
+    // top border row rtop of this lane's column j = c0 + 1 + lane
+    const int j = c0 + 1 + lane;
+    int Mu, Xu, Yu;
+    if (rtop == 0) {
+        const int ls = j * se + (so - se);
+        Mu = ls + sent; Xu = ls; Yu = ls + sent;
+        S.h0[lane + 1] = ls; S.hm1[lane + 1] = 0;
+    } else {
+        const unsigned *w = C.rb + ((size_t)(m - 1) * C.n_pass + q) * K3_ROWB_WORDS;
+        const int k = lane & 15;
+        int hm1, h0, f0;
+        if (lane < 16) { hm1 = lo16(w[k]) - open; h0 = lo16(w[16 + k]) - open; f0 = lo16(w[48 + k]); }
+        else { hm1 = hi16(w[16 + k]) - open; h0 = hi16(w[32 + k]) - open; f0 = hi16(w[64 + k]); }
+        S.hm1[lane + 1] = hm1; S.h0[lane + 1] = h0;
+        Yu = f0; Mu = 0; Xu = 0;
+    }
+    __syncwarp();
+    if (rtop > 0) {
+        const int sc = (j <= lb) ? C.mat_sh[(int)C.a[rtop - 1] * nl + (int)C.b[j - 1]] : 0;
+        Mu = S.hm1[lane] + sc;                               // M(rtop, j) = H(rtop-1, j-1) + s
+        int ev = S.left[0].w + (lane + 1) * e;               // X(rtop, j): the row recurrence from the stored E of column c0
+        for (int k = 0; k <= lane; ++k) ev = max(ev, S.h0[k] + o + (lane - k) * e);
+        Xu = ev;
+        if (MODE == SWB_LOCAL) { Mu = max(Mu, 0); Xu = max(Xu, 0); Yu = max(Yu, 0); }
+    }
+    // diagonal of this lane's first cell: cell (rtop, j - 1)
+    int dM = __shfl_up_sync(0xffffffffu, Mu, 1), dX = __shfl_up_sync(0xffffffffu, Xu, 1), dY = __shfl_up_sync(0xffffffffu, Yu, 1);
+    if (lane == 0) { const int4 v = S.left[0]; dM = v.x; dX = v.y; dY = v.z; }
+    int hd0 = __vimax3_s32(dM, dX, dY); unsigned ad0 = am(dM, dX, dY);
+    int lastM = 0, lastX = 0, lastY = 0;
+    const int bcode = (j <= lb) ? (int)C.b[j - 1] : 0;
+    const int n_steps = nrows + ncols - 1;
+    auto score_of = [&](int r) { return (lane < ncols && r >= 1 && r <= nrows) ? C.mat_sh[S.arow[r] + bcode] : 0; };
+    int s_nxt = score_of(1 - lane);
+    for (int t = 0; t < n_steps; ++t) {
+        const int r = t - lane + 1;                          // row of this lane in this step, 1 .. nrows
+        int tM = __shfl_up_sync(0xffffffffu, lastM, 1), tX = __shfl_up_sync(0xffffffffu, lastX, 1), tY = __shfl_up_sync(0xffffffffu, lastY, 1);
+        const int sc = s_nxt;
+        s_nxt = score_of(r + 1);                             // the next step's score: two shared-memory loads off the critical path
+        if (lane < ncols && r >= 1 && r <= nrows) {
+            if (lane == 0) { const int4 v = S.left[r]; tM = v.x; tX = v.y; tY = v.z; }
+            const int hd = hd0; const unsigned ad = ad0;
+            hd0 = __vimax3_s32(tM, tX, tY); ad0 = am(tM, tX, tY);
+            int mm, xx, yy; unsigned code;
+            kw_cell<MODE>(hd, ad, tM, tX, tY, Mu, Xu, Yu, sc, o, e, o, e, mm, xx, yy, code);
+            Mu = mm; Xu = xx; Yu = yy;
+            lastM = mm; lastX = xx; lastY = yy;
+            S.dir[r - 1][lane] = (uint8_t)code;
+        }
+    }
+    if (lane == ncols - 1) { S.fin[0] = Mu; S.fin[1] = Xu; S.fin[2] = Yu; }
+    __syncwarp();
+}
+
+struct KT3Walk { int cx, cy, st, n, score, done; };
+
 template <int MODE>
 __global__ void __launch_bounds__(KT3_WARPS * 32)
 kt3_walk_kernel(const uint8_t *__restrict__ a_all, const uint8_t *__restrict__ b_all, const K3Pair *__restrict__ pairs, int n_pairs,
@@ -280,146 +380,112 @@ kt3_walk_kernel(const uint8_t *__restrict__ a_all, const uint8_t *__restrict__ b
 {
     extern __shared__ int mat_sh[];
     __shared__ KT3Smem sm_all[KT3_WARPS];
+    __shared__ KT3Walk W;
     for (int k = threadIdx.x; k < nl * nl; k += blockDim.x) mat_sh[k] = mat[k];
-    __syncthreads();
     const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
-    const int p = blockIdx.x * KT3_WARPS + wib;
-    if (p >= n_pairs) return;
-    KT3Smem &S = sm_all[wib];
+    const int p = blockIdx.x;
     const K3Pair P = pairs[p];
     // Transposed pairs (P.swap): rows = b, columns = a.  The gap-state rules of the reference mirror each other (GAPINX prefers
     // X > M > Y where GAPINY prefers Y > M > X, SA.rs:172-211; local Y > M > X / X > M > Y, SA.rs:214-252) and so do the
     // boundaries (SA.rs:100-118), so the cell is the same with the state names X and Y exchanged; what is NOT symmetric is
     // the MATCH predecessor priority M > X > Y (SA.rs:139-158) and the start-state order M, X, Y (SA.rs:302-308): in the
     // transposed names they read M > Y > X.  The host exchanges the two column lists and the end cell back.
-    const bool swp = P.swap != 0;
-    const uint8_t *a = swp ? b_all + P.b_off : a_all + P.a_off, *b = swp ? a_all + P.a_off : b_all + P.b_off;
-    auto am = [swp](int m, int x, int y) -> unsigned { return (m >= x && m >= y) ? 0u : (swp ? ((y >= x) ? 2u : 1u) : ((x >= y) ? 1u : 2u)); };
+    KT3Ctx C;
+    C.swp = P.swap != 0;
+    C.a = C.swp ? b_all + P.b_off : a_all + P.a_off; C.b = C.swp ? a_all + P.a_off : b_all + P.b_off;
+    C.la = P.la; C.lb = P.lb; C.nblk = (P.la + 1 + 3) >> 2; C.n_pass = (P.lb + K1_STRIP - 1) / K1_STRIP;
+    C.nl = nl; C.o = o; C.e = e; C.cb = colb + P.colb_off; C.rb = rowb + P.rowb_off; C.mat_sh = mat_sh;
     const int la = P.la, lb = P.lb;
-    const int nblk = (la + 1 + 3) >> 2, n_pass = (lb + K1_STRIP - 1) / K1_STRIP;
-    const uint4 *cb = colb + P.colb_off;
-    const unsigned *rb = rowb + P.rowb_off;
-    const int open = o, sent = 10 * o + 10 * e;
-    const int so = (MODE == SWB_GLOBAL) ? o : 0, se = (MODE == SWB_GLOBAL) ? e : 0;
+    const int sent = 10 * o + 10 * e;
     int32_t *xa = idx_a + P.out_off, *xb = idx_b + P.out_off;
-
-    int cx = la, cy = lb, st = P.start_state, n = 0, score = P.score;
-    int rtop = 0, c0 = 0, tcx = -1, tcy = -1;           // the tile in shared memory: rows (rtop, tcx], columns (c0, tcy]
+    if (threadIdx.x == 0) { W.cx = la; W.cy = lb; W.st = P.start_state; W.n = 0; W.score = P.score; W.done = 0; }
+    if (lane == 0) sm_all[wib].tcx = -1;
     bool need_start = (MODE != SWB_LOCAL);
+    __syncthreads();
 
     for (;;) {
-        if (cx >= 1 && cy >= 1 && !(tcx >= 0 && cx > rtop && cx <= tcx && cy > c0 && cy <= tcy)) {
-            // ---- recompute the part of the tile of (cx, cy) that lies above-left of the cursor
-            const int q = (cy - 1) >> 5;
-            c0 = q << 5;
-            const int m = cx / K3_R;
-            rtop = m ? K3_R * m - 1 : 0;
-            const int nrows = cx - rtop, ncols = cy - c0;
-            tcx = cx; tcy = cy;
-            __syncwarp();
-            for (int r = lane; r <= nrows; r += 32) {
-                int M, X, Y, Er, H;
-                kt3_border_cell<MODE>(cb, nblk, q - 1, rtop + r, c0, open, o, e, M, X, Y, Er, H);
-                S.left[r] = make_int4(M, X, Y, Er);
-                if (r == 0) S.h0[0] = H;
-                S.arow[r] = (rtop + r >= 1) ? (int)a[rtop + r - 1] * nl : 0;
+        // ---- every warp: the w-th tile on the straight diagonal from the cursor
+        {
+            int x = W.cx, y = W.cy;
+            bool have = (x >= 1 && y >= 1);
+            for (int k = 0; k < wib && have; ++k) {
+                const int rt = (x / K3_R) ? K3_R * (x / K3_R) - 1 : 0, cc = ((y - 1) >> 5) << 5;
+                const int d = min(x - rt, y - cc);
+                x -= d; y -= d;
+                have = (x >= 1 && y >= 1);
             }
-            if (lane == 0) {
-                int M, X, Y, Er, H = 0;
-                if (rtop > 0) kt3_border_cell<MODE>(cb, nblk, q - 1, rtop - 1, c0, open, o, e, M, X, Y, Er, H);
-                S.hm1[0] = H;
-            }
-            // top border row rtop of this lane's column j = c0 + 1 + lane
-            const int j = c0 + 1 + lane;
-            int Mu, Xu, Yu;
-            if (rtop == 0) {
-                const int ls = j * se + (so - se);
-                Mu = ls + sent; Xu = ls; Yu = ls + sent;
-                S.h0[lane + 1] = ls; S.hm1[lane + 1] = 0;
-            } else {
-                const unsigned *w = rb + ((size_t)(m - 1) * n_pass + q) * K3_ROWB_WORDS;
-                const int k = lane & 15;
-                int hm1, h0, f0;
-                if (lane < 16) { hm1 = lo16(w[k]) - open; h0 = lo16(w[16 + k]) - open; f0 = lo16(w[48 + k]); }
-                else { hm1 = hi16(w[16 + k]) - open; h0 = hi16(w[32 + k]) - open; f0 = hi16(w[64 + k]); }
-                S.hm1[lane + 1] = hm1; S.h0[lane + 1] = h0;
-                Yu = f0; Mu = 0; Xu = 0;
-            }
-            __syncwarp();
-            if (rtop > 0) {
-                const int sc = (j <= lb) ? mat_sh[(int)a[rtop - 1] * nl + (int)b[j - 1]] : 0;
-                Mu = S.hm1[lane] + sc;                               // M(rtop, j) = H(rtop-1, j-1) + s
-                int ev = S.left[0].w + (lane + 1) * e;               // X(rtop, j): the row recurrence from the stored E of column c0
-                for (int k = 0; k <= lane; ++k) ev = max(ev, S.h0[k] + o + (lane - k) * e);
-                Xu = ev;
-                if (MODE == SWB_LOCAL) { Mu = max(Mu, 0); Xu = max(Xu, 0); Yu = max(Yu, 0); }
-            }
-            // diagonal of this lane's first cell: cell (rtop, j - 1)
-            int dM = __shfl_up_sync(0xffffffffu, Mu, 1), dX = __shfl_up_sync(0xffffffffu, Xu, 1), dY = __shfl_up_sync(0xffffffffu, Yu, 1);
-            if (lane == 0) { const int4 v = S.left[0]; dM = v.x; dX = v.y; dY = v.z; }
-            int hd0 = __vimax3_s32(dM, dX, dY); unsigned ad0 = am(dM, dX, dY);
-            int lastM = 0, lastX = 0, lastY = 0;
-            const int bcode = (j <= lb) ? (int)b[j - 1] : 0;
-            const int n_steps = nrows + ncols - 1;
-            auto score_of = [&](int r) { return (lane < ncols && r >= 1 && r <= nrows) ? mat_sh[S.arow[r] + bcode] : 0; };
-            int s_nxt = score_of(1 - lane);
-            for (int t = 0; t < n_steps; ++t) {
-                const int r = t - lane + 1;                          // row of this lane in this step, 1 .. nrows
-                int tM = __shfl_up_sync(0xffffffffu, lastM, 1), tX = __shfl_up_sync(0xffffffffu, lastX, 1), tY = __shfl_up_sync(0xffffffffu, lastY, 1);
-                const int s = s_nxt;
-                s_nxt = score_of(r + 1);                             // the next step's score: two shared-memory loads off the critical path
-                if (lane < ncols && r >= 1 && r <= nrows) {
-                    if (lane == 0) { const int4 v = S.left[r]; tM = v.x; tX = v.y; tY = v.z; }
-                    const int hd = hd0; const unsigned ad = ad0;
-                    hd0 = __vimax3_s32(tM, tX, tY); ad0 = am(tM, tX, tY);
-                    int mm, xx, yy; unsigned code;
-                    kw_cell<MODE>(hd, ad, tM, tX, tY, Mu, Xu, Yu, s, o, e, o, e, mm, xx, yy, code);
-                    Mu = mm; Xu = xx; Yu = yy;
-                    lastM = mm; lastX = xx; lastY = yy;
-                    S.dir[r - 1][lane] = (uint8_t)code;
+            if (have) {
+                int hi_row = x, hi_col = y;
+                if (wib > 0) {                                       // a predicted tile: all of it (the entry point is not known yet)
+                    const int m = x / K3_R;
+                    hi_row = min(m ? K3_R * m + K3_R - 1 : K3_R - 1, la); hi_col = min((((y - 1) >> 5) << 5) + 32, lb);
                 }
+                kt3_tile<MODE>(sm_all[wib], C, lane, hi_row, hi_col);
+            } else if (lane == 0) sm_all[wib].tcx = -1;
+        }
+        __syncthreads();
+        // ---- warp 0: walk through the tiles at hand (backtrack, SA.rs:346-383); the same on every lane, lane 0 writes
+        if (wib == 0) {
+            int cx = W.cx, cy = W.cy, st = W.st, n = W.n, score = W.score, done = 0;
+            if (need_start && cx >= 1 && cy >= 1) {                  // cell (la, lb): first strict maximum in the order M, X, Y (SA.rs:302-308)
+                const int fm = sm_all[0].fin[0], fx = sm_all[0].fin[1], fy = sm_all[0].fin[2];
+                score = fm; st = 0;
+                if (!C.swp) { if (fx > score) { score = fx; st = 1; } if (fy > score) { score = fy; st = 2; } }
+                else { if (fy > score) { score = fy; st = 2; } if (fx > score) { score = fx; st = 1; } }
+            }
+            int cur = 0;
+            for (;;) {
+                unsigned prev;
+                if (cx >= 1 && cy >= 1) {
+                    const KT3Smem *T = &sm_all[cur];
+                    if (!(T->tcx >= 0 && cx > T->rtop && cx <= T->tcx && cy > T->c0 && cy <= T->tcy)) {
+                        int found = -1;
+#pragma unroll
+                        for (int k = 0; k < KT3_WARPS; ++k) {
+                            const KT3Smem *Q = &sm_all[k];
+                            if (found < 0 && Q->tcx >= 0 && cx > Q->rtop && cx <= Q->tcx && cy > Q->c0 && cy <= Q->tcy) found = k;
+                        }
+                        if (found < 0) break;                        // not predicted: next round
+                        cur = found; T = &sm_all[cur];
+                    }
+                    prev = ((unsigned)T->dir[cx - T->rtop - 1][cy - T->c0 - 1] >> (2 * st)) & 3u;
+                }
+                else if (cx == 0 && cy == 0) prev = 0;
+                else if (cx == 0) {                                  // row 0: prev = GAPINX for all states (SA.rs:105-107)
+                    prev = 1;
+                    if (MODE == SWB_LOCAL && (st == 1 || sent == 0)) prev = 3;
+                } else {                                             // column 0: prev = GAPINY (SA.rs:114-116)
+                    prev = 2;
+                    if (MODE == SWB_LOCAL && (st == 2 || sent == 0)) prev = 3;
+                }
+                if (MODE == SWB_LOCAL && prev == 3) { done = 1; break; }
+                if (st == 0) {
+                    if (cx == 0 || cy == 0) { n = -2; done = 1; break; }
+                    if (lane == 0) { xa[n] = cx - 1; xb[n] = cy - 1; }
+                    ++n; --cx; --cy;
+                } else if (st == 1) {
+                    if (cy == 0) { n = -2; done = 1; break; }
+                    if (lane == 0) { xa[n] = -1; xb[n] = cy - 1; }
+                    ++n; --cy;
+                } else {
+                    if (cx == 0) { n = -2; done = 1; break; }
+                    if (lane == 0) { xa[n] = cx - 1; xb[n] = -1; }
+                    ++n; --cx;
+                }
+                if (cx == 0 && cy == 0) { done = 1; break; }
+                st = (int)prev;
             }
             __syncwarp();
-            if (need_start) {                                        // cell (la, lb): first strict maximum in the order M, X, Y (SA.rs:302-308)
-                const int src = ncols - 1;
-                const int fm = __shfl_sync(0xffffffffu, Mu, src), fx = __shfl_sync(0xffffffffu, Xu, src), fy = __shfl_sync(0xffffffffu, Yu, src);
-                score = fm; st = 0;
-                if (!swp) { if (fx > score) { score = fx; st = 1; } if (fy > score) { score = fy; st = 2; } }
-                else { if (fy > score) { score = fy; st = 2; } if (fx > score) { score = fx; st = 1; } }
-                need_start = false;
-            }
+            if (lane == 0) { W.cx = cx; W.cy = cy; W.st = st; W.n = n; W.score = score; W.done = done; }
         }
-        // ---- one step of the walk (backtrack, SA.rs:346-383), the same on every lane; lane 0 writes
-        unsigned prev;
-        if (cx >= 1 && cy >= 1) prev = ((unsigned)S.dir[cx - rtop - 1][cy - c0 - 1] >> (2 * st)) & 3u;
-        else if (cx == 0 && cy == 0) prev = 0;
-        else if (cx == 0) {                                          // row 0: prev = GAPINX for all states (SA.rs:105-107)
-            prev = 1;
-            if (MODE == SWB_LOCAL && (st == 1 || sent == 0)) prev = 3;
-        } else {                                                     // column 0: prev = GAPINY (SA.rs:114-116)
-            prev = 2;
-            if (MODE == SWB_LOCAL && (st == 2 || sent == 0)) prev = 3;
-        }
-        if (MODE == SWB_LOCAL && prev == 3) break;
-        if (st == 0) {
-            if (cx == 0 || cy == 0) { n = -2; break; }
-            if (lane == 0) { xa[n] = cx - 1; xb[n] = cy - 1; }
-            ++n; --cx; --cy;
-        } else if (st == 1) {
-            if (cy == 0) { n = -2; break; }
-            if (lane == 0) { xa[n] = -1; xb[n] = cy - 1; }
-            ++n; --cy;
-        } else {
-            if (cx == 0) { n = -2; break; }
-            if (lane == 0) { xa[n] = cx - 1; xb[n] = -1; }
-            ++n; --cx;
-        }
-        if (cx == 0 && cy == 0) break;
-        st = (int)prev;
+        need_start = false;
+        __syncthreads();
+        if (W.done) break;
+        __syncthreads();                                             // everybody has read the cursor before warp 0 may write it again
     }
-    if (lane == 0) {
-        ncols_out[p] = n;
-        KWResult R; R.score = score; R.end_i = la; R.end_j = lb; R.state = P.start_state;
+    if (threadIdx.x == 0) {
+        ncols_out[p] = W.n;
+        KWResult R; R.score = W.score; R.end_i = la; R.end_j = lb; R.state = P.start_state;
         res[p] = R;
     }
 }
@@ -471,7 +537,7 @@ cudaError_t k3_launch(const swb_engine *e, const uint8_t *d_a, const uint8_t *d_
     }
     const int slots = K3_WARPS / team;
     const int fill_blocks = std::min(e->sm_count, (n_pairs + slots - 1) / slots);
-    const int walk_blocks = (n_pairs + KT3_WARPS - 1) / KT3_WARPS;
+    const int walk_blocks = n_pairs;                                   // one block of KT3_WARPS warps per pair
     const size_t wsmem = (size_t)nl * nl * sizeof(int);
     if (e->mode == SWB_LOCAL) {
         if ((err = cudaFuncSetAttribute(k3_fill_kernel<SWB_LOCAL>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)) != cudaSuccess) return err;
