@@ -17,6 +17,7 @@
 // global mode reads the start state off the recomputed cell (la, lb).  Glocal stays on the direction-byte path.
 #include <algorithm>
 #include <cstdlib>
+#include <cstdio>
 
 #include "swb_internal.h"
 #include "k1_common.cuh"
@@ -246,7 +247,8 @@ k3_fill_kernel(const uint8_t *__restrict__ a_all, const uint8_t *__restrict__ b_
 // warp 0 walks through as many of those tiles as the path really visits and the block starts the next round at the first
 // tile that was not predicted.  A walk alone spends ~85 % of its time re-computing; with 8 warps a round costs one
 // re-compute plus the walk through several tiles.
-#define KT3_WARPS 8
+#define KT3_WARPS 8                   // default; SWB_KT3_WARPS (1..16) overrides at launch
+#define KT3_MAX_WARPS 16
 
 struct KT3Smem {
     uint8_t dir[K3_R][32];          // predecessor codes of the recomputed part of the tile
@@ -373,14 +375,15 @@ __device__ __forceinline__ void kt3_tile(KT3Smem &S, const KT3Ctx &C, int lane, 
 struct KT3Walk { int cx, cy, st, n, score, done; };
 
 template <int MODE>
-__global__ void __launch_bounds__(KT3_WARPS * 32)
+__global__ void __launch_bounds__(KT3_MAX_WARPS * 32, 2)
 kt3_walk_kernel(const uint8_t *__restrict__ a_all, const uint8_t *__restrict__ b_all, const K3Pair *__restrict__ pairs, int n_pairs,
                 const int32_t *__restrict__ mat, int nl, int o, int e, const uint4 *__restrict__ colb, const unsigned *__restrict__ rowb,
                 int32_t *__restrict__ idx_a, int32_t *__restrict__ idx_b, int32_t *__restrict__ ncols_out, KWResult *__restrict__ res)
 {
-    extern __shared__ int mat_sh[];
-    __shared__ KT3Smem sm_all[KT3_WARPS];
+    extern __shared__ __align__(16) int mat_sh[];                    // nl * nl scores (rounded up to 16 bytes), then one KT3Smem per warp
     __shared__ KT3Walk W;
+    const int n_warps = blockDim.x >> 5;
+    KT3Smem *sm_all = reinterpret_cast<KT3Smem *>(mat_sh + ((nl * nl + 3) & ~3));
     for (int k = threadIdx.x; k < nl * nl; k += blockDim.x) mat_sh[k] = mat[k];
     const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
     const int p = blockIdx.x;
@@ -401,6 +404,7 @@ kt3_walk_kernel(const uint8_t *__restrict__ a_all, const uint8_t *__restrict__ b
     if (threadIdx.x == 0) { W.cx = la; W.cy = lb; W.st = P.start_state; W.n = 0; W.score = P.score; W.done = 0; }
     if (lane == 0) sm_all[wib].tcx = -1;
     bool need_start = (MODE != SWB_LOCAL);
+    int va = 0, vb = 0;                                              // warp 0: lane (n & 31) holds column n of the lists (one coalesced store per 32 columns)
     __syncthreads();
 
     for (;;) {
@@ -433,48 +437,51 @@ kt3_walk_kernel(const uint8_t *__restrict__ a_all, const uint8_t *__restrict__ b
                 if (!C.swp) { if (fx > score) { score = fx; st = 1; } if (fy > score) { score = fy; st = 2; } }
                 else { if (fy > score) { score = fy; st = 2; } if (fx > score) { score = fx; st = 1; } }
             }
-            int cur = 0;
+            // Inside a tile the walk is a tight loop: one code byte per step at a linear position, no boundary, panic or end
+            // tests (a tile's cells have cx, cy >= 1); everything else -- changing tiles, the matrix boundary, the end of the
+            // walk -- is the slow path around it.
             for (;;) {
-                unsigned prev;
                 if (cx >= 1 && cy >= 1) {
-                    const KT3Smem *T = &sm_all[cur];
-                    if (!(T->tcx >= 0 && cx > T->rtop && cx <= T->tcx && cy > T->c0 && cy <= T->tcy)) {
-                        int found = -1;
-#pragma unroll
-                        for (int k = 0; k < KT3_WARPS; ++k) {
-                            const KT3Smem *Q = &sm_all[k];
-                            if (found < 0 && Q->tcx >= 0 && cx > Q->rtop && cx <= Q->tcx && cy > Q->c0 && cy <= Q->tcy) found = k;
-                        }
-                        if (found < 0) break;                        // not predicted: next round
-                        cur = found; T = &sm_all[cur];
+                    int found = -1;
+                    for (int k = 0; k < n_warps; ++k) {
+                        const KT3Smem *Q = &sm_all[k];
+                        if (found < 0 && Q->tcx >= 0 && cx > Q->rtop && cx <= Q->tcx && cy > Q->c0 && cy <= Q->tcy) found = k;
                     }
-                    prev = ((unsigned)T->dir[cx - T->rtop - 1][cy - T->c0 - 1] >> (2 * st)) & 3u;
+                    if (found < 0) break;                            // not predicted: next round
+                    const KT3Smem *T = &sm_all[found];
+                    const int t_rtop = T->rtop, t_c0 = T->c0;
+                    const uint8_t *t_dir = &T->dir[0][0];
+                    int pos = (cx - t_rtop - 1) * 32 + (cy - t_c0 - 1);
+                    bool stop = false;
+                    do {
+                        const unsigned prev = ((unsigned)t_dir[pos] >> (2 * st)) & 3u;
+                        if (MODE == SWB_LOCAL && prev == 3) { stop = true; break; }
+                        const int dx = (st != 1), dy = (st != 2);
+                        if (lane == (n & 31)) { va = dx ? cx - 1 : -1; vb = dy ? cy - 1 : -1; }
+                        ++n;
+                        if ((n & 31) == 0) { xa[n - 32 + lane] = va; xb[n - 32 + lane] = vb; }
+                        cx -= dx; cy -= dy; pos -= dx * 32 + dy;
+                        st = (int)prev;
+                    } while (cx > t_rtop && cy > t_c0);
+                    if (stop) { done = 1; break; }
+                    if (cx == 0 && cy == 0) { done = 1; break; }
+                    continue;
                 }
-                else if (cx == 0 && cy == 0) prev = 0;
-                else if (cx == 0) {                                  // row 0: prev = GAPINX for all states (SA.rs:105-107)
-                    prev = 1;
-                    if (MODE == SWB_LOCAL && (st == 1 || sent == 0)) prev = 3;
-                } else {                                             // column 0: prev = GAPINY (SA.rs:114-116)
-                    prev = 2;
-                    if (MODE == SWB_LOCAL && (st == 2 || sent == 0)) prev = 3;
-                }
+                // on the matrix boundary (SA.rs:105-116): row 0 -> GAPINX, column 0 -> GAPINY for all states
+                unsigned prev;
+                if (cx == 0 && cy == 0) prev = 0;
+                else if (cx == 0) { prev = 1; if (MODE == SWB_LOCAL && (st == 1 || sent == 0)) prev = 3; }
+                else { prev = 2; if (MODE == SWB_LOCAL && (st == 2 || sent == 0)) prev = 3; }
                 if (MODE == SWB_LOCAL && prev == 3) { done = 1; break; }
-                if (st == 0) {
-                    if (cx == 0 || cy == 0) { n = -2; done = 1; break; }
-                    if (lane == 0) { xa[n] = cx - 1; xb[n] = cy - 1; }
-                    ++n; --cx; --cy;
-                } else if (st == 1) {
-                    if (cy == 0) { n = -2; done = 1; break; }
-                    if (lane == 0) { xa[n] = -1; xb[n] = cy - 1; }
-                    ++n; --cy;
-                } else {
-                    if (cx == 0) { n = -2; done = 1; break; }
-                    if (lane == 0) { xa[n] = cx - 1; xb[n] = -1; }
-                    ++n; --cx;
-                }
+                if ((st != 2 && cy == 0) || (st != 1 && cx == 0)) { n = -2; done = 1; break; }   // the reference's panic cases (SA.rs:360-371)
+                if (lane == (n & 31)) { va = (st == 1) ? -1 : cx - 1; vb = (st == 2) ? -1 : cy - 1; }
+                ++n;
+                if ((n & 31) == 0) { xa[n - 32 + lane] = va; xb[n - 32 + lane] = vb; }
+                cx -= (st != 1); cy -= (st != 2);
                 if (cx == 0 && cy == 0) { done = 1; break; }
                 st = (int)prev;
             }
+            if (n > 0 && lane < (n & 31)) { xa[(n & ~31) + lane] = va; xb[(n & ~31) + lane] = vb; }   // the columns of the last, partial group
             __syncwarp();
             if (lane == 0) { W.cx = cx; W.cy = cy; W.st = st; W.n = n; W.score = score; W.done = done; }
         }
@@ -538,16 +545,20 @@ cudaError_t k3_launch(const swb_engine *e, const uint8_t *d_a, const uint8_t *d_
     const int slots = K3_WARPS / team;
     const int fill_blocks = std::min(e->sm_count, (n_pairs + slots - 1) / slots);
     const int walk_blocks = n_pairs;                                   // one block of KT3_WARPS warps per pair
-    const size_t wsmem = (size_t)nl * nl * sizeof(int);
+    int kt3_warps = KT3_WARPS;
+    if (const char *f = getenv("SWB_KT3_WARPS")) { const int v = atoi(f); if (v >= 1 && v <= KT3_MAX_WARPS) kt3_warps = v; }
+    const size_t wsmem = (size_t)((nl * nl + 3) & ~3) * sizeof(int) + (size_t)kt3_warps * sizeof(KT3Smem);
     if (e->mode == SWB_LOCAL) {
         if ((err = cudaFuncSetAttribute(k3_fill_kernel<SWB_LOCAL>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)) != cudaSuccess) return err;
+        if ((err = cudaFuncSetAttribute(kt3_walk_kernel<SWB_LOCAL>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)wsmem)) != cudaSuccess) return err;
         k3_fill_kernel<SWB_LOCAL><<<fill_blocks, K3_WARPS * 32, smem, st>>>(d_a, d_b, d_pairs, n_pairs, e->d_mat, nl, e->o, e->e, d_colb, d_rowb, d_counter, team);
-        kt3_walk_kernel<SWB_LOCAL><<<walk_blocks, KT3_WARPS * 32, wsmem, st>>>(d_a, d_b, d_pairs, n_pairs, e->d_mat, nl, e->o, e->e, d_colb, d_rowb,
+        kt3_walk_kernel<SWB_LOCAL><<<walk_blocks, kt3_warps * 32, wsmem, st>>>(d_a, d_b, d_pairs, n_pairs, e->d_mat, nl, e->o, e->e, d_colb, d_rowb,
                                                                               d_idx_a, d_idx_b, d_ncols, d_res);
     } else {
         if ((err = cudaFuncSetAttribute(k3_fill_kernel<SWB_GLOBAL>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)) != cudaSuccess) return err;
+        if ((err = cudaFuncSetAttribute(kt3_walk_kernel<SWB_GLOBAL>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)wsmem)) != cudaSuccess) return err;
         k3_fill_kernel<SWB_GLOBAL><<<fill_blocks, K3_WARPS * 32, smem, st>>>(d_a, d_b, d_pairs, n_pairs, e->d_mat, nl, e->o, e->e, d_colb, d_rowb, d_counter, team);
-        kt3_walk_kernel<SWB_GLOBAL><<<walk_blocks, KT3_WARPS * 32, wsmem, st>>>(d_a, d_b, d_pairs, n_pairs, e->d_mat, nl, e->o, e->e, d_colb, d_rowb,
+        kt3_walk_kernel<SWB_GLOBAL><<<walk_blocks, kt3_warps * 32, wsmem, st>>>(d_a, d_b, d_pairs, n_pairs, e->d_mat, nl, e->o, e->e, d_colb, d_rowb,
                                                                                d_idx_a, d_idx_b, d_ncols, d_res);
     }
     return cudaGetLastError();
