@@ -136,7 +136,7 @@ def search_block(swb, local_rank, rank, world, roof_gcups, hbm_peak, steps=3):
     stage = {}
 
     def one(tb):
-        return S.search(eng, q, db, topk=100, traceback=tb, rank=rank, world_size=world, device=dev, ddb=ddb, timings=stage)
+        return S.search(eng, q, db, topk=100, traceback=tb, rank=rank, world_size=world, device=dev, ddb=ddb, timings=stage, index_lists=False)
 
     hits = one(True)                                          # warm-up: scratch growth, NCCL channels
     one(False)
@@ -150,7 +150,7 @@ def search_block(swb, local_rank, rank, world, roof_gcups, hbm_peak, steps=3):
         barrier(); a2 = time.perf_counter()
         hits = one(True)
         tb_ms.append(eng.stats()["kernel_ms"])
-        stages.append([stage.get(k, 0.0) for k in ("scan", "gather_hits", "align", "gather_alignments")])
+        stages.append([stage.get(k, 0.0) for k in ("scan", "gather_hits", "align", "gather_alignments")] + list(getattr(ddb, "last_align_s", (0.0, 0.0))))
         barrier(); a3 = time.perf_counter()
         t_score.append(a2 - a1); t_full.append(a3 - a2)
     idx = S.native_shard_indices(db.offsets, rank, world)
@@ -183,7 +183,8 @@ def search_block(swb, local_rank, rank, world, roof_gcups, hbm_peak, steps=3):
             "score_plus_traceback_s": tm[1].item(), "gcups_with_traceback": cells / tm[1].item() / 1e9,
             "traceback_device_ms_max_rank": tm[4].item(), "hits_traced_by_this_rank": int(owned), "hits_traced_total": int(ts[6].item()),
             "stage_wall_ms_max_rank": {"scan": tm[7].item() * 1e3, "gather_hits": tm[8].item() * 1e3, "align_own_hits": tm[9].item() * 1e3,
-                                       "gather_alignments": tm[10].item() * 1e3},
+                                       "gather_alignments": tm[10].item() * 1e3, "align_c_call": tm[11].item() * 1e3,
+                                       "align_python_unpack": tm[12].item() * 1e3},
             "per_gpu": {"gcups_scan": per_gpu_scan, "frac_of_dpx_roof": per_gpu_scan / roof_gcups,
                         "hbm_gbs_streamed_shard": tm[5].item() / (tm[2].item() * 1e-3) / 1e9, "hbm_peak_gbs": hbm_peak,
                         "hbm_frac": tm[5].item() / (tm[2].item() * 1e-3) / 1e9 / hbm_peak},

@@ -264,9 +264,10 @@ class SequenceAlignment:
     @staticmethod
     def _unpack(out):
         n = out.n_cols
+        # (one string_at per list: np.ctypeslib.as_array builds a ctypes array type per call, ~10x slower for short lists)
         return {"score": float(out.score), "end_a": out.end_a, "end_b": out.end_b,
-                "idx_a": np.ctypeslib.as_array(out.idx_a, (n,)).copy() if n else np.zeros(0, np.int64),
-                "idx_b": np.ctypeslib.as_array(out.idx_b, (n,)).copy() if n else np.zeros(0, np.int64),
+                "idx_a": np.frombuffer(ctypes.string_at(out.idx_a, 8 * n), np.int64) if n else np.zeros(0, np.int64),
+                "idx_b": np.frombuffer(ctypes.string_at(out.idx_b, 8 * n), np.int64) if n else np.zeros(0, np.int64),
                 "aln_a": ctypes.string_at(out.aln_a, out.aln_len).decode("latin-1"),
                 "aln_b": ctypes.string_at(out.aln_b, out.aln_len).decode("latin-1")}
 

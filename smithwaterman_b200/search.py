@@ -205,13 +205,18 @@ class DeviceDatabase:
         n = len(hits)
         outs = (_lib.Alignment * max(n, 1))()
         owned = np.zeros(max(n, 1), np.int32)
+        import time
+        t0 = time.perf_counter()
         self.engine._check(self.engine.L.swb_search_align(self.engine._h, bytes(q), len(q), self.h, hits.ctypes.data, n,
                                                           1 if retain_all else 0, outs, owned.ctypes.data))
+        t1 = time.perf_counter()
         try:
             return {k: SequenceAlignment._unpack(outs[k]) for k in range(n) if owned[k]}
         finally:
             for k in range(n):
-                self.engine.L.swb_alignment_free(ctypes.byref(outs[k]))
+                if owned[k]:
+                    self.engine.L.swb_alignment_free(ctypes.byref(outs[k]))
+            self.last_align_s = (t1 - t0, time.perf_counter() - t1)      # (the C call, copying the results into Python objects)
 
     def free(self):
         if self.h is not None and self.h.value:
