@@ -243,7 +243,7 @@ static int align_jobs_k3(swb_engine *e, const uint8_t *d_a, const uint8_t *d_b, 
             rw = (rw + 3) / 4 * 4;
             if (!hp.empty() && (colb + c4) * 16 + (rowb + rw) * 4 > budget) break;
             K3Pair P; P.a_off = J.a_off; P.b_off = J.b_off; P.la = la_k; P.lb = lb_k; P.colb_off = colb; P.rowb_off = rowb; P.out_off = out_total;
-            P.start_state = 0; P.score = J.known_score == INT32_MIN ? 0 : J.known_score; P.swap = swp ? 1 : 0; P.pad_ = 0;
+            P.start_state = 0; P.score = J.known_score == INT32_MIN ? 0 : J.known_score; P.swap = swp ? 1 : 0; P.pad_ = 0; P.cx0 = 0; P.cy0 = 0;
             hp.push_back(P);
             max_sweeps = std::max(max_sweeps, (lb_k + 1023) / 1024);
             colb += c4; rowb += rw; out_total += (int64_t)J.la + J.lb + 1;
@@ -309,6 +309,80 @@ static int align_jobs_k3(swb_engine *e, const uint8_t *d_a, const uint8_t *d_b, 
     return SWB_OK;
 }
 
+// One long pair through the int32 tile path (K3W fill over the whole GPU + KT3 walk): the border store (0.5 B per cell) and
+// the row checkpoints live in the engine's direction-byte arena.
+static int64_t k3w_min_cells()
+{
+    if (getenv("SWB_NO_K3W")) return INT64_MAX;
+    if (const char *f = getenv("SWB_K3W_MIN")) { const long long v = atoll(f); if (v >= 1) return v; }    // the tests send small pairs here
+    return 400000000ll;                        // below ~2e4 x 2e4 a batch of pairs keeps the GPU busier on the direction-byte path
+}
+static bool k3w_wanted(const swb_engine *e, const AlnJob &J, int64_t budget)
+{
+    if (e->mode == SWB_GLOCAL || e->o > e->e || J.la < 1 || J.lb < 1) return false;
+    if ((int64_t)J.la * J.lb < k3w_min_cells()) return false;
+    int64_t c4, rw, sc; k3w_sizes(J.la, J.lb, &c4, &rw, &sc);
+    return c4 * 16 + rw * 4 + 256 <= budget;
+}
+static int align_pair_k3w(swb_engine *e, const uint8_t *d_a, const uint8_t *d_b, const AlnJob &J, bool retain_all, swb_alignment *out)
+{
+    const float inv = 1.0f / (float)e->scale;
+    const bool dyadic = (e->scale & (e->scale - 1)) == 0;
+    auto to_f = [&](int64_t s) { return dyadic ? (float)s * inv : (float)((double)s / e->scale); };
+    int64_t c4, rw, sc; k3w_sizes(J.la, J.lb, &c4, &rw, &sc);
+    const size_t colb_bytes = ((size_t)c4 * 16 + 255) & ~(size_t)255, need = colb_bytes + (size_t)rw * 4 + 64;
+    if (need > e->dir_bytes) {                                  // engine-owned arena, grown on demand and kept
+        CUDA_TRY(e, cudaStreamSynchronize(e->stream));
+        if (e->d_dir) cudaFree(e->d_dir);
+        e->d_dir = nullptr; e->dir_bytes = 0;
+        CUDA_TRY(e, cudaMalloc(&e->d_dir, need));
+        e->dir_bytes = need;
+    }
+    uint4 *d_colb = reinterpret_cast<uint4 *>(e->d_dir);
+    unsigned *d_rowb = reinterpret_cast<unsigned *>((char *)e->d_dir + colb_bytes);
+    const int64_t out_total = (int64_t)J.la + J.lb + 1;
+    K3Pair P; P.a_off = J.a_off; P.b_off = J.b_off; P.la = J.la; P.lb = J.lb; P.colb_off = 0; P.rowb_off = 0; P.out_off = 0;
+    P.start_state = 0; P.score = 0; P.swap = 0; P.pad_ = 0; P.cx0 = 0; P.cy0 = 0;
+    DevBuf d_pair, d_res, d_scr, d_xa, d_xb, d_nc;
+    CUDA_TRY(e, d_pair.alloc(sizeof(K3Pair), e->stream)); CUDA_TRY(e, d_res.alloc(sizeof(KWResult), e->stream));
+    CUDA_TRY(e, d_scr.alloc((size_t)sc * sizeof(int), e->stream));
+    CUDA_TRY(e, d_xa.alloc(out_total * sizeof(int32_t), e->stream)); CUDA_TRY(e, d_xb.alloc(out_total * sizeof(int32_t), e->stream));
+    CUDA_TRY(e, d_nc.alloc(sizeof(int32_t), e->stream));
+    CUDA_TRY(e, cudaMemcpyAsync(d_pair.p, &P, sizeof(K3Pair), cudaMemcpyHostToDevice, e->stream));
+    CUDA_TRY(e, cudaEventRecord(e->ev0, e->stream));
+    CUDA_TRY(e, k3w_launch(e, d_a, d_b, d_pair.as<K3Pair>(), P, d_colb, d_rowb, d_scr.as<int>(), d_xa.as<int32_t>(), d_xb.as<int32_t>(),
+                           d_nc.as<int32_t>(), d_res.as<KWResult>(), e->stream));
+    CUDA_TRY(e, cudaEventRecord(e->ev1, e->stream));
+    const size_t tb_need = sizeof(KWResult) + sizeof(int32_t) + 2 * (size_t)out_total * sizeof(int32_t) + 64;
+    if (tb_need > e->tb_bytes) {
+        if (e->h_tb) cudaFreeHost(e->h_tb);
+        e->h_tb = nullptr; e->tb_bytes = 0;
+        CUDA_TRY(e, cudaMallocHost(&e->h_tb, tb_need));
+        e->tb_bytes = tb_need;
+    }
+    KWResult *hr = (KWResult *)e->h_tb;
+    int32_t *hnc = (int32_t *)(hr + 1), *hxa = hnc + 1, *hxb = hxa + out_total;
+    CUDA_TRY(e, cudaMemcpyAsync(hr, d_res.p, sizeof(KWResult), cudaMemcpyDeviceToHost, e->stream));
+    CUDA_TRY(e, cudaMemcpyAsync(hnc, d_nc.p, sizeof(int32_t), cudaMemcpyDeviceToHost, e->stream));
+    CUDA_TRY(e, cudaStreamSynchronize(e->stream));
+    const int64_t nc = hnc[0];
+    if (nc < 0) { e->err = "traceback left the matrix (the reference panics here, SA.rs:360-371)"; return SWB_ERR_EMPTY; }
+    if (nc > 0) {                                               // the column lists: only the part that was written
+        CUDA_TRY(e, cudaMemcpyAsync(hxa, d_xa.p, nc * sizeof(int32_t), cudaMemcpyDeviceToHost, e->stream));
+        CUDA_TRY(e, cudaMemcpyAsync(hxb, d_xb.p, nc * sizeof(int32_t), cudaMemcpyDeviceToHost, e->stream));
+        CUDA_TRY(e, cudaStreamSynchronize(e->stream));
+    }
+    float ms = 0; cudaEventElapsedTime(&ms, e->ev0, e->ev1);
+    e->stats.kernel_ms += ms; e->stats.launches += 3; e->stats.k3_pairs += 1;
+    e->stats.d2h_bytes += 8.0 * nc + sizeof(KWResult) + 4;
+    std::vector<int64_t> xa(nc), xb(nc);
+    for (int64_t c = 0; c < nc; ++c) { xa[c] = hxa[nc - 1 - c]; xb[c] = hxb[nc - 1 - c]; }       // reverse (SA.rs:384-385)
+    std::string ra, rb;
+    inflate(J.ra, J.la_full, J.rb, J.lb_full, xa.data(), xb.data(), nc, e->mode, retain_all, ra, rb);
+    if (fill_out(out, to_f(hr[0].score), hr[0].end_i, hr[0].end_j, xa, xb, ra, rb) != SWB_OK) { e->err = "out of memory"; return SWB_ERR_NOMEM; }
+    return SWB_OK;
+}
+
 // Device core of the traceback path: KW with direction bytes + KT for the jobs whose bytes fit the budget (chunked),
 // checkpointed recompute for the others.  outs: full alignments; souts: the counting form.  Exactly one is non-null.
 int align_jobs_device(swb_engine *e, const uint8_t *d_a, const uint8_t *d_b, const std::vector<AlnJob> &jobs, bool retain_all,
@@ -334,6 +408,12 @@ int align_jobs_device(swb_engine *e, const uint8_t *d_a, const uint8_t *d_b, con
     }
     std::vector<char> is_packed(jobs.size(), 0);
     for (size_t w : packed) is_packed[w] = 1;
+    for (size_t w = 0; w < jobs.size() && outs && !d_pssm; ++w) {       // long pairs outside the s16 range: the int32 tile path, one at a time
+        if (is_packed[w] || !k3w_wanted(e, jobs[w], budget)) continue;
+        int rc = align_pair_k3w(e, d_a, d_b, jobs[w], retain_all, &outs[jobs[w].out]);
+        if (rc != SWB_OK) return rc;
+        is_packed[w] = 1;
+    }
     for (size_t w = 0; w < jobs.size(); ++w) {
         const AlnJob &J = jobs[w];
         if (is_packed[w]) continue;

@@ -17,6 +17,8 @@
 // global mode reads the start state off the recomputed cell (la, lb).  Glocal stays on the direction-byte path.
 #include <algorithm>
 #include <cstdlib>
+
+#include <cuda/atomic>
 #include <cstdio>
 
 #include "swb_internal.h"
@@ -240,6 +242,195 @@ k3_fill_kernel(const uint8_t *__restrict__ a_all, const uint8_t *__restrict__ b_
     }
 }
 
+// ---- K3W: the int32 form of the fill for ONE long pair -----------------------------------------------------------------------
+// A pair whose scores leave the s16 range (a 100 kb x 100 kb DNA pair scores 148 609) cannot take the packed cell; on the
+// direction-byte path it costs 98 ms of KW + 38 ms of KT.  K3W is K3 with one cell per instruction: a lane owns a 32-column
+// pass in int32 registers (Ho, F, table pointers), runs 4-row blocks, hands its last column to the next lane by shuffles and
+// stores it (Ho, E, M, F: 16 bytes per row and pass = 0.5 B/cell) for the walker; every 64 rows the pass's H of rows r-1, r
+// and F of row r (r = 64 m - 1) are saved.  The sweeps (1024 columns each) of the ONE pair are dealt to all warps of a
+// cooperative grid, consecutive sweeps to different SMs; a sweep follows the one before it ~33 row blocks behind, through
+// the border store, guarded by a progress word per sweep in global memory (release store after the rows are written,
+// acquire load before they are read; waits only ever point to a lower sweep, every warp is resident: no deadlock).
+// Local mode tracks the first maximum itself (per-lane candidates, merged by k3w_pick_kernel in the reference's scan
+// order, SA.rs:286-294); the walk then starts there inside the full-matrix border store.
+#define K3W_WARPS 4
+#define K3W_ROWB_WORDS 96             // per (checkpoint, pass): Ho of row r-1, Ho of row r, F of row r (32 words each)
+
+typedef cuda::atomic_ref<int, cuda::thread_scope_device> k3w_flag;
+
+template <int MODE>
+__global__ void __launch_bounds__(K3W_WARPS * 32, 1)
+k3w_fill_kernel(const uint8_t *__restrict__ a, const uint8_t *__restrict__ b, int la, int lb, const int32_t *__restrict__ mat, int nl,
+                int open, int ext, uint4 *colb, int *rowb, int *prog, int4 *cand)
+{
+    extern __shared__ __align__(16) int TW_sh[];                     // [nl*nl][32 lanes]: s - open
+    for (int idx = threadIdx.x; idx < nl * nl * 32; idx += blockDim.x) TW_sh[idx] = mat[idx >> 5] - open;
+    __syncthreads();
+    const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
+    const int team = gridDim.x * K3W_WARPS;
+    const int gw = wib * gridDim.x + blockIdx.x;                     // consecutive sweeps sit on different SMs
+    const unsigned tbase = (unsigned)__cvta_generic_to_shared(TW_sh) + lane * 4;
+    const unsigned rowstride = (unsigned)nl * 128u;
+    const unsigned pad = (unsigned)(nl - 1);
+    const int sent = 10 * open + 10 * ext;
+    const int n_pass = (lb + K1_STRIP - 1) / K1_STRIP;
+    const int nblk = (la + 3) >> 2;
+    const int sweeps = (n_pass + 31) >> 5;
+    const int n_ck = la / K3_R;
+    // Ho = H + open of boundary cell (0, j) / (j, 0): global 2 open + (j-1) ext (SA.rs:100-118), local 0 + open
+    auto ho_bnd = [=](int j) { return (MODE == SWB_LOCAL || j == 0) ? open : 2 * open + (j - 1) * ext; };
+    int bestHo = open, bi = -1, bj = -1;                             // local: this lane's first maximum over all its sweeps
+
+    for (int sw = gw; sw < sweeps; sw += team) {
+        const int q = sw * 32 + lane;
+        const bool has_pass = q < n_pass;
+        const int jbase = q * K1_STRIP;
+        const int lanes_here = min(32, n_pass - sw * 32);
+        const int n_gb = nblk + lanes_here - 1;
+        int Ho[K1_STRIP], F[K1_STRIP];
+        unsigned cb[K1_STRIP];
+#pragma unroll
+        for (int k = 0; k < K1_STRIP; ++k) {
+            const int j = jbase + k;
+            const unsigned c = (has_pass && j < lb) ? (unsigned)b[j] : pad;
+            cb[k] = tbase + c * 128u;
+            if (MODE == SWB_LOCAL) { Ho[k] = open; F[k] = 0; }
+            else { Ho[k] = ho_bnd(j + 1); F[k] = Ho[k] - open + sent; }       // Y(0, j) = H(0, j) + sentinel (SA.rs:100-104)
+        }
+        const bool first = (q == 0);
+        const bool from_g = (lane == 0 && sw > 0);
+        int HoD = ho_bnd(jbase);                                     // Ho of (0, jbase): the diagonal of the first cell
+        int o0 = open, o1 = open, o2 = open, o3 = open;              // this lane's last column of its previous block: Ho of rows 1..4
+        int e0 = open, e1 = open, e2 = open, e3 = open;              //                                                  E
+        const uint4 *gin = colb + ((size_t)(q > 0 ? q - 1 : 0) * (nblk + 1)) * 4;
+        uint4 *gout = colb + ((size_t)q * (nblk + 1)) * 4;
+        int seen = 0;                                                // row blocks of the sweep before this one known to be published
+
+#pragma unroll 1
+        for (int gbk = 0; gbk < n_gb; ++gbk) {
+            const int bl = gbk - lane;
+            const bool active = has_pass && bl >= 0 && bl < nblk;
+            const int i0 = bl * 4;
+            // left boundary of this block's rows: the left lane's last column of ITS previous block (it runs one block ahead)
+            int lo[4], le[4];
+            lo[0] = __shfl_up_sync(0xffffffffu, o0, 1); lo[1] = __shfl_up_sync(0xffffffffu, o1, 1);
+            lo[2] = __shfl_up_sync(0xffffffffu, o2, 1); lo[3] = __shfl_up_sync(0xffffffffu, o3, 1);
+            le[0] = __shfl_up_sync(0xffffffffu, e0, 1); le[1] = __shfl_up_sync(0xffffffffu, e1, 1);
+            le[2] = __shfl_up_sync(0xffffffffu, e2, 1); le[3] = __shfl_up_sync(0xffffffffu, e3, 1);
+            if (sw > 0 && gbk < nblk) {                              // lane 0 reads block gbk of the sweep before: wait until it is published
+                if (seen < gbk + 1) {
+                    int v = 0;
+                    do {
+                        if (lane == 0) v = k3w_flag(prog[sw - 1]).load(cuda::memory_order_acquire);
+                        v = __shfl_sync(0xffffffffu, v, 0);
+                        if (v < gbk + 1) __nanosleep(40);
+                    } while (v < gbk + 1);
+                    seen = v;
+                }
+                if (lane == 0) {
+#pragma unroll
+                    for (int t = 0; t < 4; ++t) { const uint4 g = __ldcg(gin + (size_t)gbk * 4 + t); lo[t] = (int)g.x; le[t] = (int)g.y; }
+                }
+            }
+            if (first) {
+#pragma unroll
+                for (int t = 0; t < 4; ++t) {
+                    const int hb = ho_bnd(i0 + t + 1);
+                    lo[t] = MODE == SWB_LOCAL ? open : hb;           // column 0 (SA.rs:109-118): X(i, 0) = H(i, 0) + sentinel
+                    le[t] = MODE == SWB_LOCAL ? open : hb - open + sent;
+                }
+            }
+            (void)from_g;
+            if (active) {
+                unsigned word = 0;
+#pragma unroll
+                for (int t = 0; t < 4; ++t) word |= ((i0 + t < la) ? (unsigned)a[i0 + t] : pad) << (8 * t);
+                const bool snap = ((bl + 1) % (K3_R / 4) == 0) && ((bl + 1) / (K3_R / 4) <= n_ck);
+                int *rdst = rowb + ((size_t)(snap ? (bl + 1) / (K3_R / 4) - 1 : 0) * n_pass + q) * K3W_ROWB_WORDS;
+                int oo[4], ee[4];
+#pragma unroll
+                for (int t = 0; t < 4; ++t) {
+                    const int i = i0 + t + 1;
+                    const unsigned roff = ((word >> (8 * t)) & 0xFFu) * rowstride;
+                    int GoP = lo[t], E = le[t];
+                    const int HoD_next = GoP;
+                    int m31 = 0;
+#pragma unroll
+                    for (int k = 0; k < K1_STRIP; ++k) {
+                        const int s = (int)lds32(cb[k] + roff);
+                        const int Fk = __viaddmax_s32(F[k], ext, Ho[k]);
+                        const int G = MODE == SWB_LOCAL ? __viaddmax_s32_relu(HoD, s, Fk) : __viaddmax_s32(HoD, s, Fk);
+                        if (k == K1_STRIP - 1) m31 = HoD + s;
+                        E = __viaddmax_s32(E, ext, GoP);
+                        GoP = G + open;
+                        HoD = Ho[k];
+                        Ho[k] = __viaddmax_s32(E, open, GoP);
+                        F[k] = Fk;
+                    }
+                    HoD = HoD_next;
+                    oo[t] = Ho[K1_STRIP - 1]; ee[t] = E;
+                    gout[(size_t)bl * 4 + t] = make_uint4((unsigned)Ho[K1_STRIP - 1], (unsigned)E, (unsigned)m31, (unsigned)F[K1_STRIP - 1]);
+                    if (MODE == SWB_LOCAL && i <= la) {              // first strict maximum of this lane (rows ascend; first column inside the row)
+                        int rm = __vimax3_s32(Ho[0], Ho[1], Ho[2]);
+#pragma unroll
+                        for (int k = 3; k + 1 < K1_STRIP; k += 2) rm = __vimax3_s32(rm, Ho[k], Ho[k + 1]);
+                        rm = max(rm, Ho[K1_STRIP - 1]);
+                        if (rm > bestHo) {
+                            int kk = K1_STRIP - 1;
+#pragma unroll
+                            for (int k = K1_STRIP - 1; k >= 0; --k) if (Ho[k] == rm) kk = k;
+                            bestHo = rm; bi = i; bj = jbase + kk + 1;
+                        }
+                    }
+                    if (snap && t == 1) {
+#pragma unroll
+                        for (int k = 0; k < K1_STRIP; k += 4) *reinterpret_cast<int4 *>(rdst + k) = make_int4(Ho[k], Ho[k + 1], Ho[k + 2], Ho[k + 3]);
+                    }
+                    if (snap && t == 2) {
+#pragma unroll
+                        for (int k = 0; k < K1_STRIP; k += 4) {
+                            *reinterpret_cast<int4 *>(rdst + 32 + k) = make_int4(Ho[k], Ho[k + 1], Ho[k + 2], Ho[k + 3]);
+                            *reinterpret_cast<int4 *>(rdst + 64 + k) = make_int4(F[k], F[k + 1], F[k + 2], F[k + 3]);
+                        }
+                    }
+                }
+                o0 = oo[0]; o1 = oo[1]; o2 = oo[2]; o3 = oo[3];
+                e0 = ee[0]; e1 = ee[1]; e2 = ee[2]; e3 = ee[3];
+                if (lane == lanes_here - 1 && sw + 1 < sweeps) {     // publish block bl of this sweep's last column
+                    __threadfence();
+                    k3w_flag(prog[sw]).store(bl + 1, cuda::memory_order_release);
+                }
+            }
+        }
+        __syncwarp();
+    }
+    if (MODE == SWB_LOCAL) cand[(size_t)gw * 32 + lane] = make_int4(bestHo, bi, bj, 0);
+}
+
+// Local mode: the end cell = the best candidate in the reference's scan order (score desc, row asc, column asc); written
+// into the pair record the walker reads (cx0, cy0, score).  One block.
+__global__ void __launch_bounds__(256)
+k3w_pick_kernel(const int4 *__restrict__ cand, int n_cand, int open, K3Pair *pair)
+{
+    __shared__ int4 best_sh[256];
+    int4 best = make_int4(open, -1, -1, 0);
+    for (int k = threadIdx.x; k < n_cand; k += blockDim.x) {
+        const int4 c = cand[k];
+        if (c.x > best.x || (c.x == best.x && c.x > open && (c.y < best.y || (c.y == best.y && c.z < best.z)))) best = c;
+    }
+    best_sh[threadIdx.x] = best;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        for (int k = 1; k < (int)blockDim.x; ++k) {
+            const int4 c = best_sh[k];
+            if (c.x > best.x || (c.x == best.x && c.x > open && (c.y < best.y || (c.y == best.y && c.z < best.z)))) best = c;
+        }
+        pair->score = best.x - open;
+        pair->cx0 = best.x > open ? best.y : -1;
+        pair->cy0 = best.x > open ? best.z : -1;
+    }
+}
+
 // ---- KT3: the walk ------------------------------------------------------------------------------------------------------
 // One BLOCK of KT3_WARPS warps per pair.  The walk is serial, but re-computing a tile is not part of the dependency: a tile's
 // codes follow from the stored borders alone.  Each round, warp w re-computes the w-th tile that a straight diagonal from the
@@ -260,7 +451,7 @@ struct KT3Smem {
 };
 
 // (M, X, Y, raw E, H) of a stored border cell (row, column 32 q + 32) -- or of a matrix boundary cell.
-template <int MODE>
+template <int MODE, bool WIDE>
 __device__ __forceinline__ void kt3_border_cell(const uint4 *cb, int nblk, int q_left, int row, int col0, int open, int o, int e, int &M, int &X, int &Y, int &Eraw, int &H)
 {
     const int so = (MODE == SWB_GLOBAL) ? o : 0, se = (MODE == SWB_GLOBAL) ? e : 0, sent = 10 * o + 10 * e;
@@ -272,6 +463,12 @@ __device__ __forceinline__ void kt3_border_cell(const uint4 *cb, int nblk, int q
     if (row == 0) {                                     // row 0 (SA.rs:100-108)
         const int ls = col0 * se + (so - se);
         M = ls + sent; X = ls; Y = ls + sent; Eraw = X; H = ls; return;
+    }
+    if (WIDE) {                                         // K3W: one uint4 (Ho, E, M, F) per row, rows 4 b + 1 .. 4 b + 4 in block b
+        const uint4 g = cb[((size_t)q_left * (nblk + 1) + ((row - 1) >> 2)) * 4 + ((row - 1) & 3)];
+        H = (int)g.x - open; Eraw = (int)g.y; M = (int)g.z; Y = (int)g.w; X = Eraw;
+        if (MODE == SWB_LOCAL) { M = max(M, 0); X = max(X, 0); Y = max(Y, 0); }
+        return;
     }
     const uint4 *ent = cb + ((size_t)q_left * (nblk + 1) + (row >> 2)) * 2;
     const uint4 w0 = ent[0], w1 = ent[1];
@@ -292,7 +489,7 @@ struct KT3Ctx {
 };
 
 // Re-compute rows (rtop, hi_row] x columns (c0, hi_col] of the tile of (hi_row, hi_col) into S (one warp).
-template <int MODE>
+template <int MODE, bool WIDE>
 __device__ __forceinline__ void kt3_tile(KT3Smem &S, const KT3Ctx &C, int lane, int hi_row, int hi_col)
 {
     const int o = C.o, e = C.e, open = C.o, nl = C.nl, lb = C.lb;
@@ -308,14 +505,14 @@ __device__ __forceinline__ void kt3_tile(KT3Smem &S, const KT3Ctx &C, int lane, 
     if (lane == 0) { S.rtop = rtop; S.c0 = c0; S.tcx = hi_row; S.tcy = hi_col; }
     for (int r = lane; r <= nrows; r += 32) {
         int M, X, Y, Er, H;
-        kt3_border_cell<MODE>(C.cb, C.nblk, q - 1, rtop + r, c0, open, o, e, M, X, Y, Er, H);
+        kt3_border_cell<MODE, WIDE>(C.cb, C.nblk, q - 1, rtop + r, c0, open, o, e, M, X, Y, Er, H);
         S.left[r] = make_int4(M, X, Y, Er);
         if (r == 0) S.h0[0] = H;
         S.arow[r] = (rtop + r >= 1) ? (int)C.a[rtop + r - 1] * nl : 0;
     }
     if (lane == 0) {
         int M, X, Y, Er, H = 0;
-        if (rtop > 0) kt3_border_cell<MODE>(C.cb, C.nblk, q - 1, rtop - 1, c0, open, o, e, M, X, Y, Er, H);
+        if (rtop > 0) kt3_border_cell<MODE, WIDE>(C.cb, C.nblk, q - 1, rtop - 1, c0, open, o, e, M, X, Y, Er, H);
         S.hm1[0] = H;
     }
     // top border row rtop of this lane's column j = c0 + 1 + lane
@@ -326,11 +523,16 @@ __device__ __forceinline__ void kt3_tile(KT3Smem &S, const KT3Ctx &C, int lane, 
         Mu = ls + sent; Xu = ls; Yu = ls + sent;
         S.h0[lane + 1] = ls; S.hm1[lane + 1] = 0;
     } else {
-        const unsigned *w = C.rb + ((size_t)(m - 1) * C.n_pass + q) * K3_ROWB_WORDS;
-        const int k = lane & 15;
         int hm1, h0, f0;
-        if (lane < 16) { hm1 = lo16(w[k]) - open; h0 = lo16(w[16 + k]) - open; f0 = lo16(w[48 + k]); }
-        else { hm1 = hi16(w[16 + k]) - open; h0 = hi16(w[32 + k]) - open; f0 = hi16(w[64 + k]); }
+        if (WIDE) {
+            const int *w = reinterpret_cast<const int *>(C.rb) + ((size_t)(m - 1) * C.n_pass + q) * K3W_ROWB_WORDS;
+            hm1 = w[lane] - open; h0 = w[32 + lane] - open; f0 = w[64 + lane];
+        } else {
+            const unsigned *w = C.rb + ((size_t)(m - 1) * C.n_pass + q) * K3_ROWB_WORDS;
+            const int k = lane & 15;
+            if (lane < 16) { hm1 = lo16(w[k]) - open; h0 = lo16(w[16 + k]) - open; f0 = lo16(w[48 + k]); }
+            else { hm1 = hi16(w[16 + k]) - open; h0 = hi16(w[32 + k]) - open; f0 = hi16(w[64 + k]); }
+        }
         S.hm1[lane + 1] = hm1; S.h0[lane + 1] = h0;
         Yu = f0; Mu = 0; Xu = 0;
     }
@@ -374,7 +576,7 @@ __device__ __forceinline__ void kt3_tile(KT3Smem &S, const KT3Ctx &C, int lane, 
 
 struct KT3Walk { int cx, cy, st, n, score, done; };
 
-template <int MODE>
+template <int MODE, bool WIDE>
 __global__ void __launch_bounds__(KT3_MAX_WARPS * 32, 2)
 kt3_walk_kernel(const uint8_t *__restrict__ a_all, const uint8_t *__restrict__ b_all, const K3Pair *__restrict__ pairs, int n_pairs,
                 const int32_t *__restrict__ mat, int nl, int o, int e, const uint4 *__restrict__ colb, const unsigned *__restrict__ rowb,
@@ -396,18 +598,19 @@ kt3_walk_kernel(const uint8_t *__restrict__ a_all, const uint8_t *__restrict__ b
     KT3Ctx C;
     C.swp = P.swap != 0;
     C.a = C.swp ? b_all + P.b_off : a_all + P.a_off; C.b = C.swp ? a_all + P.a_off : b_all + P.b_off;
-    C.la = P.la; C.lb = P.lb; C.nblk = (P.la + 1 + 3) >> 2; C.n_pass = (P.lb + K1_STRIP - 1) / K1_STRIP;
+    C.la = P.la; C.lb = P.lb; C.nblk = WIDE ? (P.la + 3) >> 2 : (P.la + 1 + 3) >> 2; C.n_pass = (P.lb + K1_STRIP - 1) / K1_STRIP;
     C.nl = nl; C.o = o; C.e = e; C.cb = colb + P.colb_off; C.rb = rowb + P.rowb_off; C.mat_sh = mat_sh;
     const int la = P.la, lb = P.lb;
     const int sent = 10 * o + 10 * e;
     int32_t *xa = idx_a + P.out_off, *xb = idx_b + P.out_off;
-    if (threadIdx.x == 0) { W.cx = la; W.cy = lb; W.st = P.start_state; W.n = 0; W.score = P.score; W.done = 0; }
+    const int sx = P.cx0 ? P.cx0 : la, sy = P.cy0 ? P.cy0 : lb;     // the cell the walk starts at (wide local form: found by the fill)
+    if (threadIdx.x == 0) { W.cx = max(sx, 0); W.cy = max(sy, 0); W.st = P.start_state; W.n = 0; W.score = P.score; W.done = (sx < 0) ? 1 : 0; }
     if (lane == 0) sm_all[wib].tcx = -1;
     bool need_start = (MODE != SWB_LOCAL);
     int va = 0, vb = 0;                                              // warp 0: lane (n & 31) holds column n of the lists (one coalesced store per 32 columns)
     __syncthreads();
 
-    for (;;) {
+    for (; !W.done;) {
         // ---- every warp: the w-th tile on the straight diagonal from the cursor
         {
             int x = W.cx, y = W.cy;
@@ -424,7 +627,7 @@ kt3_walk_kernel(const uint8_t *__restrict__ a_all, const uint8_t *__restrict__ b
                     const int m = x / K3_R;
                     hi_row = min(m ? K3_R * m + K3_R - 1 : K3_R - 1, la); hi_col = min((((y - 1) >> 5) << 5) + 32, lb);
                 }
-                kt3_tile<MODE>(sm_all[wib], C, lane, hi_row, hi_col);
+                kt3_tile<MODE, WIDE>(sm_all[wib], C, lane, hi_row, hi_col);
             } else if (lane == 0) sm_all[wib].tcx = -1;
         }
         __syncthreads();
@@ -492,7 +695,7 @@ kt3_walk_kernel(const uint8_t *__restrict__ a_all, const uint8_t *__restrict__ b
     }
     if (threadIdx.x == 0) {
         ncols_out[p] = W.n;
-        KWResult R; R.score = W.score; R.end_i = la; R.end_j = lb; R.state = P.start_state;
+        KWResult R; R.score = W.score; R.end_i = sx; R.end_j = sy; R.state = P.start_state;
         res[p] = R;
     }
 }
@@ -550,16 +753,66 @@ cudaError_t k3_launch(const swb_engine *e, const uint8_t *d_a, const uint8_t *d_
     const size_t wsmem = (size_t)((nl * nl + 3) & ~3) * sizeof(int) + (size_t)kt3_warps * sizeof(KT3Smem);
     if (e->mode == SWB_LOCAL) {
         if ((err = cudaFuncSetAttribute(k3_fill_kernel<SWB_LOCAL>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)) != cudaSuccess) return err;
-        if ((err = cudaFuncSetAttribute(kt3_walk_kernel<SWB_LOCAL>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)wsmem)) != cudaSuccess) return err;
+        if ((err = cudaFuncSetAttribute(kt3_walk_kernel<SWB_LOCAL, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)wsmem)) != cudaSuccess) return err;
         k3_fill_kernel<SWB_LOCAL><<<fill_blocks, K3_WARPS * 32, smem, st>>>(d_a, d_b, d_pairs, n_pairs, e->d_mat, nl, e->o, e->e, d_colb, d_rowb, d_counter, team);
-        kt3_walk_kernel<SWB_LOCAL><<<walk_blocks, kt3_warps * 32, wsmem, st>>>(d_a, d_b, d_pairs, n_pairs, e->d_mat, nl, e->o, e->e, d_colb, d_rowb,
+        kt3_walk_kernel<SWB_LOCAL, false><<<walk_blocks, kt3_warps * 32, wsmem, st>>>(d_a, d_b, d_pairs, n_pairs, e->d_mat, nl, e->o, e->e, d_colb, d_rowb,
                                                                               d_idx_a, d_idx_b, d_ncols, d_res);
     } else {
         if ((err = cudaFuncSetAttribute(k3_fill_kernel<SWB_GLOBAL>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)) != cudaSuccess) return err;
-        if ((err = cudaFuncSetAttribute(kt3_walk_kernel<SWB_GLOBAL>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)wsmem)) != cudaSuccess) return err;
+        if ((err = cudaFuncSetAttribute(kt3_walk_kernel<SWB_GLOBAL, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)wsmem)) != cudaSuccess) return err;
         k3_fill_kernel<SWB_GLOBAL><<<fill_blocks, K3_WARPS * 32, smem, st>>>(d_a, d_b, d_pairs, n_pairs, e->d_mat, nl, e->o, e->e, d_colb, d_rowb, d_counter, team);
-        kt3_walk_kernel<SWB_GLOBAL><<<walk_blocks, kt3_warps * 32, wsmem, st>>>(d_a, d_b, d_pairs, n_pairs, e->d_mat, nl, e->o, e->e, d_colb, d_rowb,
+        kt3_walk_kernel<SWB_GLOBAL, false><<<walk_blocks, kt3_warps * 32, wsmem, st>>>(d_a, d_b, d_pairs, n_pairs, e->d_mat, nl, e->o, e->e, d_colb, d_rowb,
                                                                                d_idx_a, d_idx_b, d_ncols, d_res);
     }
     return cudaGetLastError();
 }
+
+// ---- K3W host side ------------------------------------------------------------------------------------------------------
+static int k3w_team_cap(const swb_engine *e) { return e->sm_count * K3W_WARPS; }
+
+void k3w_sizes(int32_t la, int32_t lb, int64_t *colb_uint4, int64_t *rowb_words, int64_t *scratch_ints)
+{
+    const int64_t n_pass = (lb + K1_STRIP - 1) / K1_STRIP, nblk = (la + 3) >> 2, n_ck = la / K3_R, sweeps = (n_pass + 31) / 32;
+    *colb_uint4 = n_pass * (nblk + 1) * 4;
+    *rowb_words = std::max<int64_t>(n_ck * n_pass * K3W_ROWB_WORDS, 4);
+    *scratch_ints = ((sweeps + 3) / 4 * 4) + 4 * 32 * (int64_t)(148 * 2 * K3W_WARPS);      // progress words, then the candidates (int4 per lane)
+}
+
+cudaError_t k3w_launch(const swb_engine *e, const uint8_t *d_a, const uint8_t *d_b, K3Pair *d_pair, const K3Pair &hp,
+                       uint4 *d_colb, unsigned *d_rowb, int *d_scratch, int32_t *d_idx_a, int32_t *d_idx_b, int32_t *d_ncols,
+                       KWResult *d_res, cudaStream_t st)
+{
+    const int nl = e->n + 1;
+    const size_t smem = (size_t)nl * nl * 32 * sizeof(int);
+    const int n_pass = (hp.lb + K1_STRIP - 1) / K1_STRIP, sweeps = (n_pass + 31) / 32;
+    const int blocks = std::max(1, std::min(e->sm_count, sweeps));
+    const int team = blocks * K3W_WARPS;
+    if (team > k3w_team_cap(e) * 2) return cudaErrorInvalidValue;
+    int *d_prog = d_scratch;
+    int4 *d_cand = reinterpret_cast<int4 *>(d_scratch + (sweeps + 3) / 4 * 4);
+    cudaError_t err = cudaMemsetAsync(d_prog, 0, (size_t)((sweeps + 3) / 4 * 4) * sizeof(int), st);
+    if (err != cudaSuccess) return err;
+    const uint8_t *pa = d_a + hp.a_off, *pb = d_b + hp.b_off;
+    int la = hp.la, lb = hp.lb, nl_ = nl, open = e->o, ext = e->e;
+    const int32_t *mat = e->d_mat;
+    int *rowb_i = reinterpret_cast<int *>(d_rowb);
+    void *args[] = {(void *)&pa, (void *)&pb, (void *)&la, (void *)&lb, (void *)&mat, (void *)&nl_, (void *)&open, (void *)&ext,
+                    (void *)&d_colb, (void *)&rowb_i, (void *)&d_prog, (void *)&d_cand};
+    const void *fn = e->mode == SWB_LOCAL ? reinterpret_cast<const void *>(&k3w_fill_kernel<SWB_LOCAL>) : reinterpret_cast<const void *>(&k3w_fill_kernel<SWB_GLOBAL>);
+    if ((err = cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)) != cudaSuccess) return err;
+    // the sweeps wait for each other across blocks: the grid must be resident at once (one block per SM by launch bounds)
+    if ((err = cudaLaunchCooperativeKernel(fn, dim3(blocks), dim3(K3W_WARPS * 32), args, smem, st)) != cudaSuccess) return err;
+    if (e->mode == SWB_LOCAL) k3w_pick_kernel<<<1, 256, 0, st>>>(d_cand, team * 32, e->o, d_pair);
+    int kt3_warps = KT3_WARPS;
+    if (const char *f = getenv("SWB_KT3_WARPS")) { const int v = atoi(f); if (v >= 1 && v <= KT3_MAX_WARPS) kt3_warps = v; }
+    const size_t wsmem = (size_t)((nl * nl + 3) & ~3) * sizeof(int) + (size_t)kt3_warps * sizeof(KT3Smem);
+    if (e->mode == SWB_LOCAL) {
+        if ((err = cudaFuncSetAttribute(kt3_walk_kernel<SWB_LOCAL, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)wsmem)) != cudaSuccess) return err;
+        kt3_walk_kernel<SWB_LOCAL, true><<<1, kt3_warps * 32, wsmem, st>>>(d_a, d_b, d_pair, 1, e->d_mat, nl, e->o, e->e, d_colb, d_rowb, d_idx_a, d_idx_b, d_ncols, d_res);
+    } else {
+        if ((err = cudaFuncSetAttribute(kt3_walk_kernel<SWB_GLOBAL, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)wsmem)) != cudaSuccess) return err;
+        kt3_walk_kernel<SWB_GLOBAL, true><<<1, kt3_warps * 32, wsmem, st>>>(d_a, d_b, d_pair, 1, e->d_mat, nl, e->o, e->e, d_colb, d_rowb, d_idx_a, d_idx_b, d_ncols, d_res);
+    }
+    return cudaGetLastError();
+}
+

@@ -233,7 +233,14 @@ struct K3Pair {
     int32_t score;                  // local: the scan's score (scaled); global: filled in by the walker
     int32_t swap;                   // 1: the kernels run the TRANSPOSED problem (rows = b, columns = a; la / lb above are the transposed
     int32_t pad_;                   //    extents): a tall box becomes a wide one, whose sweeps pipeline over a team of warps
-};
+    int32_t cx0, cy0;               // wide (int32) form: the cell the walk starts at, inside a border store laid out for la x lb
+};                                  //    (0, 0 = (la, lb); -1 = local score 0, nothing to walk); written by k3w_pick_kernel in local mode
+// K3W: the int32 form of K3 for ONE long pair whose scores leave the s16 range (100 kb DNA pairs): sweeps spread over the
+// whole GPU (cooperative launch, progress words in global memory), local mode finds its end cell itself.
+void k3w_sizes(int32_t la, int32_t lb, int64_t *colb_uint4, int64_t *rowb_words, int64_t *scratch_ints);
+cudaError_t k3w_launch(const swb_engine *e, const uint8_t *d_a, const uint8_t *d_b, K3Pair *d_pair, const K3Pair &h_pair,
+                       uint4 *d_colb, unsigned *d_rowb, int *d_scratch, int32_t *d_idx_a, int32_t *d_idx_b, int32_t *d_ncols,
+                       KWResult *d_res, cudaStream_t st);
 bool k3_eligible(const swb_engine *e, int64_t la, int64_t lb);       // mode, |open| >= |extend| and the static s16 bound (global)
 void k3_sizes(int32_t la, int32_t lb, int64_t *colb_uint4, int64_t *rowb_words);
 cudaError_t k3_launch(const swb_engine *e, const uint8_t *d_a, const uint8_t *d_b, const K3Pair *d_pairs, int n_pairs,

@@ -1039,6 +1039,38 @@ def test_packed_traceback_path_global(go, ge, protein, swap, monkeypatch):
     eng.close()
 
 
+@pytest.mark.parametrize("mode", [swb.ALIGN_LOCAL, swb.ALIGN_GLOBAL])
+@pytest.mark.parametrize("go,ge,protein", [(5.0, 2.0, False), (10.0, 0.5, True), (2.0, 2.0, False)])
+def test_wide_tile_path_small_pairs(go, ge, protein, mode, monkeypatch):
+    """K3W + KT3 (the int32 tile path of single long pairs, csrc/k3_tile.cu) forced onto pairs of every shape -- one pass, several
+    sweeps spread over several blocks (the cross-block progress words), fewer rows than one checkpoint, one-letter sequences,
+    unrelated pairs (local score 0 -> empty alignment), the maximum in the last column / last row -- against the dense
+    oracle: strings, index lists, score, end cell."""
+    monkeypatch.setenv("SWB_NO_K3", "1"); monkeypatch.setenv("SWB_K3W_MIN", "1")
+    rng = np.random.default_rng(int(go * 11 + ge * 5 + mode))
+    m = swb.SubstitutionMatrix.get_blosum62_matrix() if protein else swb.SubstitutionMatrix.get_mat_matrix(2.0, -3.0)
+    al = AA if protein else "ACGT"
+    eng = swb.SequenceAlignment(m, go, ge, mode)
+    oeng = O.Engine(_omatrix(m), go, ge, mode)
+    sa, sb = [], []
+    for la, lb in [(1, 1), (1, 40), (40, 1), (5, 70), (63, 33), (64, 32), (65, 31), (130, 1100), (1100, 130), (300, 3100), (700, 700), (257, 96), (4, 2050)]:
+        sa.append(_rand_seqs(rng, 1, la, la, al)[0]); sb.append(_rand_seqs(rng, 1, lb, lb, al)[0])
+    for k in range(14):
+        base = _rand_seqs(rng, 1, 30, 2600, al)[0]
+        sa.append(base); sb.append(_mutate(rng, base, 0.1, 0.04, 0.04, alphabet=al.encode()))
+    sa.append(_rand_seqs(rng, 1, 900, 900, al)[0]); sb.append(_rand_seqs(rng, 1, 50, 50, al)[0] + sa[-1][300:] )      # maximum in the last row and column
+    if not protein:
+        sa.append(b"AAAA"); sb.append(b"CCCCCC")                                                              # local: score 0
+    res = eng.align_list(sa, sb, True)
+    assert eng.stats()["k3_pairs"] >= 1
+    for k, r in enumerate(res):
+        r1, r2, s = oeng.align(sa[k].decode(), sb[k].decode(), True)
+        assert (r["aln_a"], r["aln_b"], r["score"]) == ("".join(r1), "".join(r2), s), k
+        xa, xb, _, ei, ej = oeng.raw(_omatrix(m).seq_to_index(sa[k].decode()), _omatrix(m).seq_to_index(sb[k].decode()))
+        assert np.array_equal(r["idx_a"], xa) and np.array_equal(r["idx_b"], xb) and (r["end_a"], r["end_b"]) == (ei, ej), k
+    eng.close()
+
+
 @pytest.mark.parametrize("swap", [None, "0", "1"])
 def test_packed_traceback_path_local_hits(swap, monkeypatch):
     """Local mode on the packed path: hits of a database search are traced inside the prefix box of their end cell with
