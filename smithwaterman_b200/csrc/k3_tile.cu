@@ -254,6 +254,7 @@ k3_fill_kernel(const uint8_t *__restrict__ a_all, const uint8_t *__restrict__ b_
 // Local mode tracks the first maximum itself (per-lane candidates, merged by k3w_pick_kernel in the reference's scan
 // order, SA.rs:286-294); the walk then starts there inside the full-matrix border store.
 #define K3W_WARPS 4
+#define K3W_AHEAD 6                   // a sweep polls the progress of the sweep before it for this many row blocks at once
 #define K3W_ROWB_WORDS 96             // per (checkpoint, pass): Ho of row r-1, Ho of row r, F of row r (32 words each)
 
 typedef cuda::atomic_ref<int, cuda::thread_scope_device> k3w_flag;
@@ -305,6 +306,26 @@ k3w_fill_kernel(const uint8_t *__restrict__ a, const uint8_t *__restrict__ b, in
         const uint4 *gin = colb + ((size_t)(q > 0 ? q - 1 : 0) * (nblk + 1)) * 4;
         uint4 *gout = colb + ((size_t)q * (nblk + 1)) * 4;
         int seen = 0;                                                // row blocks of the sweep before this one known to be published
+        // lane 0 of a later sweep reads the last column of the sweep before it from the border store.  Neither the progress
+        // poll nor the data load may sit on a step's critical path (two L2 round trips, ~1200 cycles, against ~2000 of
+        // arithmetic): the poll waits for K3W_AHEAD blocks at once, the data of block k + 1 is loaded during block k.
+        auto wait_pub = [&](int need) {
+            if (seen < need) {
+                const int want = min(need + K3W_AHEAD, nblk);
+                int v = 0;
+                do {
+                    if (lane == 0) v = k3w_flag(prog[sw - 1]).load(cuda::memory_order_acquire);
+                    v = __shfl_sync(0xffffffffu, v, 0);
+                    if (v < want) __nanosleep(200);
+                } while (v < want);
+                seen = v;
+            }
+        };
+        uint4 pf0 = make_uint4(0, 0, 0, 0), pf1 = pf0, pf2 = pf0, pf3 = pf0;
+        if (sw > 0) {
+            wait_pub(1);
+            if (lane == 0) { pf0 = __ldcg(gin + 0); pf1 = __ldcg(gin + 1); pf2 = __ldcg(gin + 2); pf3 = __ldcg(gin + 3); }
+        }
 
 #pragma unroll 1
         for (int gbk = 0; gbk < n_gb; ++gbk) {
@@ -317,19 +338,17 @@ k3w_fill_kernel(const uint8_t *__restrict__ a, const uint8_t *__restrict__ b, in
             lo[2] = __shfl_up_sync(0xffffffffu, o2, 1); lo[3] = __shfl_up_sync(0xffffffffu, o3, 1);
             le[0] = __shfl_up_sync(0xffffffffu, e0, 1); le[1] = __shfl_up_sync(0xffffffffu, e1, 1);
             le[2] = __shfl_up_sync(0xffffffffu, e2, 1); le[3] = __shfl_up_sync(0xffffffffu, e3, 1);
-            if (sw > 0 && gbk < nblk) {                              // lane 0 reads block gbk of the sweep before: wait until it is published
-                if (seen < gbk + 1) {
-                    int v = 0;
-                    do {
-                        if (lane == 0) v = k3w_flag(prog[sw - 1]).load(cuda::memory_order_acquire);
-                        v = __shfl_sync(0xffffffffu, v, 0);
-                        if (v < gbk + 1) __nanosleep(40);
-                    } while (v < gbk + 1);
-                    seen = v;
-                }
+            if (sw > 0 && gbk < nblk) {                              // lane 0: block gbk of the sweep before (loaded one step ago)
                 if (lane == 0) {
-#pragma unroll
-                    for (int t = 0; t < 4; ++t) { const uint4 g = __ldcg(gin + (size_t)gbk * 4 + t); lo[t] = (int)g.x; le[t] = (int)g.y; }
+                    lo[0] = (int)pf0.x; le[0] = (int)pf0.y; lo[1] = (int)pf1.x; le[1] = (int)pf1.y;
+                    lo[2] = (int)pf2.x; le[2] = (int)pf2.y; lo[3] = (int)pf3.x; le[3] = (int)pf3.y;
+                }
+                if (gbk + 1 < nblk) {
+                    wait_pub(gbk + 2);
+                    if (lane == 0) {
+                        const uint4 *gp = gin + (size_t)(gbk + 1) * 4;
+                        pf0 = __ldcg(gp); pf1 = __ldcg(gp + 1); pf2 = __ldcg(gp + 2); pf3 = __ldcg(gp + 3);
+                    }
                 }
             }
             if (first) {
@@ -371,10 +390,14 @@ k3w_fill_kernel(const uint8_t *__restrict__ a, const uint8_t *__restrict__ b, in
                     oo[t] = Ho[K1_STRIP - 1]; ee[t] = E;
                     gout[(size_t)bl * 4 + t] = make_uint4((unsigned)Ho[K1_STRIP - 1], (unsigned)E, (unsigned)m31, (unsigned)F[K1_STRIP - 1]);
                     if (MODE == SWB_LOCAL && i <= la) {              // first strict maximum of this lane (rows ascend; first column inside the row)
-                        int rm = __vimax3_s32(Ho[0], Ho[1], Ho[2]);
+                        // (a tree, not a chain: eleven independent maxima fill the bubbles of the row's E chain)
+                        int r3[11];
 #pragma unroll
-                        for (int k = 3; k + 1 < K1_STRIP; k += 2) rm = __vimax3_s32(rm, Ho[k], Ho[k + 1]);
-                        rm = max(rm, Ho[K1_STRIP - 1]);
+                        for (int k = 0; k < 10; ++k) r3[k] = __vimax3_s32(Ho[3 * k], Ho[3 * k + 1], Ho[3 * k + 2]);
+                        r3[10] = max(Ho[30], Ho[31]);
+                        const int ra = __vimax3_s32(r3[0], r3[1], r3[2]), rb2 = __vimax3_s32(r3[3], r3[4], r3[5]),
+                                  rc = __vimax3_s32(r3[6], r3[7], r3[8]), rd = max(r3[9], r3[10]);
+                        const int rm = max(__vimax3_s32(ra, rb2, rc), rd);
                         if (rm > bestHo) {
                             int kk = K1_STRIP - 1;
 #pragma unroll
@@ -396,10 +419,10 @@ k3w_fill_kernel(const uint8_t *__restrict__ a, const uint8_t *__restrict__ b, in
                 }
                 o0 = oo[0]; o1 = oo[1]; o2 = oo[2]; o3 = oo[3];
                 e0 = ee[0]; e1 = ee[1]; e2 = ee[2]; e3 = ee[3];
-                if (lane == lanes_here - 1 && sw + 1 < sweeps) {     // publish block bl of this sweep's last column
-                    __threadfence();
+                // publish this sweep's last column every 4 row blocks (the release store waits for the rows to be visible:
+                // an L2 round trip that must not be paid in every step)
+                if (lane == lanes_here - 1 && sw + 1 < sweeps && (((bl + 1) & 3) == 0 || bl + 1 == nblk))
                     k3w_flag(prog[sw]).store(bl + 1, cuda::memory_order_release);
-                }
             }
         }
         __syncwarp();
