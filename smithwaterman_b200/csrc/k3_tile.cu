@@ -254,7 +254,7 @@ k3_fill_kernel(const uint8_t *__restrict__ a_all, const uint8_t *__restrict__ b_
 // Local mode tracks the first maximum itself (per-lane candidates, merged by k3w_pick_kernel in the reference's scan
 // order, SA.rs:286-294); the walk then starts there inside the full-matrix border store.
 #define K3W_WARPS 4
-#define K3W_AHEAD 6                   // a sweep polls the progress of the sweep before it for this many row blocks at once
+#define K3W_AHEAD 10                  // a sweep polls the progress of the sweep before it for this many row blocks at once
 #define K3W_ROWB_WORDS 96             // per (checkpoint, pass): Ho of row r-1, Ho of row r, F of row r (32 words each)
 
 typedef cuda::atomic_ref<int, cuda::thread_scope_device> k3w_flag;
@@ -321,6 +321,15 @@ k3w_fill_kernel(const uint8_t *__restrict__ a, const uint8_t *__restrict__ b, in
                 seen = v;
             }
         };
+        auto load_rows = [&](int blk) -> unsigned {                  // residues of rows 4 blk + 1 .. 4 blk + 4, PAD beyond la
+            unsigned wd = 0;
+            if (has_pass && blk >= 0 && blk < nblk) {
+#pragma unroll
+                for (int t = 0; t < 4; ++t) wd |= ((4 * blk + t < la) ? (unsigned)a[4 * blk + t] : pad) << (8 * t);
+            }
+            return wd;
+        };
+        unsigned word_next = load_rows(-lane);
         uint4 pf0 = make_uint4(0, 0, 0, 0), pf1 = pf0, pf2 = pf0, pf3 = pf0;
         if (sw > 0) {
             wait_pub(1);
@@ -360,10 +369,9 @@ k3w_fill_kernel(const uint8_t *__restrict__ a, const uint8_t *__restrict__ b, in
                 }
             }
             (void)from_g;
+            const unsigned word = word_next;                         // fetched one block ahead: no load latency on the block's critical path
+            word_next = load_rows(bl + 1);
             if (active) {
-                unsigned word = 0;
-#pragma unroll
-                for (int t = 0; t < 4; ++t) word |= ((i0 + t < la) ? (unsigned)a[i0 + t] : pad) << (8 * t);
                 const bool snap = ((bl + 1) % (K3_R / 4) == 0) && ((bl + 1) / (K3_R / 4) <= n_ck);
                 int *rdst = rowb + ((size_t)(snap ? (bl + 1) / (K3_R / 4) - 1 : 0) * n_pass + q) * K3W_ROWB_WORDS;
                 int oo[4], ee[4];
@@ -419,9 +427,9 @@ k3w_fill_kernel(const uint8_t *__restrict__ a, const uint8_t *__restrict__ b, in
                 }
                 o0 = oo[0]; o1 = oo[1]; o2 = oo[2]; o3 = oo[3];
                 e0 = ee[0]; e1 = ee[1]; e2 = ee[2]; e3 = ee[3];
-                // publish this sweep's last column every 4 row blocks (the release store waits for the rows to be visible:
+                // publish this sweep's last column every 8 row blocks (the release store waits for the rows to be visible:
                 // an L2 round trip that must not be paid in every step)
-                if (lane == lanes_here - 1 && sw + 1 < sweeps && (((bl + 1) & 3) == 0 || bl + 1 == nblk))
+                if (lane == lanes_here - 1 && sw + 1 < sweeps && (((bl + 1) & 7) == 0 || bl + 1 == nblk))
                     k3w_flag(prog[sw]).store(bl + 1, cuda::memory_order_release);
             }
         }
@@ -826,7 +834,7 @@ cudaError_t k3w_launch(const swb_engine *e, const uint8_t *d_a, const uint8_t *d
     // the sweeps wait for each other across blocks: the grid must be resident at once (one block per SM by launch bounds)
     if ((err = cudaLaunchCooperativeKernel(fn, dim3(blocks), dim3(K3W_WARPS * 32), args, smem, st)) != cudaSuccess) return err;
     if (e->mode == SWB_LOCAL) k3w_pick_kernel<<<1, 256, 0, st>>>(d_cand, team * 32, e->o, d_pair);
-    int kt3_warps = KT3_WARPS;
+    int kt3_warps = KT3_MAX_WARPS;                                   // one pair, the GPU is otherwise idle: the deepest prediction (measured 8 / 12 / 16 warps: 68.8 / 67.2 / 66.8 ms)
     if (const char *f = getenv("SWB_KT3_WARPS")) { const int v = atoi(f); if (v >= 1 && v <= KT3_MAX_WARPS) kt3_warps = v; }
     const size_t wsmem = (size_t)((nl * nl + 3) & ~3) * sizeof(int) + (size_t)kt3_warps * sizeof(KT3Smem);
     if (e->mode == SWB_LOCAL) {
