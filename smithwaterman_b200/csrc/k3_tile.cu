@@ -831,8 +831,13 @@ cudaError_t k3w_launch(const swb_engine *e, const uint8_t *d_a, const uint8_t *d
                     (void *)&d_colb, (void *)&rowb_i, (void *)&d_prog, (void *)&d_cand};
     const void *fn = e->mode == SWB_LOCAL ? reinterpret_cast<const void *>(&k3w_fill_kernel<SWB_LOCAL>) : reinterpret_cast<const void *>(&k3w_fill_kernel<SWB_GLOBAL>);
     if ((err = cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)) != cudaSuccess) return err;
-    // the sweeps wait for each other across blocks: the grid must be resident at once (one block per SM by launch bounds)
+    // the sweeps wait for each other across blocks: the grid must be resident at once (one block per SM by launch bounds), and
+    // like KW's team launches it is chained through the engine's team event so that two such grids never share the GPU
+    swb_engine *me = const_cast<swb_engine *>(e);
+    if (!me->ev_team) { if ((err = cudaEventCreateWithFlags(&me->ev_team, cudaEventDisableTiming)) != cudaSuccess) return err; }
+    else if ((err = cudaStreamWaitEvent(st, me->ev_team, 0)) != cudaSuccess) return err;
     if ((err = cudaLaunchCooperativeKernel(fn, dim3(blocks), dim3(K3W_WARPS * 32), args, smem, st)) != cudaSuccess) return err;
+    if ((err = cudaEventRecord(me->ev_team, st)) != cudaSuccess) return err;
     if (e->mode == SWB_LOCAL) k3w_pick_kernel<<<1, 256, 0, st>>>(d_cand, team * 32, e->o, d_pair);
     int kt3_warps = KT3_MAX_WARPS;                                   // one pair, the GPU is otherwise idle: the deepest prediction (measured 8 / 12 / 16 warps: 68.8 / 67.2 / 66.8 ms)
     if (const char *f = getenv("SWB_KT3_WARPS")) { const int v = atoi(f); if (v >= 1 && v <= KT3_MAX_WARPS) kt3_warps = v; }
