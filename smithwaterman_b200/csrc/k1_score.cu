@@ -515,7 +515,8 @@ __global__ void __launch_bounds__(K1_THREADS * 2, 1)
 k2p_search_kernel(const uint8_t *__restrict__ a_codes, int la, const uint8_t *__restrict__ codes_b,
                   const int64_t *__restrict__ off_b, long long base_b, const int32_t *__restrict__ item_pairs,
                   const int32_t *__restrict__ item_sweeps, int n_items, const int32_t *__restrict__ mat, int nl, int open,
-                  int ext, int limit_ho, int pitch, uint4 *__restrict__ gbnd, int gb_blocks, int *counter, K1Result *__restrict__ res)
+                  int ext, int limit_ho, int pitch, uint4 *__restrict__ gbnd, int gb_blocks, int *counter, K1Result *__restrict__ res,
+                  unsigned one)
 {
     extern __shared__ __align__(16) unsigned char QP_sh[];          // [nl][pitch] bytes, then the snapshot slots
     __shared__ int cand_sh[K1_THREADS * 2 / 32][32][4];
@@ -598,8 +599,13 @@ k2p_search_kernel(const uint8_t *__restrict__ a_codes, int la, const uint8_t *__
                 bq[3] = open2;
                 unsigned wout[4];
                 K2P_ROW(0) K2P_ROW(1) K2P_ROW(2) K2P_ROW(3)
+                // the 32 pointer bumps go to the FMA pipe (x * one + 4 with `one` a kernel argument the compiler cannot fold): the
+                // ALU pipe, which the DPX instructions saturate, is the kernel's limit, the FMA pipe is 78 % idle
 #pragma unroll
-                for (int k = 0; k < K1_HALF; ++k) { plo[k] += 4u; phi[k] += 4u; }
+                for (int k = 0; k < K1_HALF; ++k) {
+                    asm("mad.lo.u32 %0, %0, %1, 4;" : "+r"(plo[k]) : "r"(one));
+                    asm("mad.lo.u32 %0, %0, %1, 4;" : "+r"(phi[k]) : "r"(one));
+                }
                 c1 = wout[1]; c2 = wout[2]; c3 = wout[3];
                 {
                     const int up = __shfl_up_sync(0xffffffffu, tb, 1), dn = __shfl_down_sync(0xffffffffu, tb, 1);
@@ -674,7 +680,7 @@ cudaError_t k2_launch(const swb_engine *e, const uint8_t *d_query, int la, const
         if (err != cudaSuccess) return err;
         k2p_search_kernel<<<n_blocks, K1_THREADS * 2, psmem, st>>>(
             d_query, la, d_codes_b, d_off_b, (long long)base_b, d_item_pairs, d_item_sweeps, n_items, e->d_mat, nl, e->o, e->e, limit_ho,
-            pitch, reinterpret_cast<uint4 *>(d_gbnd), (la + 1 + 3) / 4 + 2, d_counter, d_res);
+            pitch, reinterpret_cast<uint4 *>(d_gbnd), (la + 1 + 3) / 4 + 2, d_counter, d_res, 1u);
         return cudaGetLastError();
     }
     k2_search_kernel<<<n_blocks, K1_THREADS * 2, smem, st>>>(
