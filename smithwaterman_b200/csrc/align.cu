@@ -296,7 +296,8 @@ static int align_jobs_k3(swb_engine *e, const uint8_t *d_a, const uint8_t *d_b, 
                 if (fill_out(&outs[J.out], to_f(hr[t].score), ei, ej, xa, xb, ra, rb) != SWB_OK) { fail.store(SWB_ERR_NOMEM); return; }
             }
         };
-        const int n_thr = (np >= 8) ? (int)std::min<unsigned>(std::max(1u, std::thread::hardware_concurrency()), 16u) : 1;
+        // (a thread costs ~20 us to start: worth it from a few dozen alignments on, not for the dozen hits a shard owns)
+        const int n_thr = (np >= 48) ? (int)std::min<unsigned>(std::max(1u, std::thread::hardware_concurrency()), std::min(16u, (unsigned)np / 12u)) : 1;
         if (n_thr > 1) {
             std::vector<std::thread> pool;
             for (int w = 0; w < n_thr; ++w) pool.emplace_back(worker);

@@ -442,7 +442,7 @@ extern "C" int swb_search_align(swb_engine *e, const char *query, int64_t lq, sw
     // the query on the device (encoded on the host: a few kB)
     if (lq + 32 > db->query_cap) {
         CUDA_TRY(e, cudaStreamSynchronize(e->stream));
-        cudaFree(db->d_query); db->d_query = nullptr; db->query_cap = 0;
+        cudaFree(db->d_query); db->d_query = nullptr; db->query_cap = 0; db->h_query.clear();
         CUDA_TRY(e, cudaMalloc(&db->d_query, (size_t)lq + 64)); db->query_cap = lq + 64;
     }
     std::vector<uint8_t> cq((size_t)lq + 32, (uint8_t)e->n);
@@ -451,8 +451,11 @@ extern "C" int swb_search_align(swb_engine *e, const char *query, int64_t lq, sw
         if (c < 0) { e->err = std::string("unknown letter ") + query[t] + ". please set X to allow scoring for undefined letter pair."; return SWB_ERR_LETTER; }
         cq[t] = (uint8_t)c;
     }
-    CUDA_TRY(e, cudaMemcpyAsync(db->d_query, cq.data(), cq.size(), cudaMemcpyHostToDevice, e->stream));
-    CUDA_TRY(e, cudaStreamSynchronize(e->stream));
+    if (db->h_query != cq) {                                    // the same query as in the last call: its codes are on the device already
+        CUDA_TRY(e, cudaMemcpyAsync(db->d_query, cq.data(), cq.size(), cudaMemcpyHostToDevice, e->stream));
+        CUDA_TRY(e, cudaStreamSynchronize(e->stream));
+        db->h_query = cq;
+    }
     int rc = align_jobs_device(e, db->d_query, db->d_codes, jobs, retain_all, alns, nullptr, nullptr, nullptr, nullptr);
     if (rc == SWB_OK)
         for (const AlnJob &J : jobs)

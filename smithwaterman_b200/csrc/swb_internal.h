@@ -100,6 +100,7 @@ struct swb_db {
     // per-search scratch, kept between searches
     K1Result *d_res = nullptr;              // score / end cell / flags per subject (local index)
     uint8_t *d_query = nullptr; int64_t query_cap = 0;
+    std::vector<uint8_t> h_query;           // the codes d_query holds (swb_search_align uploads a query once)
     void *d_sel = nullptr;                  // top-K selection state + keys
     void *h_hits = nullptr;                 // pinned: the hits of the last search + counters
     int64_t last_lq = -1;                   // query length of the last search (its scores are in d_res)
