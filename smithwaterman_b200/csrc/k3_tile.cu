@@ -17,6 +17,7 @@
 // global mode reads the start state off the recomputed cell (la, lb).  Glocal stays on the direction-byte path.
 #include <algorithm>
 #include <cstdlib>
+#include <climits>
 
 #include <cuda/atomic>
 #include <cstdio>
@@ -406,12 +407,10 @@ k3w_fill_kernel(const uint8_t *__restrict__ a, const uint8_t *__restrict__ b, in
                         const int ra = __vimax3_s32(r3[0], r3[1], r3[2]), rb2 = __vimax3_s32(r3[3], r3[4], r3[5]),
                                   rc = __vimax3_s32(r3[6], r3[7], r3[8]), rd = max(r3[9], r3[10]);
                         const int rm = max(__vimax3_s32(ra, rb2, rc), rd);
-                        if (rm > bestHo) {
-                            int kk = K1_STRIP - 1;
-#pragma unroll
-                            for (int k = K1_STRIP - 1; k >= 0; --k) if (Ho[k] == rm) kk = k;
-                            bestHo = rm; bi = i; bj = jbase + kk + 1;
-                        }
+                        // only the row and the pass are kept (two predicated moves): along a long alignment the best improves in
+                        // almost every row, and finding the column here (32 compares) cost 13 of the fill's 50 ms.  The walker
+                        // reads the column off the first tile it re-computes (KT3Smem::lastM).
+                        if (rm > bestHo) { bestHo = rm; bi = i; bj = min(jbase + K1_STRIP, lb); }
                     }
                     if (snap && t == 1) {
 #pragma unroll
@@ -438,8 +437,9 @@ k3w_fill_kernel(const uint8_t *__restrict__ a, const uint8_t *__restrict__ b, in
     if (MODE == SWB_LOCAL) cand[(size_t)gw * 32 + lane] = make_int4(bestHo, bi, bj, 0);
 }
 
-// Local mode: the end cell = the best candidate in the reference's scan order (score desc, row asc, column asc); written
-// into the pair record the walker reads (cx0, cy0, score).  One block.
+// Local mode: the end cell = the best candidate in the reference's scan order (score desc, row asc, column asc -- the passes
+// are ordered by column, the column inside the pass is resolved by the walker); written into the pair record the walker
+// reads (cx0, cy0, score).  One block.
 __global__ void __launch_bounds__(256)
 k3w_pick_kernel(const int4 *__restrict__ cand, int n_cand, int open, K3Pair *pair)
 {
@@ -458,7 +458,8 @@ k3w_pick_kernel(const int4 *__restrict__ cand, int n_cand, int open, K3Pair *pai
         }
         pair->score = best.x - open;
         pair->cx0 = best.x > open ? best.y : -1;
-        pair->cy0 = best.x > open ? best.z : -1;
+        pair->cy0 = best.x > open ? best.z : -1;                     // the LAST column of the pass that holds the end cell:
+        pair->pad_ = 1;                                              // the walker finds the column itself (first MATCH == score in that row)
     }
 }
 
@@ -479,6 +480,7 @@ struct KT3Smem {
     int arow[K3_R + 2];             // score-table row offset of the residue of row rtop + r (no global load inside the wavefront)
     int rtop, c0, tcx, tcy;         // the tile held: rows (rtop, tcx], columns (c0, tcy]; tcx < 0 = none
     int fin[3];                     // (M, X, Y) of the tile's last cell (tcx, tcy): the start state of a global walk
+    int lastM[32];                  // MATCH of the tile's last row, per column: the wide local form finds its start column here
 };
 
 // (M, X, Y, raw E, H) of a stored border cell (row, column 32 q + 32) -- or of a matrix boundary cell.
@@ -602,10 +604,11 @@ __device__ __forceinline__ void kt3_tile(KT3Smem &S, const KT3Ctx &C, int lane, 
         }
     }
     if (lane == ncols - 1) { S.fin[0] = Mu; S.fin[1] = Xu; S.fin[2] = Yu; }
+    S.lastM[lane] = (lane < ncols) ? Mu : INT_MIN;
     __syncwarp();
 }
 
-struct KT3Walk { int cx, cy, st, n, score, done; };
+struct KT3Walk { int cx, cy, st, n, score, done, sy; };
 
 template <int MODE, bool WIDE>
 __global__ void __launch_bounds__(KT3_MAX_WARPS * 32, 2)
@@ -635,7 +638,8 @@ kt3_walk_kernel(const uint8_t *__restrict__ a_all, const uint8_t *__restrict__ b
     const int sent = 10 * o + 10 * e;
     int32_t *xa = idx_a + P.out_off, *xb = idx_b + P.out_off;
     const int sx = P.cx0 ? P.cx0 : la, sy = P.cy0 ? P.cy0 : lb;     // the cell the walk starts at (wide local form: found by the fill)
-    if (threadIdx.x == 0) { W.cx = max(sx, 0); W.cy = max(sy, 0); W.st = P.start_state; W.n = 0; W.score = P.score; W.done = (sx < 0) ? 1 : 0; }
+    if (threadIdx.x == 0) { W.cx = max(sx, 0); W.cy = max(sy, 0); W.st = P.start_state; W.n = 0; W.score = P.score; W.done = (sx < 0) ? 1 : 0; W.sy = sy; }
+    bool need_col = WIDE && MODE == SWB_LOCAL && P.pad_ == 1 && sx >= 1;      // sy is the end of the start cell's pass, not yet its column
     if (lane == 0) sm_all[wib].tcx = -1;
     bool need_start = (MODE != SWB_LOCAL);
     int va = 0, vb = 0;                                              // warp 0: lane (n & 31) holds column n of the lists (one coalesced store per 32 columns)
@@ -665,6 +669,11 @@ kt3_walk_kernel(const uint8_t *__restrict__ a_all, const uint8_t *__restrict__ b
         // ---- warp 0: walk through the tiles at hand (backtrack, SA.rs:346-383); the same on every lane, lane 0 writes
         if (wib == 0) {
             int cx = W.cx, cy = W.cy, st = W.st, n = W.n, score = W.score, done = 0;
+            if (need_col) {                                          // first MATCH == score in the start row (SA.rs:286-294: columns ascend)
+                const unsigned hit = __ballot_sync(0xffffffffu, sm_all[0].lastM[lane] == score);
+                if (hit) { cy = sm_all[0].c0 + __ffs(hit); if (lane == 0) W.sy = cy; }
+                else { n = -2; done = 1; }                           // cannot happen: the fill saw this value in this row of this pass
+            }
             if (need_start && cx >= 1 && cy >= 1) {                  // cell (la, lb): first strict maximum in the order M, X, Y (SA.rs:302-308)
                 const int fm = sm_all[0].fin[0], fx = sm_all[0].fin[1], fy = sm_all[0].fin[2];
                 score = fm; st = 0;
@@ -674,7 +683,7 @@ kt3_walk_kernel(const uint8_t *__restrict__ a_all, const uint8_t *__restrict__ b
             // Inside a tile the walk is a tight loop: one code byte per step at a linear position, no boundary, panic or end
             // tests (a tile's cells have cx, cy >= 1); everything else -- changing tiles, the matrix boundary, the end of the
             // walk -- is the slow path around it.
-            for (;;) {
+            for (; !done;) {
                 if (cx >= 1 && cy >= 1) {
                     int found = -1;
                     for (int k = 0; k < n_warps; ++k) {
@@ -719,14 +728,14 @@ kt3_walk_kernel(const uint8_t *__restrict__ a_all, const uint8_t *__restrict__ b
             __syncwarp();
             if (lane == 0) { W.cx = cx; W.cy = cy; W.st = st; W.n = n; W.score = score; W.done = done; }
         }
-        need_start = false;
+        need_start = false; need_col = false;
         __syncthreads();
         if (W.done) break;
         __syncthreads();                                             // everybody has read the cursor before warp 0 may write it again
     }
     if (threadIdx.x == 0) {
         ncols_out[p] = W.n;
-        KWResult R; R.score = W.score; R.end_i = sx; R.end_j = sy; R.state = P.start_state;
+        KWResult R; R.score = W.score; R.end_i = sx; R.end_j = (sx >= 1) ? W.sy : sy; R.state = P.start_state;
         res[p] = R;
     }
 }
