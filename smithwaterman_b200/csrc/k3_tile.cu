@@ -255,6 +255,7 @@ k3_fill_kernel(const uint8_t *__restrict__ a_all, const uint8_t *__restrict__ b_
 // Local mode tracks the first maximum itself (per-lane candidates, merged by k3w_pick_kernel in the reference's scan
 // order, SA.rs:286-294); the walk then starts there inside the full-matrix border store.
 #define K3W_WARPS 4
+#define K3W_COLS 16                   // columns per lane: half a 32-column pass
 #define K3W_AHEAD 10                  // a sweep polls the progress of the sweep before it for this many row blocks at once
 #define K3W_ROWB_WORDS 96             // per (checkpoint, pass): Ho of row r-1, Ho of row r, F of row r (32 words each)
 
@@ -276,30 +277,33 @@ k3w_fill_kernel(const uint8_t *__restrict__ a, const uint8_t *__restrict__ b, in
     const unsigned pad = (unsigned)(nl - 1);
     const int sent = 10 * open + 10 * ext;
     const int n_pass = (lb + K1_STRIP - 1) / K1_STRIP;
-    const int nblk = (la + 3) >> 2;
-    const int sweeps = (n_pass + 31) >> 5;
+    const int n_half = 2 * n_pass;                                   // a lane owns HALF a pass (K3W_COLS = 16 columns): twice the sweeps,
+    const int nblk = (la + 3) >> 2;                                  // half the work per step -- a lone warp per SM sub-partition is latency-bound
+    const int sweeps = (n_half + 31) >> 5;
     const int n_ck = la / K3_R;
     // Ho = H + open of boundary cell (0, j) / (j, 0): global 2 open + (j-1) ext (SA.rs:100-118), local 0 + open
     auto ho_bnd = [=](int j) { return (MODE == SWB_LOCAL || j == 0) ? open : 2 * open + (j - 1) * ext; };
     int bestHo = open, bi = -1, bj = -1;                             // local: this lane's first maximum over all its sweeps
 
     for (int sw = gw; sw < sweeps; sw += team) {
-        const int q = sw * 32 + lane;
-        const bool has_pass = q < n_pass;
-        const int jbase = q * K1_STRIP;
-        const int lanes_here = min(32, n_pass - sw * 32);
+        const int hq = sw * 32 + lane;                               // half-pass index; pass q = hq / 2, right half = hq & 1
+        const int q = hq >> 1;
+        const bool right = (hq & 1) != 0;
+        const bool has_pass = hq < n_half;
+        const int jbase = hq * K3W_COLS;
+        const int lanes_here = min(32, n_half - sw * 32);            // even: the last lane of a sweep is a right half
         const int n_gb = nblk + lanes_here - 1;
-        int Ho[K1_STRIP], F[K1_STRIP];
-        unsigned cb[K1_STRIP];
+        int Ho[K3W_COLS], F[K3W_COLS];
+        unsigned cb[K3W_COLS];
 #pragma unroll
-        for (int k = 0; k < K1_STRIP; ++k) {
+        for (int k = 0; k < K3W_COLS; ++k) {
             const int j = jbase + k;
             const unsigned c = (has_pass && j < lb) ? (unsigned)b[j] : pad;
             cb[k] = tbase + c * 128u;
             if (MODE == SWB_LOCAL) { Ho[k] = open; F[k] = 0; }
             else { Ho[k] = ho_bnd(j + 1); F[k] = Ho[k] - open + sent; }       // Y(0, j) = H(0, j) + sentinel (SA.rs:100-104)
         }
-        const bool first = (q == 0);
+        const bool first = (hq == 0);
         const bool from_g = (lane == 0 && sw > 0);
         int HoD = ho_bnd(jbase);                                     // Ho of (0, jbase): the diagonal of the first cell
         int o0 = open, o1 = open, o2 = open, o3 = open;              // this lane's last column of its previous block: Ho of rows 1..4
@@ -374,7 +378,7 @@ k3w_fill_kernel(const uint8_t *__restrict__ a, const uint8_t *__restrict__ b, in
             word_next = load_rows(bl + 1);
             if (active) {
                 const bool snap = ((bl + 1) % (K3_R / 4) == 0) && ((bl + 1) / (K3_R / 4) <= n_ck);
-                int *rdst = rowb + ((size_t)(snap ? (bl + 1) / (K3_R / 4) - 1 : 0) * n_pass + q) * K3W_ROWB_WORDS;
+                int *rdst = rowb + ((size_t)(snap ? (bl + 1) / (K3_R / 4) - 1 : 0) * n_pass + q) * K3W_ROWB_WORDS + (right ? K3W_COLS : 0);
                 int oo[4], ee[4];
 #pragma unroll
                 for (int t = 0; t < 4; ++t) {
@@ -384,11 +388,11 @@ k3w_fill_kernel(const uint8_t *__restrict__ a, const uint8_t *__restrict__ b, in
                     const int HoD_next = GoP;
                     int m31 = 0;
 #pragma unroll
-                    for (int k = 0; k < K1_STRIP; ++k) {
+                    for (int k = 0; k < K3W_COLS; ++k) {
                         const int s = (int)lds32(cb[k] + roff);
                         const int Fk = __viaddmax_s32(F[k], ext, Ho[k]);
                         const int G = MODE == SWB_LOCAL ? __viaddmax_s32_relu(HoD, s, Fk) : __viaddmax_s32(HoD, s, Fk);
-                        if (k == K1_STRIP - 1) m31 = HoD + s;
+                        if (k == K3W_COLS - 1) m31 = HoD + s;
                         E = __viaddmax_s32(E, ext, GoP);
                         GoP = G + open;
                         HoD = Ho[k];
@@ -396,29 +400,26 @@ k3w_fill_kernel(const uint8_t *__restrict__ a, const uint8_t *__restrict__ b, in
                         F[k] = Fk;
                     }
                     HoD = HoD_next;
-                    oo[t] = Ho[K1_STRIP - 1]; ee[t] = E;
-                    gout[(size_t)bl * 4 + t] = make_uint4((unsigned)Ho[K1_STRIP - 1], (unsigned)E, (unsigned)m31, (unsigned)F[K1_STRIP - 1]);
+                    oo[t] = Ho[K3W_COLS - 1]; ee[t] = E;
+                    if (right) gout[(size_t)bl * 4 + t] = make_uint4((unsigned)Ho[K3W_COLS - 1], (unsigned)E, (unsigned)m31, (unsigned)F[K3W_COLS - 1]);
                     if (MODE == SWB_LOCAL && i <= la) {              // first strict maximum of this lane (rows ascend; first column inside the row)
-                        // (a tree, not a chain: eleven independent maxima fill the bubbles of the row's E chain)
-                        int r3[11];
-#pragma unroll
-                        for (int k = 0; k < 10; ++k) r3[k] = __vimax3_s32(Ho[3 * k], Ho[3 * k + 1], Ho[3 * k + 2]);
-                        r3[10] = max(Ho[30], Ho[31]);
-                        const int ra = __vimax3_s32(r3[0], r3[1], r3[2]), rb2 = __vimax3_s32(r3[3], r3[4], r3[5]),
-                                  rc = __vimax3_s32(r3[6], r3[7], r3[8]), rd = max(r3[9], r3[10]);
-                        const int rm = max(__vimax3_s32(ra, rb2, rc), rd);
+                        // (a tree, not a chain: independent maxima fill the bubbles of the row's E chain)
+                        const int ra = __vimax3_s32(Ho[0], Ho[1], Ho[2]), rb2 = __vimax3_s32(Ho[3], Ho[4], Ho[5]),
+                                  rc = __vimax3_s32(Ho[6], Ho[7], Ho[8]), rd = __vimax3_s32(Ho[9], Ho[10], Ho[11]),
+                                  re = __vimax3_s32(Ho[12], Ho[13], Ho[14]);
+                        const int rm = __vimax3_s32(__vimax3_s32(ra, rb2, rc), __vimax3_s32(rd, re, Ho[15]), bestHo);
                         // only the row and the pass are kept (two predicated moves): along a long alignment the best improves in
                         // almost every row, and finding the column here (32 compares) cost 13 of the fill's 50 ms.  The walker
                         // reads the column off the first tile it re-computes (KT3Smem::lastM).
-                        if (rm > bestHo) { bestHo = rm; bi = i; bj = min(jbase + K1_STRIP, lb); }
+                        if (rm > bestHo) { bestHo = rm; bi = i; bj = min((q + 1) * K1_STRIP, lb); }
                     }
                     if (snap && t == 1) {
 #pragma unroll
-                        for (int k = 0; k < K1_STRIP; k += 4) *reinterpret_cast<int4 *>(rdst + k) = make_int4(Ho[k], Ho[k + 1], Ho[k + 2], Ho[k + 3]);
+                        for (int k = 0; k < K3W_COLS; k += 4) *reinterpret_cast<int4 *>(rdst + k) = make_int4(Ho[k], Ho[k + 1], Ho[k + 2], Ho[k + 3]);
                     }
                     if (snap && t == 2) {
 #pragma unroll
-                        for (int k = 0; k < K1_STRIP; k += 4) {
+                        for (int k = 0; k < K3W_COLS; k += 4) {
                             *reinterpret_cast<int4 *>(rdst + 32 + k) = make_int4(Ho[k], Ho[k + 1], Ho[k + 2], Ho[k + 3]);
                             *reinterpret_cast<int4 *>(rdst + 64 + k) = make_int4(F[k], F[k + 1], F[k + 2], F[k + 3]);
                         }
@@ -812,7 +813,7 @@ static int k3w_team_cap(const swb_engine *e) { return e->sm_count * K3W_WARPS; }
 
 void k3w_sizes(int32_t la, int32_t lb, int64_t *colb_uint4, int64_t *rowb_words, int64_t *scratch_ints)
 {
-    const int64_t n_pass = (lb + K1_STRIP - 1) / K1_STRIP, nblk = (la + 3) >> 2, n_ck = la / K3_R, sweeps = (n_pass + 31) / 32;
+    const int64_t n_pass = (lb + K1_STRIP - 1) / K1_STRIP, nblk = (la + 3) >> 2, n_ck = la / K3_R, sweeps = (2 * n_pass + 31) / 32;
     *colb_uint4 = n_pass * (nblk + 1) * 4;
     *rowb_words = std::max<int64_t>(n_ck * n_pass * K3W_ROWB_WORDS, 4);
     *scratch_ints = ((sweeps + 3) / 4 * 4) + 4 * 32 * (int64_t)(148 * 2 * K3W_WARPS);      // progress words, then the candidates (int4 per lane)
@@ -824,7 +825,7 @@ cudaError_t k3w_launch(const swb_engine *e, const uint8_t *d_a, const uint8_t *d
 {
     const int nl = e->n + 1;
     const size_t smem = (size_t)nl * nl * 32 * sizeof(int);
-    const int n_pass = (hp.lb + K1_STRIP - 1) / K1_STRIP, sweeps = (n_pass + 31) / 32;
+    const int n_pass = (hp.lb + K1_STRIP - 1) / K1_STRIP, sweeps = (2 * n_pass + 31) / 32;    // a sweep = 32 half-passes of 16 columns
     const int blocks = std::max(1, std::min(e->sm_count, sweeps));
     const int team = blocks * K3W_WARPS;
     if (team > k3w_team_cap(e) * 2) return cudaErrorInvalidValue;
