@@ -255,7 +255,10 @@ k3_fill_kernel(const uint8_t *__restrict__ a_all, const uint8_t *__restrict__ b_
 // Local mode tracks the first maximum itself (per-lane candidates, merged by k3w_pick_kernel in the reference's scan
 // order, SA.rs:286-294); the walk then starts there inside the full-matrix border store.
 #define K3W_WARPS 4
-#define K3W_COLS 16                   // columns per lane: half a 32-column pass
+#ifndef K3W_COLS
+#define K3W_COLS 16                   // columns per lane: half a 32-column pass (measured 32 / 16 / 8: 48.5 / 40.8 / 43.6 ms for the 100 kb global pair)
+#endif
+#define K3W_PARTS (K1_STRIP / K3W_COLS)
 #define K3W_AHEAD 10                  // a sweep polls the progress of the sweep before it for this many row blocks at once
 #define K3W_ROWB_WORDS 96             // per (checkpoint, pass): Ho of row r-1, Ho of row r, F of row r (32 words each)
 
@@ -277,7 +280,7 @@ k3w_fill_kernel(const uint8_t *__restrict__ a, const uint8_t *__restrict__ b, in
     const unsigned pad = (unsigned)(nl - 1);
     const int sent = 10 * open + 10 * ext;
     const int n_pass = (lb + K1_STRIP - 1) / K1_STRIP;
-    const int n_half = 2 * n_pass;                                   // a lane owns HALF a pass (K3W_COLS = 16 columns): twice the sweeps,
+    const int n_half = K3W_PARTS * n_pass;                                  // a lane owns HALF a pass (K3W_COLS = 16 columns): twice the sweeps,
     const int nblk = (la + 3) >> 2;                                  // half the work per step -- a lone warp per SM sub-partition is latency-bound
     const int sweeps = (n_half + 31) >> 5;
     const int n_ck = la / K3_R;
@@ -287,8 +290,8 @@ k3w_fill_kernel(const uint8_t *__restrict__ a, const uint8_t *__restrict__ b, in
 
     for (int sw = gw; sw < sweeps; sw += team) {
         const int hq = sw * 32 + lane;                               // half-pass index; pass q = hq / 2, right half = hq & 1
-        const int q = hq >> 1;
-        const bool right = (hq & 1) != 0;
+        const int q = hq / K3W_PARTS, part = hq - q * K3W_PARTS;
+        const bool right = (part == K3W_PARTS - 1);                  // the part that holds the pass's last column
         const bool has_pass = hq < n_half;
         const int jbase = hq * K3W_COLS;
         const int lanes_here = min(32, n_half - sw * 32);            // even: the last lane of a sweep is a right half
@@ -378,7 +381,7 @@ k3w_fill_kernel(const uint8_t *__restrict__ a, const uint8_t *__restrict__ b, in
             word_next = load_rows(bl + 1);
             if (active) {
                 const bool snap = ((bl + 1) % (K3_R / 4) == 0) && ((bl + 1) / (K3_R / 4) <= n_ck);
-                int *rdst = rowb + ((size_t)(snap ? (bl + 1) / (K3_R / 4) - 1 : 0) * n_pass + q) * K3W_ROWB_WORDS + (right ? K3W_COLS : 0);
+                int *rdst = rowb + ((size_t)(snap ? (bl + 1) / (K3_R / 4) - 1 : 0) * n_pass + q) * K3W_ROWB_WORDS + part * K3W_COLS;
                 int oo[4], ee[4];
 #pragma unroll
                 for (int t = 0; t < 4; ++t) {
@@ -404,10 +407,15 @@ k3w_fill_kernel(const uint8_t *__restrict__ a, const uint8_t *__restrict__ b, in
                     if (right) gout[(size_t)bl * 4 + t] = make_uint4((unsigned)Ho[K3W_COLS - 1], (unsigned)E, (unsigned)m31, (unsigned)F[K3W_COLS - 1]);
                     if (MODE == SWB_LOCAL && i <= la) {              // first strict maximum of this lane (rows ascend; first column inside the row)
                         // (a tree, not a chain: independent maxima fill the bubbles of the row's E chain)
-                        const int ra = __vimax3_s32(Ho[0], Ho[1], Ho[2]), rb2 = __vimax3_s32(Ho[3], Ho[4], Ho[5]),
-                                  rc = __vimax3_s32(Ho[6], Ho[7], Ho[8]), rd = __vimax3_s32(Ho[9], Ho[10], Ho[11]),
-                                  re = __vimax3_s32(Ho[12], Ho[13], Ho[14]);
-                        const int rm = __vimax3_s32(__vimax3_s32(ra, rb2, rc), __vimax3_s32(rd, re, Ho[15]), bestHo);
+                        int rmx[K3W_COLS / 2];
+#pragma unroll
+                        for (int k = 0; k < K3W_COLS / 2; ++k) rmx[k] = max(Ho[2 * k], Ho[2 * k + 1]);
+#pragma unroll
+                        for (int w2 = K3W_COLS / 4; w2 >= 1; w2 >>= 1) {
+#pragma unroll
+                            for (int k = 0; k < w2; ++k) rmx[k] = max(rmx[k], rmx[k + w2]);
+                        }
+                        const int rm = max(rmx[0], bestHo);
                         // only the row and the pass are kept (two predicated moves): along a long alignment the best improves in
                         // almost every row, and finding the column here (32 compares) cost 13 of the fill's 50 ms.  The walker
                         // reads the column off the first tile it re-computes (KT3Smem::lastM).
@@ -813,7 +821,7 @@ static int k3w_team_cap(const swb_engine *e) { return e->sm_count * K3W_WARPS; }
 
 void k3w_sizes(int32_t la, int32_t lb, int64_t *colb_uint4, int64_t *rowb_words, int64_t *scratch_ints)
 {
-    const int64_t n_pass = (lb + K1_STRIP - 1) / K1_STRIP, nblk = (la + 3) >> 2, n_ck = la / K3_R, sweeps = (2 * n_pass + 31) / 32;
+    const int64_t n_pass = (lb + K1_STRIP - 1) / K1_STRIP, nblk = (la + 3) >> 2, n_ck = la / K3_R, sweeps = (K3W_PARTS * n_pass + 31) / 32;
     *colb_uint4 = n_pass * (nblk + 1) * 4;
     *rowb_words = std::max<int64_t>(n_ck * n_pass * K3W_ROWB_WORDS, 4);
     *scratch_ints = ((sweeps + 3) / 4 * 4) + 4 * 32 * (int64_t)(148 * 2 * K3W_WARPS);      // progress words, then the candidates (int4 per lane)
@@ -825,7 +833,7 @@ cudaError_t k3w_launch(const swb_engine *e, const uint8_t *d_a, const uint8_t *d
 {
     const int nl = e->n + 1;
     const size_t smem = (size_t)nl * nl * 32 * sizeof(int);
-    const int n_pass = (hp.lb + K1_STRIP - 1) / K1_STRIP, sweeps = (2 * n_pass + 31) / 32;    // a sweep = 32 half-passes of 16 columns
+    const int n_pass = (hp.lb + K1_STRIP - 1) / K1_STRIP, sweeps = (K3W_PARTS * n_pass + 31) / 32;    // a sweep = 32 lanes of K3W_COLS columns
     const int blocks = std::max(1, std::min(e->sm_count, sweeps));
     const int team = blocks * K3W_WARPS;
     if (team > k3w_team_cap(e) * 2) return cudaErrorInvalidValue;
