@@ -1,7 +1,7 @@
 #!/usr/bin/env python3
 """Small pass through every kernel of the library (K1, K2, KW with and without directions for both strip widths, the
 team-scheduled long-pair path, KT, the PSSM fill, the staged batch API) in a few seconds: the run to put under a
-profiler or a debugger (`python tools/exercise_kernels.py [k1 k2 kw team search k3 glocal pssm staged static]`).  No oracle here -- the parity
+profiler or a debugger (`python tools/exercise_kernels.py [k1 k2 kw team search k3 k3w glocal pssm staged static]`).  No oracle here -- the parity
 tests check the values.
 """
 import os
@@ -107,6 +107,17 @@ def main():
         print("staged", float(np.asarray(sc).sum()))
         bt.free()
         eng.close()
+    if want("k3w"):                                                # int32 tile path of single long pairs, forced onto two small pairs
+        os.environ["SWB_NO_K3"] = "1"; os.environ["SWB_K3W_MIN"] = "1"
+        try:
+            for mode in (swb.ALIGN_LOCAL, swb.ALIGN_GLOBAL):
+                eng = swb.SequenceAlignment(swb.SubstitutionMatrix.get_mat_matrix(2.0, -3.0), 5.0, 2.0, mode)
+                s1 = rand(rng, 1, 2500, 2500)[0]
+                r = eng.align_list([s1, s1[:300]], [s1[100:2400], s1[:290]], True)
+                print("k3w", mode, r[0]["score"], eng.stats()["k3_pairs"])
+                eng.close()
+        finally:
+            os.environ.pop("SWB_NO_K3", None); os.environ.pop("SWB_K3W_MIN", None)
     if want("static"):                                             # allocation-free scorer: scratch in a static __device__ array
         import ctypes
         import torch
