@@ -330,7 +330,14 @@ static int align_pair_k3w(swb_engine *e, const uint8_t *d_a, const uint8_t *d_b,
     const float inv = 1.0f / (float)e->scale;
     const bool dyadic = (e->scale & (e->scale - 1)) == 0;
     auto to_f = [&](int64_t s) { return dyadic ? (float)s * inv : (float)((double)s / e->scale); };
-    int64_t c4, rw, sc; k3w_sizes(J.la, J.lb, &c4, &rw, &sc);
+    // more columns than rows = more sweeps side by side and fewer row steps: a pair with la > lb runs transposed (see K3)
+    // (global mode only: a local fill finds the end cell itself, and its first-maximum order -- rows, then columns,
+    //  SA.rs:286-294 -- is not the transposed problem's)
+    bool swp = e->mode == SWB_GLOBAL && J.la > J.lb && !getenv("SWB_K3W_NOSWAP");
+    for (int r = 0; r < e->n && swp; ++r)
+        for (int c = 0; c < r; ++c) if (e->mat[(size_t)r * e->n + c] != e->mat[(size_t)c * e->n + r]) { swp = false; break; }
+    const int32_t la_k = swp ? J.lb : J.la, lb_k = swp ? J.la : J.lb;
+    int64_t c4, rw, sc; k3w_sizes(la_k, lb_k, &c4, &rw, &sc);
     const size_t colb_bytes = ((size_t)c4 * 16 + 255) & ~(size_t)255, need = colb_bytes + (size_t)rw * 4 + 64;
     if (need > e->dir_bytes) {                                  // engine-owned arena, grown on demand and kept
         CUDA_TRY(e, cudaStreamSynchronize(e->stream));
@@ -342,8 +349,8 @@ static int align_pair_k3w(swb_engine *e, const uint8_t *d_a, const uint8_t *d_b,
     uint4 *d_colb = reinterpret_cast<uint4 *>(e->d_dir);
     unsigned *d_rowb = reinterpret_cast<unsigned *>((char *)e->d_dir + colb_bytes);
     const int64_t out_total = (int64_t)J.la + J.lb + 1;
-    K3Pair P; P.a_off = J.a_off; P.b_off = J.b_off; P.la = J.la; P.lb = J.lb; P.colb_off = 0; P.rowb_off = 0; P.out_off = 0;
-    P.start_state = 0; P.score = 0; P.swap = 0; P.pad_ = 0; P.cx0 = 0; P.cy0 = 0;
+    K3Pair P; P.a_off = J.a_off; P.b_off = J.b_off; P.la = la_k; P.lb = lb_k; P.colb_off = 0; P.rowb_off = 0; P.out_off = 0;
+    P.start_state = 0; P.score = 0; P.swap = swp ? 1 : 0; P.pad_ = 0; P.cx0 = 0; P.cy0 = 0;
     DevBuf d_pair, d_res, d_scr, d_xa, d_xb, d_nc;
     CUDA_TRY(e, d_pair.alloc(sizeof(K3Pair), e->stream)); CUDA_TRY(e, d_res.alloc(sizeof(KWResult), e->stream));
     CUDA_TRY(e, d_scr.alloc((size_t)sc * sizeof(int), e->stream));
@@ -377,10 +384,12 @@ static int align_pair_k3w(swb_engine *e, const uint8_t *d_a, const uint8_t *d_b,
     e->stats.kernel_ms += ms; e->stats.launches += 3; e->stats.k3_pairs += 1;
     e->stats.d2h_bytes += 8.0 * nc + sizeof(KWResult) + 4;
     std::vector<int64_t> xa(nc), xb(nc);
-    for (int64_t c = 0; c < nc; ++c) { xa[c] = hxa[nc - 1 - c]; xb[c] = hxb[nc - 1 - c]; }       // reverse (SA.rs:384-385)
+    const int32_t *la_list = swp ? hxb : hxa, *lb_list = swp ? hxa : hxb;                          // transposed: rows were b
+    for (int64_t c = 0; c < nc; ++c) { xa[c] = la_list[nc - 1 - c]; xb[c] = lb_list[nc - 1 - c]; }   // reverse (SA.rs:384-385)
     std::string ra, rb;
     inflate(J.ra, J.la_full, J.rb, J.lb_full, xa.data(), xb.data(), nc, e->mode, retain_all, ra, rb);
-    if (fill_out(out, to_f(hr[0].score), hr[0].end_i, hr[0].end_j, xa, xb, ra, rb) != SWB_OK) { e->err = "out of memory"; return SWB_ERR_NOMEM; }
+    const int64_t ei = swp ? hr[0].end_j : hr[0].end_i, ej = swp ? hr[0].end_i : hr[0].end_j;
+    if (fill_out(out, to_f(hr[0].score), ei, ej, xa, xb, ra, rb) != SWB_OK) { e->err = "out of memory"; return SWB_ERR_NOMEM; }
     return SWB_OK;
 }
 

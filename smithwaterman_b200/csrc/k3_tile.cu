@@ -841,7 +841,7 @@ cudaError_t k3w_launch(const swb_engine *e, const uint8_t *d_a, const uint8_t *d
     int4 *d_cand = reinterpret_cast<int4 *>(d_scratch + (sweeps + 3) / 4 * 4);
     cudaError_t err = cudaMemsetAsync(d_prog, 0, (size_t)((sweeps + 3) / 4 * 4) * sizeof(int), st);
     if (err != cudaSuccess) return err;
-    const uint8_t *pa = d_a + hp.a_off, *pb = d_b + hp.b_off;
+    const uint8_t *pa = hp.swap ? d_b + hp.b_off : d_a + hp.a_off, *pb = hp.swap ? d_a + hp.a_off : d_b + hp.b_off;   // transposed: rows = b
     int la = hp.la, lb = hp.lb, nl_ = nl, open = e->o, ext = e->e;
     const int32_t *mat = e->d_mat;
     int *rowb_i = reinterpret_cast<int *>(d_rowb);
