@@ -536,11 +536,15 @@ def test_cli_list_mode_vs_emboss(emboss, flag, key, tmp_path):
         assert float(ln[0]) == r[key]["score"]
 
 
+@pytest.mark.parametrize("path", ["default", "wide"])
 @pytest.mark.parametrize("seed", range(6))
-def test_fuzz_random_models(seed):
+def test_fuzz_random_models(seed, path, monkeypatch):
     """Random scoring models (random integer / half-integer matrices over a random alphabet with X, random penalties
     including open < extend, which K1 must hand to the exact 3-state kernel), all three modes, lengths 0..90 with
-    low-complexity sequences (many ties): score batch and full alignments vs the oracle."""
+    low-complexity sequences (many ties): score batch and full alignments vs the oracle.  path "wide": the alignments
+    are forced onto the int32 tile path (K3W + KT3) wherever it applies (local / global, open >= extend)."""
+    if path == "wide":
+        monkeypatch.setenv("SWB_NO_K3", "1"); monkeypatch.setenv("SWB_K3W_MIN", "1")
     rng = np.random.default_rng(9000 + seed)
     nlet = int(rng.integers(3, 12))
     letters = "X" + "".join(rng.choice(list("ACDEFGHIKLMNPQRSTVWY"), nlet - 1, replace=False))
