@@ -215,6 +215,7 @@ def other_configs(swb, dev):
         return sa, sb
     dna = swb.SubstitutionMatrix.get_mat_matrix(2.0, -3.0)
     for tag, mode, n, length, sub, indel in (("configs[3] 100 kb x 100 kb DNA pair, local, full traceback", swb.ALIGN_LOCAL, 1, 100000, 0.08, 0.02),
+                                             ("configs[3] 100 kb x 100 kb DNA pair, global, full traceback", swb.ALIGN_GLOBAL, 1, 100000, 0.08, 0.02),
                                              ("configs[4] 256 x 10 kb DNA pairs, global, strings", swb.ALIGN_GLOBAL, 256, 10000, 0.05, 0.05)):
         sa, sb = noisy(n, length, sub, indel)
         eng = swb.SequenceAlignment(dna, 5.0, 2.0, mode, device=dev)
@@ -223,7 +224,7 @@ def other_configs(swb, dev):
         cells = float(sum(len(x) * len(y) for x, y in zip(sa, sb)))
         out[tag] = {"gcups": cells / dt / 1e9, "seconds": dt, "device_ms": eng.stats()["kernel_ms"],
                     "gcups_device": cells / (eng.stats()["kernel_ms"] * 1e-3) / 1e9, "score0": r[0]["score"]}
-        if n == 1:                                             # the same pair through checkpointed recompute (256 MB of direction bytes)
+        if n == 1 and mode == swb.ALIGN_LOCAL:                 # the same pair through checkpointed recompute (256 MB of direction bytes)
             os.environ["SWB_CKPT_BYTES"] = str(256 << 20)
             try:
                 t0 = time.perf_counter(); c = eng.align_list(sa, sb, True); dt = time.perf_counter() - t0

@@ -1043,6 +1043,33 @@ def test_packed_traceback_path_global(go, ge, protein, swap, monkeypatch):
     eng.close()
 
 
+@pytest.mark.parametrize("go,ge", [(5.0, 2.0), (10.0, 0.5)])
+def test_wide_tile_path_20kb_default_routing(go, ge):
+    """A 20 kb x ~20 kb DNA pair (4e8 cells, score outside s16) takes the int32 tile path by default routing, with both gap
+    models SURVEY 8(d) names for configs[3] (5/2 and 10/0.5, the latter on the half-integer grid): score and end cell
+    against the linear-memory integer oracle, the strings re-score to the score and spell the inputs."""
+    rng = np.random.default_rng(31 + int(go))
+    a = _rand_seqs(rng, 1, 20500, 20500, "ACGT")[0]
+    b = _mutate(rng, a, 0.08, 0.02, 0.02)
+    m = swb.SubstitutionMatrix.get_mat_matrix(2.0, -3.0)
+    om = _omatrix(m)
+    scale = 1 if float(ge).is_integer() else 2
+    ia, oa = O.pack([om.seq_to_index(a.decode())]); ib, ob = O.pack([om.seq_to_index(b.decode())])
+    for mode in (swb.ALIGN_LOCAL, swb.ALIGN_GLOBAL):
+        eng = swb.SequenceAlignment(m, go, ge, mode)
+        out = eng.align_raw(a, b, False)
+        assert eng.stats()["k3_pairs"] == 1
+        osc, oi, oj = O.score_batch_int(ia, oa, ib, ob, np.rint(m.scores * scale).astype(np.int32), -int(round(go * scale)),
+                                        -int(round(ge * scale)), scale, mode, 1)
+        assert (out["score"], out["end_a"], out["end_b"]) == (float(osc[0]) / scale, int(oi[0]), int(oj[0]))
+        assert _rescore(out["aln_a"], out["aln_b"], 2.0, -3.0, go, ge) == out["score"]
+        if mode == swb.ALIGN_GLOBAL:
+            assert out["aln_a"].replace("-", "") == a.decode() and out["aln_b"].replace("-", "") == b.decode()
+        else:
+            assert out["aln_a"].replace("-", "") in a.decode() and out["aln_b"].replace("-", "") in b.decode()
+        eng.close()
+
+
 @pytest.mark.parametrize("mode", [swb.ALIGN_LOCAL, swb.ALIGN_GLOBAL])
 @pytest.mark.parametrize("go,ge,protein", [(5.0, 2.0, False), (10.0, 0.5, True), (2.0, 2.0, False)])
 def test_wide_tile_path_small_pairs(go, ge, protein, mode, monkeypatch):
