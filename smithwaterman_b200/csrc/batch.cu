@@ -925,6 +925,15 @@ static int score_pipeline(swb_engine *e, const char *a_all, const int64_t *off_a
         if (n - next < chunk_first) next = n;                // no crumbs at the end
         cuts.push_back(next);
     }
+    // a tapered tail (tuning knob, off by default): when the copy engine is the bottleneck (eight ranks behind one host) the DP
+    // of the last chunk runs after everything else has finished, so SWB_CHUNK_LAST cuts the last chunk down.  On one GPU,
+    // where the DP is the bottleneck, the extra launch costs its own floor: measured 24.7 -> 26.4 ms (65536) / 27.0 ms (32768)
+    int64_t chunk_last = 0;
+    if (const char *v = getenv("SWB_CHUNK_LAST")) chunk_last = std::max<int64_t>(0, atoll(v));
+    if (chunk_last >= 1024 && cuts.size() >= 3) {
+        const int64_t beg = cuts[cuts.size() - 2], len = n - beg;
+        if (len > 2 * chunk_last) cuts.insert(cuts.end() - 1, n - chunk_last);
+    }
     if (cuts.size() == 1) cuts.push_back(0);
     const int64_t n_chunks = (int64_t)cuts.size() - 1;
     const size_t need = (size_t)n * (sizeof(float) + 2 * sizeof(int64_t)) + (size_t)n_chunks * 8192;    // staging for pageable callers
