@@ -243,7 +243,7 @@ static int align_jobs_k3(swb_engine *e, const uint8_t *d_a, const uint8_t *d_b, 
             rw = (rw + 3) / 4 * 4;
             if (!hp.empty() && (colb + c4) * 16 + (rowb + rw) * 4 > budget) break;
             K3Pair P; P.a_off = J.a_off; P.b_off = J.b_off; P.la = la_k; P.lb = lb_k; P.colb_off = colb; P.rowb_off = rowb; P.out_off = out_total;
-            P.start_state = 0; P.score = J.known_score == INT32_MIN ? 0 : J.known_score; P.swap = swp ? 1 : 0; P.pad_ = 0; P.cx0 = 0; P.cy0 = 0;
+            P.start_state = 0; P.score = J.known_score == INT32_MIN ? 0 : J.known_score; P.swap = swp ? 1 : 0; P.find_col = 0; P.cx0 = 0; P.cy0 = 0;
             hp.push_back(P);
             max_sweeps = std::max(max_sweeps, (lb_k + 1023) / 1024);
             colb += c4; rowb += rw; out_total += (int64_t)J.la + J.lb + 1;
@@ -350,7 +350,7 @@ static int align_pair_k3w(swb_engine *e, const uint8_t *d_a, const uint8_t *d_b,
     unsigned *d_rowb = reinterpret_cast<unsigned *>((char *)e->d_dir + colb_bytes);
     const int64_t out_total = (int64_t)J.la + J.lb + 1;
     K3Pair P; P.a_off = J.a_off; P.b_off = J.b_off; P.la = la_k; P.lb = lb_k; P.colb_off = 0; P.rowb_off = 0; P.out_off = 0;
-    P.start_state = 0; P.score = 0; P.swap = swp ? 1 : 0; P.pad_ = 0; P.cx0 = 0; P.cy0 = 0;
+    P.start_state = 0; P.score = 0; P.swap = swp ? 1 : 0; P.find_col = 0; P.cx0 = 0; P.cy0 = 0;
     DevBuf d_pair, d_res, d_scr, d_xa, d_xb, d_nc;
     CUDA_TRY(e, d_pair.alloc(sizeof(K3Pair), e->stream)); CUDA_TRY(e, d_res.alloc(sizeof(KWResult), e->stream));
     CUDA_TRY(e, d_scr.alloc((size_t)sc * sizeof(int), e->stream));

@@ -468,7 +468,7 @@ k3w_pick_kernel(const int4 *__restrict__ cand, int n_cand, int open, K3Pair *pai
         pair->score = best.x - open;
         pair->cx0 = best.x > open ? best.y : -1;
         pair->cy0 = best.x > open ? best.z : -1;                     // the LAST column of the pass that holds the end cell:
-        pair->pad_ = 1;                                              // the walker finds the column itself (first MATCH == score in that row)
+        pair->find_col = 1;                                              // the walker finds the column itself (first MATCH == score in that row)
     }
 }
 
@@ -648,7 +648,7 @@ kt3_walk_kernel(const uint8_t *__restrict__ a_all, const uint8_t *__restrict__ b
     int32_t *xa = idx_a + P.out_off, *xb = idx_b + P.out_off;
     const int sx = P.cx0 ? P.cx0 : la, sy = P.cy0 ? P.cy0 : lb;     // the cell the walk starts at (wide local form: found by the fill)
     if (threadIdx.x == 0) { W.cx = max(sx, 0); W.cy = max(sy, 0); W.st = P.start_state; W.n = 0; W.score = P.score; W.done = (sx < 0) ? 1 : 0; W.sy = sy; }
-    bool need_col = WIDE && MODE == SWB_LOCAL && P.pad_ == 1 && sx >= 1;      // sy is the end of the start cell's pass, not yet its column
+    bool need_col = WIDE && MODE == SWB_LOCAL && P.find_col == 1 && sx >= 1;      // sy is the end of the start cell's pass, not yet its column
     if (lane == 0) sm_all[wib].tcx = -1;
     bool need_start = (MODE != SWB_LOCAL);
     int va = 0, vb = 0;                                              // warp 0: lane (n & 31) holds column n of the lists (one coalesced store per 32 columns)

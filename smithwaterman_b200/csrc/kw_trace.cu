@@ -28,7 +28,6 @@
 
 #include "swb_internal.h"
 
-#define KW_WARPS 8
 #define KT_AHEAD 16
 
 int64_t kw_dir_bytes(int32_t la, int32_t lb, int cols)

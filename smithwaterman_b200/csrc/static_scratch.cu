@@ -155,7 +155,7 @@ extern "C" int swb_score_batch_static(swb_engine *e, const char *d_a_all, const 
     KWPlan pl;                                                     // one warp per pair, 256-column strips, no teams: a plain launch
     pl.cols = 8; pl.team_warps = 1;
     pl.n_teams = (int)std::min<int64_t>(n, SS_TEAMS);
-    pl.blocks = (pl.n_teams + 7) / 8;
+    pl.blocks = (pl.n_teams + KW_WARPS - 1) / KW_WARPS;
     pl.bnd_elems = (int64_t)SS_RING_ELEMS * SS_TEAMS;
     pl.scratch_ints = n * SS_SCR_INTS;                             // cleared by kw_launch (cudaMemsetAsync on st)
     pl.dir_bytes = 0;

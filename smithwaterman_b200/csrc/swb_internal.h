@@ -128,6 +128,7 @@ cudaError_t k2_launch(const swb_engine *e, const uint8_t *d_query, int la, const
                       int *d_counter, K1Result *d_res, int n_blocks, cudaStream_t st);
 
 // KW: one warp per pair, exact 3-state int32 recurrence (all modes), optional direction bytes.
+#define KW_WARPS 8                  // warps per block of kw_kernel (a plan's `blocks` = ceil(team warps / KW_WARPS))
 struct KWPair {
     int64_t a_off, b_off;           // offsets into the code arrays
     int32_t la, lb;
@@ -233,7 +234,8 @@ struct K3Pair {
     int32_t start_state;            // local: 0 (MATCH); global: taken from the recomputed cell (la, lb)
     int32_t score;                  // local: the scan's score (scaled); global: filled in by the walker
     int32_t swap;                   // 1: the kernels run the TRANSPOSED problem (rows = b, columns = a; la / lb above are the transposed
-    int32_t pad_;                   //    extents): a tall box becomes a wide one, whose sweeps pipeline over a team of warps
+                                    //    extents): a tall box becomes a wide one, whose sweeps pipeline over a team of warps
+    int32_t find_col;               // wide local form: 1 = cy0 is the LAST column of the pass that holds the start cell, the walker finds the column
     int32_t cx0, cy0;               // wide (int32) form: the cell the walk starts at, inside a border store laid out for la x lb
 };                                  //    (0, 0 = (la, lb); -1 = local score 0, nothing to walk); written by k3w_pick_kernel in local mode
 // K3W: the int32 form of K3 for ONE long pair whose scores leave the s16 range (100 kb DNA pairs): sweeps spread over the
